@@ -1,0 +1,133 @@
+/*
+ * b200mp.h -- C ABI of the B200-native (sm_100a) message-passing kernels.
+ *
+ * This is the drop-in boundary one level below the reference's torch.nn.Module API
+ * (src/nn/gnn/gine.py:80-91, src/nn/gnn/pna.py:90-101 in the reference).  The reference
+ * itself binds no native code on this path: everything below replaces *third-party*
+ * operator calls (torch_geometric 2.5.3 / ATen) made from the cited reference lines.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless named host_*; tensors are dense row-major;
+ *   - fp32 activations ("float"), int64 indices at the reference-facing surface
+ *     (edge_index, perm, colptr), int32 indices inside the kernels (E, N < 2^31);
+ *   - `stream` is a cudaStream_t passed as void*; calls enqueue work and return, they never
+ *     synchronise, never allocate device memory (the caller passes workspaces) and never
+ *     throw;  return value 0 = ok, >0 = cudaError_t of the failed launch, <0 = B200MP_E*.
+ *   - "segment order": edges sorted (stably) by the node they are aggregated at.  For the
+ *     forward direction that is CSC order (sorted by destination); e-storage is kept in that
+ *     order for the whole backbone, so edge tensors stream sequentially from HBM.
+ */
+#ifndef B200MP_H
+#define B200MP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200MP_EINVAL   (-1)   /* bad argument (unsupported H, null pointer, ...) */
+#define B200MP_EWORKSP  (-2)   /* workspace too small */
+
+/* Library / device introspection. */
+int b200mp_version(void);
+/* Number of CTAs the persistent edge kernels are launched with (= rows of the per-CTA
+ * weight-gradient partial buffers the caller must allocate). */
+int b200mp_partial_rows(int* rows);
+/* Edges per tile of the per-edge kernels for hidden width H (callers size n_part with it). */
+int b200mp_tile_edges(int H, int* te);
+
+/* ------------------------------------------------------------------ graph structure
+ * Replaces torch_geometric `to_csc` reached from create_graph (src/datasets/util/graph.py:31-57)
+ * and `sampler.edge_permutation` (src/datasets/ibm_transactions_for_aml.py:91):
+ *   perm   = stable argsort(key)          int64 [E]
+ *   ptr    = index2ptr(key[perm], N)      int64 [N+1]
+ *   other  = other_end[perm]              int64 [E]   (CSC `row` when key = dst)
+ *   other32/key32 = int32 copies in sorted order (kernel-side arrays)
+ * Bit-exact. */
+int b200mp_csc_workspace_bytes(int64_t E, int64_t N, size_t* bytes);
+int b200mp_csc_build(const int64_t* key, const int64_t* other_end, int64_t E, int64_t N,
+                     int64_t* perm, int64_t* ptr, int64_t* other,
+                     int32_t* other32, int32_t* key32,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* In-degree and its histogram (main.py:284-286, utils.py:179-182):
+ *   deg[v] = ptr[v+1]-ptr[v];  *max_deg (device scalar) = max(deg);  hist = bincount(deg). */
+int b200mp_degree(const int64_t* ptr, int64_t N, int64_t* deg, int64_t* max_deg, void* stream);
+int b200mp_bincount(const int64_t* vals, int64_t n, int64_t* hist, int64_t nbins, void* stream);
+
+/* Batch relabel (src/utils/batch_processing.py:65-72, ibm_transactions_for_aml.py:166-173):
+ *   nodes = unique(ids) ascending (first *n_unique entries of `nodes` valid),
+ *   local[i] = rank of ids[i] in nodes. */
+int b200mp_relabel_workspace_bytes(int64_t M, size_t* bytes);
+int b200mp_relabel(const int64_t* ids, int64_t M, int64_t* nodes, int64_t* n_unique,
+                   int64_t* local, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Row permutation of an [n,H] fp32 matrix: out[i] = in[idx[i]] / out[idx[i]] = in[i]. */
+int b200mp_gather_rows(const float* in, const int64_t* idx, float* out, int64_t n, int H, void* stream);
+int b200mp_scatter_rows(const float* in, const int64_t* idx, float* out, int64_t n, int H, void* stream);
+
+/* ------------------------------------------------------------------ per-edge linear (forward)
+ * One pass over E edges in segment order k = 0..E-1; H in {16,32,64,128}.
+ *   z_k   = e[row(k)] W1^T + b1 + T1[idx1[k]] + T2[idx2[k]]        (T1/T2 nullable)
+ *   mode 0: out1[k] = z_k                      PNAConv message with hoisted node terms
+ *                                              (pna.py:71-74 -> PyG PNAConv.message)
+ *   mode 1: out1[k] = relu(z_k)                GINEConv message (gine.py:66-70)
+ *   mode 2: out1[k] = h_k = relu(z_k);  out2[row(k)] = alpha e[row(k)] + beta (h_k W2^T + b2)
+ *                                              edge update (gine.py:88-89, pna.py:97-99,
+ *                                              models/fused.py:254)
+ * row(k) = eid ? eid[k] : k  (eid maps segment order -> e-storage row; null = identity). */
+int b200mp_edge_linear_fwd(int mode, int H, int64_t E,
+                           const float* e, const int32_t* eid,
+                           const float* W1, const float* b1,
+                           const float* T1, const int32_t* idx1,
+                           const float* T2, const int32_t* idx2,
+                           const float* W2, const float* b2, float alpha, float beta,
+                           float* out1, float* out2, void* stream);
+
+/* ------------------------------------------------------------------ segmented reductions
+ * Replaces PyG DegreeScalerAggregation's scatter kernels (mean/min/max/std; App. A.2 of
+ * SURVEY.md) and GINEConv's scatter_add, without atomics.
+ * Segments with more than `light_max` rows are split into chunks of `chunk` rows listed in
+ * hchunk_* (built once per graph), reduced to partials and combined in order.
+ *   kind 0 (PNA): agg[N,4H] = [mean | min | max | std], tie[N,2H] = multiplicity of min | max
+ *   kind 1 (sum): agg[N,H]  = sum                              (tie unused) */
+int b200mp_segment_reduce_fwd(int kind, int H, int64_t N, const int64_t* ptr, const float* m,
+                              float* agg, float* tie,
+                              int64_t light_max, int64_t chunk,
+                              int64_t n_heavy, const int32_t* heavy_node, const int32_t* heavy_chunk_ptr,
+                              int64_t n_chunks, const int32_t* chunk_heavy, const int64_t* chunk_begin,
+                              float* partial /* [n_chunks, 6H] */, void* stream);
+
+/* ------------------------------------------------------------------ per-edge backward
+ * Message backward (autograd of the mode 0 / mode 1 forward + its reduction):
+ *   kind 0 (PNA):  G_k = c0[d] + c1[d] m_k + gmin'[d] [m_k==min[d]] + gmax'[d] [m_k==max[d]]
+ *                  with node_in = coef[N,6H] = [c0 | c1 | gmin' | min | gmax' | max]
+ *   kind 1 (GINE): G_k = node_in[d] [m_k > 0],  node_in = grad_agg[N,H]
+ *   d = seg[k].  Then
+ *     gT1[nbr[k]] += G_k                  (vector atomics)
+ *     g_e[row(k)] (+)= G_k W              (accumulate != 0 adds to the existing value)
+ *     gW_part[cta]  = sum_k G_k^T e_k ,  gb_part[cta] = sum_k G_k     (per-CTA partials) */
+int b200mp_message_bwd(int kind, int H, int64_t E,
+                       const float* m, const float* e, const int32_t* eid,
+                       const float* node_in, const int32_t* seg, const int32_t* nbr,
+                       const float* W, float* g_e, int accumulate, float* gT1,
+                       float* gW_part, float* gb_part, int n_part, void* stream);
+
+/* Edge-update backward (mode 2).  g_out = dL/d out2 [E,H] (e-storage order = segment order).
+ *   g_e = alpha g_out + Gh W1 ,  Gh = (beta g_out W2) * [h>0]
+ *   gP[src[k]] += Gh_k ,  gQ[dst[k]] += Gh_k  (run-length reduced over equal consecutive dst)
+ *   partials of grad W1, b1, W2, b2 per CTA. */
+int b200mp_edge_update_bwd(int H, int64_t E,
+                           const float* g_out, const float* h, const float* e,
+                           const int32_t* src, const int32_t* dst,
+                           const float* W1, const float* W2, float alpha, float beta,
+                           float* g_e, float* gP, float* gQ,
+                           float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part,
+                           int n_part, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200MP_H */
