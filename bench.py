@@ -1,0 +1,360 @@
+#!/usr/bin/env python
+"""bench.py -- message-passing edges/s (fwd+bwd) of the L-layer PNA (or GINE) backbone on a
+synthetic transaction graph of a named shape, one process per GPU.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload hi_medium|hi_small|tiny]
+                    [--model pna|gine] [--impl b200|reference]
+
+Prints ONE JSON line (rank 0).  `value` = edges/s with inputs resident in HBM and the graph
+structure already built; `e2e` = the same through the public module API from pinned HOST buffers
+(H2D of x / edge_index / edge features, CSC build, fwd+bwd, D2H of the loss) every step;
+`roofline` = the dominant kernel's algorithmic bytes / CUDA-event time against the measured HBM
+peak; `cpu_baseline` = the CPU oracle (port of the reference path) on a bounded sample.
+`--impl reference` times that CPU path alone (the reference has no GPU-independent build here:
+torch_geometric is absent).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {   # name: (nodes, edges, seed)  -- SURVEY.md section 8(d)
+    "hi_medium": (2_077_023, 31_898_238, 20240721),
+    "hi_small": (515_080, 5_078_345, 20240719),
+    "tiny": (8_989, 5_198 * 16, 20240718),
+}
+H, LAYERS = 64, 2
+CPU_SAMPLE_EDGES = 1_000_000
+
+
+def synth_graph(n, e, seed, device):
+    """src uniform; dst = P[floor(n u^3)] (heavy-tailed in-degree, hubs); 10 % self loops;
+    generation order (unsorted)."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    src = torch.randint(0, n, (e,), generator=g, device=device)
+    u = torch.rand(e, generator=g, device=device, dtype=torch.float64)
+    P = torch.randperm(n, generator=g, device=device)
+    dst = P[(u ** 3 * n).long().clamp_(max=n - 1)]
+    loops = torch.rand(e, generator=g, device=device) < 0.1
+    dst = torch.where(loops, src, dst)
+    return torch.stack([src, dst])
+
+
+def make_model(kind, deg_hist, device):
+    import b200mp
+    torch.manual_seed(1234)
+    if kind == "pna":
+        m = b200mp.PNAS(num_features=H, num_gnn_layers=LAYERS, n_hidden=H, edge_updates=True, edge_dim=H, deg=deg_hist)
+    else:
+        m = b200mp.GINe(num_features=H, num_gnn_layers=LAYERS, n_hidden=H, edge_updates=True, edge_dim=H)
+    return m.to(device).train()
+
+
+def algorithmic_bytes_per_edge(kind):
+    """compulsory [E,H]-row touches per layer fwd+bwd, fp32."""
+    s = 4
+    return (22 if kind == "pna" else 19) * s * H + 64
+
+
+# algorithmic bytes per edge of each kernel (DESIGN.md "kernels"): [E,H] rows read/written or
+# gathered/scattered once, plus the int32 index reads
+KERNEL_BYTES = {
+    "pna_message_fwd": 3 * 4 * H + 8,      # read e, gather B[src], write m (+ A[dst] cached) ; src,dst ids
+    "gine_message_fwd": 3 * 4 * H + 4,
+    "segment_reduce_pna": 1 * 4 * H,       # read m
+    "segment_reduce_sum": 1 * 4 * H,
+    "edge_update_fwd": 4 * 4 * H + 8,      # read e, gather P[src], write h, write e'
+    "edge_update_bwd": 5 * 4 * H + 8,      # read g_e', h, e; write g_e; scatter g_P[src]
+    "pna_message_bwd": 4 * 4 * H + 8,      # read m, e; write g_e; scatter g_B[src]
+    "gine_message_bwd": 4 * 4 * H + 8,
+    "permute_rows": 2 * 4 * H + 8,
+}
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_reference_steps(kind, steps, warmup, threads=None):
+    """The CPU restatement of the reference path (oracle/models.py: reference model files'
+    layer loop over restated PyG ops), fwd+bwd, on a bounded sample of the workload shape:
+    CPU_SAMPLE_EDGES edges at the workload's edge/node ratio.  Returns (edges/s, cores, sample)."""
+    import b200mp
+    from oracle import models as OM
+    cores = threads or os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    n_full, e_full, seed = WORKLOADS["hi_medium"]
+    e = CPU_SAMPLE_EDGES
+    n = max(2, int(round(n_full * e / e_full)))
+    ei = synth_graph(n, e, seed, "cpu")
+    deg_hist = torch.bincount(torch.bincount(ei[1], minlength=n))
+    torch.manual_seed(1234)
+    if kind == "pna":
+        mod = b200mp.PNAS(num_features=H, num_gnn_layers=LAYERS, n_hidden=H, edge_updates=True, edge_dim=H, deg=deg_hist)
+    else:
+        mod = b200mp.GINe(num_features=H, num_gnn_layers=LAYERS, n_hidden=H, edge_updates=True, edge_dim=H)
+    p = {k: v.clone() for k, v in mod.state_dict().items()}
+    for k, v in p.items():
+        v.requires_grad_(v.is_floating_point() and "running" not in k and "avg_deg" not in k and not k.endswith("eps"))
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(n, H, generator=g).requires_grad_(True)
+    ea = torch.randn(e, H, generator=g).requires_grad_(True)
+    gx, ge = torch.randn(n, H, generator=g), torch.randn(e, H, generator=g)
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        ox, oe = OM.mp_stack(p, kind, x, ei, ea, LAYERS, True, False, True)
+        torch.autograd.backward([ox, oe], [gx, ge])
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    sample = f"{e} edges / {n} nodes (hi_medium edge/node ratio, same generator), {warmup} warm-up + {steps} timed fwd+bwd steps"
+    return e * len(times) / sum(times), cores, sample, sum(times) / len(times)
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    steps, warmup = max(1, min(args.steps, 3)), max(1, min(args.warmup, 1))
+    eps, cores, sample, sec = cpu_reference_steps(args.model, steps, warmup)
+    line = {
+        "impl": "reference", "metric": "message-passing edges/sec (fwd+bwd)", "value": eps, "unit": "edges/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, world),
+        "cpu_baseline": {"value": eps, "unit": "edges/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": eps, "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "CPU oracle port of the reference path (reference model files' layer loop over restated PyG 2.5.3 ops); "
+                "the reference itself cannot be installed: torch_geometric / pytorch-frame fork are absent (DESIGN.md)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world):
+    n, e, _ = WORKLOADS[args.workload]
+    return {"workload": f"{args.model.upper()} backbone ({LAYERS} layers, H={H}, edge updates) fwd+bwd on synthetic "
+                        f"{args.workload} shape: {n} accounts, {e} transactions per GPU",
+            "nodes": n, "edges": e, "layers": LAYERS, "hidden": H, "model": "PNAS" if args.model == "pna" else "GINe",
+            "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (one graph per GPU; dst-range partition + halo all-gather not built yet)",
+            "l2": "inputs exceed L2 (every [E,H] tensor >> 126 MB)"}
+
+
+def run_b200(args, rank, world, local_rank):
+    import torch.distributed as dist
+
+    import b200mp
+    from b200mp import functional as BF
+    from b200mp import graph as BG
+
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    n, e, seed = WORKLOADS[args.workload]
+    ei = synth_graph(n, e, seed + rank, dev)
+    st = b200mp.edge_structure(ei, n)
+    _, deg_hist = b200mp.degree_histogram(st.fwd.ptr)
+    model = make_model(args.model, deg_hist.cpu(), dev)
+    g = torch.Generator(device=dev).manual_seed(seed)
+    x = torch.randn(n, H, generator=g, device=dev).requires_grad_(True)
+    ea = torch.randn(e, H, generator=g, device=dev).requires_grad_(True)
+    gx = torch.randn(n, H, generator=g, device=dev)
+    ge = torch.randn(e, H, generator=g, device=dev)
+
+    def step():
+        ox, oe = model.message_passing(x, ei, ea)
+        torch.autograd.backward([ox, oe], [gx, ge])
+        x.grad = None
+        ea.grad = None
+        model.zero_grad(set_to_none=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    stats = BF.KernelStats(timing=True)
+    clocks = ClockSampler(local_rank)
+    barrier()
+    clocks.start()
+    BF.set_kernel_stats(stats)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(args.steps):
+        step()
+    t1.record()
+    barrier()
+    BF.set_kernel_stats(None)
+    clk = clocks.stop()
+    ms = t0.elapsed_time(t1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_step = ms / args.steps
+    value = world * e / (ms_step * 1e-3)
+
+    # per-kernel accounting -> roofline of the dominant kernel
+    summ = stats.summary()
+    peak, peak_src = measured_peak_gbs()
+    kern = {}
+    for name, (calls, total_ms) in summ.items():
+        per = total_ms / calls
+        kern[name] = {"calls_per_step": calls / args.steps, "ms_per_call": round(per, 4),
+                      "share_of_step": round(total_ms / ms, 4),
+                      "achieved_gbs": round(KERNEL_BYTES[name] * e / (per * 1e-3) / 1e9, 1)}
+    top = max(summ.items(), key=lambda kv: kv[1][1])[0]
+    achieved = kern[top]["achieved_gbs"]
+    roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": KERNEL_BYTES[top] * e}
+    step_bytes = LAYERS * (e * algorithmic_bytes_per_edge(args.model) + n * 12 * 4 * H)
+    step_roofline = {"algorithmic_bytes_per_step": step_bytes, "achieved_gbs": round(step_bytes / (ms_step * 1e-3) / 1e9, 1),
+                     "frac": round(step_bytes / (ms_step * 1e-3) / 1e9 / peak, 4),
+                     "formula": "L*(E*(22*s*H+64) + N*12*s*H), SURVEY.md 8(d)"}
+
+    # end-to-end: pinned host buffers -> device -> CSC build -> fwd+bwd -> loss to host, every step
+    e2e = None
+    try:
+        del st
+        BG.clear_cache()
+        hx, hea, hei = x.detach().cpu().pin_memory(), ea.detach().cpu().pin_memory(), ei.cpu().pin_memory()
+        del ea, ge
+        torch.cuda.empty_cache()
+        h2d = hx.numel() * 4 + hea.numel() * 4 + hei.numel() * 8
+        e2e_steps = max(1, min(args.steps, 3))
+
+        def e2e_step():
+            BG.clear_cache()
+            dx = hx.to(dev, non_blocking=True).requires_grad_(True)
+            dea = hea.to(dev, non_blocking=True).requires_grad_(True)
+            dei = hei.to(dev, non_blocking=True)
+            ox, oe = model.message_passing(dx, dei, dea)
+            loss = ox.square().mean() + oe.square().mean()
+            loss.backward()
+            model.zero_grad(set_to_none=True)
+            return float(loss.item())          # D2H read of the step's result
+
+        e2e_step()
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(e2e_steps):
+            e2e_step()
+        b.record()
+        barrier()
+        ems = a.elapsed_time(b)
+        if world > 1:
+            t = torch.tensor([ems], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ems = float(t.item())
+        e2e = {"value": world * e / (ems / e2e_steps * 1e-3), "unit": "edges/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": 4, "steps": e2e_steps, "ms_per_step": ems / e2e_steps,
+               "includes": "H2D of x, edge_index, edge features from pinned host memory; CSC build; fwd+bwd; loss D2H"}
+    except Exception as ex:          # reported, never silently dropped
+        e2e = {"value": None, "unit": "edges/s", "error": f"{type(ex).__name__}: {ex}"[:300]}
+
+    if rank != 0:
+        return
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        eps, cores, sample, _ = cpu_reference_steps(args.model, 2, 1)
+        cpu = {"value": eps, "unit": "edges/s", "cores": cores, "kind": "port", "sample": sample}
+    line = {
+        "metric": "message-passing edges/sec (fwd+bwd)", "value": value, "unit": "edges/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
+        "clocks": clk, "e2e": e2e, "gpu_launches": stats.launches, "roofline": roofline, "step_roofline": step_roofline,
+        "kernels": kern, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="hi_medium", choices=sorted(WORKLOADS))
+    ap.add_argument("--model", default="pna", choices=["pna", "gine"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if args.warmup < 3:
+        args.warmup = 3
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_b200(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

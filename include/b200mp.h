@@ -102,8 +102,10 @@ int b200mp_segment_reduce_fwd(int kind, int H, int64_t N, const int64_t* ptr, co
 
 /* ------------------------------------------------------------------ per-edge backward
  * Message backward (autograd of the mode 0 / mode 1 forward + its reduction):
- *   kind 0 (PNA):  G_k = c0[d] + c1[d] m_k + gmin'[d] [m_k==min[d]] + gmax'[d] [m_k==max[d]]
- *                  with node_in = coef[N,6H] = [c0 | c1 | gmin' | min | gmax' | max]
+ *   kind 0 (PNA):  G_k = c0[d] + c1[d] (m_k - mean[d]) + gmin'[d] [m_k==min[d]] + gmax'[d] [m_k==max[d]]
+ *                  with node_in = coef[N,7H] = [c0 | c1 | gmin' | min | gmax' | max | mean]
+ *                  (c0 = g_mean/deg, c1 = g_std/(deg std) where std is not clamped/masked, else 0,
+ *                   gmin' = g_min / #ties, gmax' likewise)
  *   kind 1 (GINE): G_k = node_in[d] [m_k > 0],  node_in = grad_agg[N,H]
  *   d = seg[k].  Then
  *     gT1[nbr[k]] += G_k                  (vector atomics)

@@ -1,0 +1,109 @@
+"""ctypes binding of libb200mp.so (the C ABI declared in include/b200mp.h).
+
+There is no CPU fallback: if the library is missing or a call fails, an exception is raised."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+from typing import Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200mp.so")
+HEADER = os.path.join(os.path.dirname(_HERE), "include", "b200mp.h")
+
+_lib: Optional[C.CDLL] = None
+
+_p, _i, _l, _f, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
+_SIGS = {
+    "b200mp_version": [],
+    "b200mp_partial_rows": [_p],
+    "b200mp_tile_edges": [_i, _p],
+    "b200mp_csc_workspace_bytes": [_l, _l, _p],
+    "b200mp_csc_build": [_p, _p, _l, _l, _p, _p, _p, _p, _p, _p, _sz, _p],
+    "b200mp_degree": [_p, _l, _p, _p, _p],
+    "b200mp_bincount": [_p, _l, _p, _l, _p],
+    "b200mp_relabel_workspace_bytes": [_l, _p],
+    "b200mp_relabel": [_p, _l, _p, _p, _p, _p, _sz, _p],
+    "b200mp_gather_rows": [_p, _p, _p, _l, _i, _p],
+    "b200mp_scatter_rows": [_p, _p, _p, _l, _i, _p],
+    "b200mp_edge_linear_fwd": [_i, _i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p],
+    "b200mp_segment_reduce_fwd": [_i, _i, _l, _p, _p, _p, _p, _l, _l, _l, _p, _p, _l, _p, _p, _p, _p],
+    "b200mp_message_bwd": [_i, _i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p],
+    "b200mp_edge_update_bwd": [_i, _l, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p, _i, _p],
+}
+
+
+def declared_symbols():
+    """Every entry point include/b200mp.h declares (used by the CPU test that checks the
+    library exports all of them)."""
+    with open(HEADER) as f:
+        return sorted(set(re.findall(r"\bint\s+(b200mp_\w+)\s*\(", f.read())))
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(b200mp has no CPU or PyTorch fallback)")
+        l = C.CDLL(LIB_PATH)
+        for name, args in _SIGS.items():
+            fn = getattr(l, name)
+            fn.argtypes = args
+            fn.restype = _i
+        _lib = l
+    return _lib
+
+
+class B200MPError(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        kind = {-1: "invalid argument", -2: "workspace too small"}.get(rc, f"cudaError {rc}" if rc > 0 else "error")
+        raise B200MPError(f"{what} failed: {kind} (rc={rc})")
+
+
+def ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def stream() -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise B200MPError("b200mp kernels run on CUDA tensors only (no CPU fallback): got a "
+                              f"{t.device} tensor")
+
+
+_cache = {}
+
+
+def partial_rows() -> int:
+    if "pr" not in _cache:
+        v = C.c_int(0)
+        check(lib().b200mp_partial_rows(C.byref(v)), "b200mp_partial_rows")
+        _cache["pr"] = v.value
+    return _cache["pr"]
+
+
+def tile_edges(H: int) -> int:
+    if ("te", H) not in _cache:
+        v = C.c_int(0)
+        rc = lib().b200mp_tile_edges(H, C.byref(v))
+        if rc != 0:
+            raise B200MPError(f"hidden width {H} is not supported by the kernels (16/32/64/128)")
+        _cache[("te", H)] = v.value
+    return _cache[("te", H)]
+
+
+def n_part(E: int, H: int) -> int:
+    return max(1, min(partial_rows(), (E + tile_edges(H) - 1) // tile_edges(H)))

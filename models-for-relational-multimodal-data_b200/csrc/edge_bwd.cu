@@ -57,13 +57,13 @@ __global__ void __launch_bounds__(NT) message_bwd_kernel(MsgBwdArgs a) {
                 const float4 mv = ldg4(a.m + k * H + c);
                 const int64_t d = __ldg(a.seg + k);
                 if (KIND == 0) {
-                    const float* q = a.node_in + d * 6 * H + c;
+                    const float* q = a.node_in + d * 7 * H + c;
                     const float4 c0 = ldg4(q), c1 = ldg4(q + H), gmn = ldg4(q + 2 * H), mn = ldg4(q + 3 * H),
-                                 gmx = ldg4(q + 4 * H), mx = ldg4(q + 5 * H);
-                    G.x = fmaf(c1.x, mv.x, c0.x) + (mv.x == mn.x ? gmn.x : 0.f) + (mv.x == mx.x ? gmx.x : 0.f);
-                    G.y = fmaf(c1.y, mv.y, c0.y) + (mv.y == mn.y ? gmn.y : 0.f) + (mv.y == mx.y ? gmx.y : 0.f);
-                    G.z = fmaf(c1.z, mv.z, c0.z) + (mv.z == mn.z ? gmn.z : 0.f) + (mv.z == mx.z ? gmx.z : 0.f);
-                    G.w = fmaf(c1.w, mv.w, c0.w) + (mv.w == mn.w ? gmn.w : 0.f) + (mv.w == mx.w ? gmx.w : 0.f);
+                                 gmx = ldg4(q + 4 * H), mx = ldg4(q + 5 * H), mu = ldg4(q + 6 * H);
+                    G.x = fmaf(c1.x, mv.x - mu.x, c0.x) + (mv.x == mn.x ? gmn.x : 0.f) + (mv.x == mx.x ? gmx.x : 0.f);
+                    G.y = fmaf(c1.y, mv.y - mu.y, c0.y) + (mv.y == mn.y ? gmn.y : 0.f) + (mv.y == mx.y ? gmx.y : 0.f);
+                    G.z = fmaf(c1.z, mv.z - mu.z, c0.z) + (mv.z == mn.z ? gmn.z : 0.f) + (mv.z == mx.z ? gmx.z : 0.f);
+                    G.w = fmaf(c1.w, mv.w - mu.w, c0.w) + (mv.w == mn.w ? gmn.w : 0.f) + (mv.w == mx.w ? gmx.w : 0.f);
                 } else {
                     const float4 ga = ldg4(a.node_in + d * H + c);
                     G = f4(mv.x > 0.f ? ga.x : 0.f, mv.y > 0.f ? ga.y : 0.f, mv.z > 0.f ? ga.z : 0.f, mv.w > 0.f ? ga.w : 0.f);
@@ -248,8 +248,8 @@ extern "C" int b200mp_message_bwd(int kind, int H, int64_t E,
                                   const float* W, float* g_e, int accumulate, float* gT1,
                                   float* gW_part, float* gb_part, int n_part, void* stream) {
     using namespace b200mp;
-    if (E < 0 || n_part <= 0 || !W || !g_e || !gW_part || !gb_part) return B200MP_EINVAL;
-    if (E > 0 && (!m || !e || !node_in || !seg || (gT1 && !nbr))) return B200MP_EINVAL;
+    if (E < 0 || n_part <= 0 || !W || !gW_part || !gb_part) return B200MP_EINVAL;
+    if (E > 0 && (!g_e || !m || !e || !node_in || !seg || (gT1 && !nbr))) return B200MP_EINVAL;
     MsgBwdArgs a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part};
     cudaStream_t st = (cudaStream_t)stream;
 #define B200MP_MB(HH) return kind == 0 ? launch_msg_bwd<HH, 0>(a, n_part, st) : launch_msg_bwd<HH, 1>(a, n_part, st)
@@ -267,8 +267,8 @@ extern "C" int b200mp_edge_update_bwd(int H, int64_t E,
                                       float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part,
                                       int n_part, void* stream) {
     using namespace b200mp;
-    if (E < 0 || n_part <= 0 || !W1 || !W2 || !g_e || !gW1_part || !gb1_part || !gW2_part || !gb2_part) return B200MP_EINVAL;
-    if (E > 0 && (!g_out || !h || !e || !dst || (gP && !src))) return B200MP_EINVAL;
+    if (E < 0 || n_part <= 0 || !W1 || !W2 || !gW1_part || !gb1_part || !gW2_part || !gb2_part) return B200MP_EINVAL;
+    if (E > 0 && (!g_e || !g_out || !h || !e || !dst || (gP && !src))) return B200MP_EINVAL;
     UpdBwdArgs a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part};
     cudaStream_t st = (cudaStream_t)stream;
     switch (H) {

@@ -125,10 +125,11 @@ extern "C" int b200mp_edge_linear_fwd(int mode, int H, int64_t E,
                                       const float* W2, const float* b2, float alpha, float beta,
                                       float* out1, float* out2, void* stream) {
     using namespace b200mp;
-    if (E < 0 || !W1 || !b1 || !out1 || (E > 0 && !e)) return B200MP_EINVAL;
+    if (E < 0 || mode < 0 || mode > 2) return B200MP_EINVAL;
+    if (E == 0) return 0;
+    if (!W1 || !b1 || !out1 || !e) return B200MP_EINVAL;
     if ((T1 && !idx1) || (T2 && !idx2)) return B200MP_EINVAL;
     if (mode == 2 && (!W2 || !b2 || !out2)) return B200MP_EINVAL;
-    if (E == 0) return 0;
     EdgeFwdArgs a{E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2};
     cudaStream_t st = (cudaStream_t)stream;
     switch (H) {

@@ -1,0 +1,268 @@
+"""torch.autograd Functions over the C-ABI kernels (include/b200mp.h).
+
+All edge tensors handled here are in *e-storage order* = CSC order of the graph
+(``EdgeStructure.fwd``); ``permute_rows`` moves between the caller's edge order and it.
+Saved tensors are never modified, so ``retain_graph=True`` + repeated backward (MoCo,
+/root/reference/src/nn/weighting/MoCo.py:45) works.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib as L
+from .graph import CHUNK, LIGHT_MAX, EdgeStructure, SegmentIndex
+
+
+class KernelStats:
+    """Optional per-kernel accounting (bench.py / profiling): number of kernel launches issued
+    through the C ABI and, when ``timing`` is on, a CUDA-event pair around each call recorded on
+    the launching (current) stream."""
+
+    def __init__(self, timing: bool = False):
+        self.timing = timing
+        self.launches = 0
+        self.calls = {}        # name -> number of calls
+        self.events = {}       # name -> [(start, stop)]
+
+    def summary(self):
+        """name -> (calls, total_ms); call after torch.cuda.synchronize()."""
+        return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in self.events.items()}
+
+
+_STATS = None
+
+
+def set_kernel_stats(stats):
+    global _STATS
+    _STATS = stats
+
+
+class _track:
+    def __init__(self, name, n_kernels=1):
+        self.name, self.n = name, n_kernels
+
+    def __enter__(self):
+        st = _STATS
+        self.ev = None
+        if st is not None:
+            st.launches += self.n
+            st.calls[self.name] = st.calls.get(self.name, 0) + 1
+            if st.timing:
+                self.ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                self.ev[0].record()
+
+    def __exit__(self, *exc):
+        if self.ev is not None:
+            self.ev[1].record()
+            _STATS.events.setdefault(self.name, []).append(self.ev)
+        return False
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.float32:
+        raise TypeError(f"b200mp kernels compute in fp32; got {t.dtype}")
+    return t.contiguous()
+
+
+def _H(t: torch.Tensor) -> int:
+    H = t.shape[-1]
+    L.tile_edges(H)      # raises for unsupported widths
+    return H
+
+
+# ----------------------------------------------------------------------------- row permutation
+class _PermuteRows(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, idx, scatter):
+        x = _f32c(x)
+        L.require_cuda(x, idx)
+        ctx.save_for_backward(idx)
+        ctx.scatter = scatter
+        return _permute(x, idx, scatter)
+
+    @staticmethod
+    def backward(ctx, g):
+        (idx,) = ctx.saved_tensors
+        return _permute(_f32c(g), idx, not ctx.scatter), None, None
+
+
+def _permute(x, idx, scatter):
+    n, H = x.shape
+    if H % 4:
+        raise L.B200MPError("row width must be a multiple of 4")
+    out = torch.empty_like(x)
+    fn = L.lib().b200mp_scatter_rows if scatter else L.lib().b200mp_gather_rows
+    with torch.cuda.device(x.device), _track("permute_rows"):
+        L.check(fn(L.ptr(x), L.ptr(idx), L.ptr(out), n, H, L.stream()), "b200mp_permute_rows")
+    return out
+
+
+def gather_rows(x: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """out[i] = x[idx[i]] for a permutation idx (backward = scatter, no atomics)."""
+    return _PermuteRows.apply(x, idx, False)
+
+
+def scatter_rows(x: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """out[idx[i]] = x[i] for a permutation idx."""
+    return _PermuteRows.apply(x, idx, True)
+
+
+# ----------------------------------------------------------------------------- raw launches
+def _edge_linear_fwd(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2=None, b2=None, alpha=0.0, beta=0.0):
+    E, H = e.shape
+    out1 = torch.empty((E, H), dtype=torch.float32, device=e.device)
+    out2 = torch.empty((E, H), dtype=torch.float32, device=e.device) if mode == 2 else None
+    with torch.cuda.device(e.device), _track(("pna_message_fwd", "gine_message_fwd", "edge_update_fwd")[mode]):
+        L.check(L.lib().b200mp_edge_linear_fwd(mode, H, E, L.ptr(e), L.ptr(eid), L.ptr(W1), L.ptr(b1),
+                                               L.ptr(T1), L.ptr(idx1), L.ptr(T2), L.ptr(idx2),
+                                               L.ptr(W2), L.ptr(b2), alpha, beta, L.ptr(out1), L.ptr(out2), L.stream()),
+                "b200mp_edge_linear_fwd")
+    return out1, out2
+
+
+def _segment_reduce(kind, seg: SegmentIndex, m, H):
+    N, dev = seg.num_nodes, m.device
+    agg = torch.empty((N, 4 * H if kind == 0 else H), dtype=torch.float32, device=dev)
+    tie = torch.empty((N, 2 * H), dtype=torch.float32, device=dev) if kind == 0 else None
+    nh, hnode, hcptr, nc, chv, cbeg = seg.heavy()
+    partial = torch.empty((nc, 6 * H), dtype=torch.float32, device=dev) if nh else None
+    with torch.cuda.device(dev), _track("segment_reduce_pna" if kind == 0 else "segment_reduce_sum", 3 if nh else 1):
+        L.check(L.lib().b200mp_segment_reduce_fwd(kind, H, N, L.ptr(seg.ptr), L.ptr(m), L.ptr(agg), L.ptr(tie),
+                                                  LIGHT_MAX, CHUNK, nh, L.ptr(hnode), L.ptr(hcptr), nc, L.ptr(chv),
+                                                  L.ptr(cbeg), L.ptr(partial), L.stream()),
+                "b200mp_segment_reduce_fwd")
+    return agg, tie
+
+
+def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N):
+    E, H = m.shape
+    dev = m.device
+    g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
+    gT1 = torch.zeros((N, H), dtype=torch.float32, device=dev) if need_T1 else None
+    npart = L.n_part(E, H)
+    gW = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
+    gb = torch.empty((npart, H), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _track("pna_message_bwd" if kind == 0 else "gine_message_bwd"):
+        L.check(L.lib().b200mp_message_bwd(kind, H, E, L.ptr(m), L.ptr(e), L.ptr(seg.eid32), L.ptr(node_in),
+                                           L.ptr(seg.seg32), L.ptr(seg.nbr32), L.ptr(W), L.ptr(g_e), 0, L.ptr(gT1),
+                                           L.ptr(gW), L.ptr(gb), npart, L.stream()),
+                "b200mp_message_bwd")
+    return g_e, gT1, gW.sum(0), gb.sum(0)
+
+
+def _edge_update_bwd(st: EdgeStructure, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q):
+    E, H = e.shape
+    dev = e.device
+    g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
+    gP = torch.zeros((st.num_nodes, H), dtype=torch.float32, device=dev) if need_P else None
+    gQ = torch.zeros((st.num_nodes, H), dtype=torch.float32, device=dev) if need_Q else None
+    npart = L.n_part(E, H)
+    gW1 = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
+    gW2 = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
+    gb1 = torch.empty((npart, H), dtype=torch.float32, device=dev)
+    gb2 = torch.empty((npart, H), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _track("edge_update_bwd"):
+        L.check(L.lib().b200mp_edge_update_bwd(H, E, L.ptr(g_out), L.ptr(h), L.ptr(e), L.ptr(st.src32),
+                                               L.ptr(st.dst32), L.ptr(W1), L.ptr(W2), alpha, beta,
+                                               L.ptr(g_e), L.ptr(gP), L.ptr(gQ), L.ptr(gW1), L.ptr(gb1),
+                                               L.ptr(gW2), L.ptr(gb2), npart, L.stream()),
+                "b200mp_edge_update_bwd")
+    return g_e, gP, gQ, gW1.sum(0), gb1.sum(0), gW2.sum(0), gb2.sum(0)
+
+
+# ----------------------------------------------------------------------------- PNA aggregation
+class _PNAAggregate(torch.autograd.Function):
+    """agg4[N,4H] = [mean|min|max|std] over incoming m_k = A[seg_k] + B[nbr_k] + e_k W^T + b."""
+
+    @staticmethod
+    def forward(ctx, A, B, e, W, b, seg: SegmentIndex):
+        A, B, e, W, b = map(_f32c, (A, B, e, W, b))
+        L.require_cuda(A, B, e, W, b)
+        H = _H(e)
+        m, _ = _edge_linear_fwd(0, e, seg.eid32, W, b, B, seg.nbr32, A, seg.seg32)
+        agg, tie = _segment_reduce(0, seg, m, H)
+        ctx.seg = seg
+        ctx.save_for_backward(m, e, W, agg, tie)
+        ctx.mark_non_differentiable(tie)
+        return agg, tie
+
+    @staticmethod
+    def backward(ctx, g_agg, _g_tie):
+        m, e, W, agg, tie = ctx.saved_tensors
+        seg: SegmentIndex = ctx.seg
+        N, H = seg.num_nodes, m.shape[1]
+        g_agg = _f32c(g_agg)
+        deg = (seg.ptr[1:] - seg.ptr[:-1]).to(torch.float32).unsqueeze(1)
+        dn = deg.clamp(min=1.0)
+        g_mean, g_min, g_max, g_std = g_agg[:, :H], g_agg[:, H:2 * H], g_agg[:, 2 * H:3 * H], g_agg[:, 3 * H:]
+        mean, mn, mx, std = agg[:, :H], agg[:, H:2 * H], agg[:, 2 * H:3 * H], agg[:, 3 * H:]
+        valid = std > 0
+        c1 = torch.where(valid, g_std / (dn * torch.where(valid, std, torch.ones_like(std))), torch.zeros_like(std))
+        c0 = g_mean / dn
+        gmn = g_min / tie[:, :H].clamp(min=1.0)
+        gmx = g_max / tie[:, H:].clamp(min=1.0)
+        coef = torch.cat([c0, c1, gmn, mn, gmx, mx, mean], dim=1).contiguous()
+        need_B = ctx.needs_input_grad[1]
+        g_e, gB, gW, gb = _message_bwd(0, seg, m, e, coef, W, need_B, N)
+        gA = None
+        if ctx.needs_input_grad[0]:
+            gA = (g_mean + g_min + g_max) * (deg > 0).to(torch.float32)
+        return gA, gB, g_e, gW, gb, None
+
+
+def pna_aggregate(A, B, e, W, b, seg: SegmentIndex):
+    """Returns (agg4 [N,4H] in the order mean,min,max,std, tie counts [N,2H])."""
+    return _PNAAggregate.apply(A, B, e, W, b, seg)
+
+
+# ----------------------------------------------------------------------------- GINE aggregation
+class _GINEAggregate(torch.autograd.Function):
+    """agg[N,H] = sum over incoming relu(x[nbr_k] + e_k W^T + b)."""
+
+    @staticmethod
+    def forward(ctx, x, e, W, b, seg: SegmentIndex):
+        x, e, W, b = map(_f32c, (x, e, W, b))
+        L.require_cuda(x, e, W, b)
+        H = _H(e)
+        m, _ = _edge_linear_fwd(1, e, seg.eid32, W, b, x, seg.nbr32, None, None)
+        agg, _ = _segment_reduce(1, seg, m, H)
+        ctx.seg = seg
+        ctx.save_for_backward(m, e, W)
+        return agg
+
+    @staticmethod
+    def backward(ctx, g_agg):
+        m, e, W = ctx.saved_tensors
+        seg: SegmentIndex = ctx.seg
+        g_e, gx, gW, gb = _message_bwd(1, seg, m, e, _f32c(g_agg), W, ctx.needs_input_grad[0], seg.num_nodes)
+        return gx, g_e, gW, gb, None
+
+
+def gine_aggregate(x, e, W, b, seg: SegmentIndex):
+    return _GINEAggregate.apply(x, e, W, b, seg)
+
+
+# ----------------------------------------------------------------------------- edge update
+class _EdgeUpdate(torch.autograd.Function):
+    """e' = alpha e + beta (relu(P[src] + Q[dst] + e W1^T + b1) W2^T + b2), e-storage order."""
+
+    @staticmethod
+    def forward(ctx, P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha, beta):
+        P, Q, e, W1, b1, W2, b2 = map(_f32c, (P, Q, e, W1, b1, W2, b2))
+        L.require_cuda(P, Q, e, W1, b1, W2, b2)
+        _H(e)
+        h, out = _edge_linear_fwd(2, e, None, W1, b1, P, st.src32, Q, st.dst32, W2, b2, float(alpha), float(beta))
+        ctx.st, ctx.alpha, ctx.beta = st, float(alpha), float(beta)
+        ctx.save_for_backward(h, e, W1, W2)
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        h, e, W1, W2 = ctx.saved_tensors
+        g_e, gP, gQ, gW1, gb1, gW2, gb2 = _edge_update_bwd(ctx.st, _f32c(g_out), h, e, W1, W2, ctx.alpha, ctx.beta,
+                                                           ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+        return gP, gQ, g_e, gW1, gb1, gW2, gb2, None, None, None
+
+
+def edge_update(P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha: float, beta: float):
+    return _EdgeUpdate.apply(P, Q, e, W1, b1, W2, b2, st, alpha, beta)

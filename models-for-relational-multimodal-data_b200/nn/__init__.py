@@ -1,0 +1,2 @@
+from .conv import BatchNorm, GINEConv, Linear, PNAConv, edge_update_sorted    # noqa: F401
+from .backbones import GINe, GINEConvHetero, PNAConvHetero, PNAS              # noqa: F401

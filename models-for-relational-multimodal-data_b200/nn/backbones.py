@@ -1,0 +1,163 @@
+"""Drop-in backbones: ``GINe`` (/root/reference/src/nn/gnn/gine.py:37-100), ``PNAS``
+(src/nn/gnn/pna.py:48-101) and their reverse-message-passing convs ``GINEConvHetero``
+(gine.py:15-35) / ``PNAConvHetero`` (pna.py:17-46).  Same constructors, ``forward(x, edge_index,
+edge_attr) -> (x, edge_attr)`` and state_dict keys.
+
+The edge tensor is permuted once into CSC storage order, stays there for all layers and is
+permuted back at the end; all per-edge work runs in the b200mp CUDA kernels.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .. import functional as BF
+from ..graph import EdgeStructure, edge_structure
+from .conv import BatchNorm, GINEConv, Linear, PNAConv, edge_update_sorted
+
+
+class _HeteroMixin:
+    def reset_parameters(self):
+        self.conv_forw.reset_parameters()
+        self.conv_back.reset_parameters()
+        self.lin.reset_parameters()
+
+
+class GINEConvHetero(_HeteroMixin, nn.Module):
+    def __init__(self, network, n_hidden):
+        super().__init__()
+        self.conv_forw = GINEConv(network, edge_dim=n_hidden)
+        self.conv_back = GINEConv(network, edge_dim=n_hidden)      # same `network` object, as in the reference
+        self.lin = Linear(n_hidden * 3, n_hidden)
+
+    def forward_sorted(self, x, st: EdgeStructure, e):
+        a_in = self.conv_forw.forward_sorted((x, None), st.fwd, e)
+        a_out = self.conv_back.forward_sorted((x, None), st.rev, e)
+        return self.lin(torch.cat([x, a_in, a_out], dim=1))
+
+    def forward(self, x, edge_index, edge_attr):
+        st = edge_structure(edge_index, x.shape[0], reverse=True)
+        return self.forward_sorted(x, st, BF.gather_rows(edge_attr, st.fwd.perm))
+
+
+class PNAConvHetero(_HeteroMixin, nn.Module):
+    def __init__(self, n_hidden, in_channels, out_channels, aggregators, scalers, deg, edge_dim, towers=1,
+                 pre_layers=1, post_layers=1, divide_input=False):
+        super().__init__()
+        kw = dict(in_channels=in_channels, out_channels=out_channels, aggregators=aggregators, scalers=scalers,
+                  deg=deg, edge_dim=edge_dim, towers=towers, pre_layers=pre_layers, post_layers=post_layers,
+                  divide_input=divide_input)
+        self.conv_forw = PNAConv(**kw)
+        self.conv_back = PNAConv(**kw)
+        self.lin = Linear(n_hidden * 3, n_hidden)
+
+    def forward_sorted(self, x, st: EdgeStructure, e):
+        a_in = self.conv_forw.forward_sorted(x, st.fwd, e)
+        a_out = self.conv_back.forward_sorted(x, st.rev, e)
+        return self.lin(torch.cat([x, a_in, a_out], dim=1))
+
+    def forward(self, x, edge_index, edge_attr):
+        st = edge_structure(edge_index, x.shape[0], reverse=True)
+        return self.forward_sorted(x, st, BF.gather_rows(edge_attr, st.fwd.perm))
+
+
+def _conv_sorted(conv, x, st: EdgeStructure, e):
+    if isinstance(conv, (GINEConvHetero, PNAConvHetero)):
+        return conv.forward_sorted(x, st, e)
+    return conv.forward_sorted(x, st.fwd, e)
+
+
+class _Backbone(nn.Module):
+    """Shared layer loop of gine.py:86-89 / pna.py:95-99."""
+
+    def _layers(self, x, edge_index, e):
+        st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
+        e = BF.gather_rows(e, st.fwd.perm)                      # caller order -> CSC storage order
+        for i in range(self.num_gnn_layers):
+            x = (x + F.relu(self.batch_norms[i](_conv_sorted(self.convs[i], x, st, e)))) / 2
+            if self.edge_updates:
+                e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5)
+        return x, BF.scatter_rows(e, st.fwd.perm)               # back to caller order
+
+    def message_passing(self, x, edge_index, e):
+        """The L-layer loop on already embedded x[N,H], e[E,H] (the region BASELINE.json's metric
+        times: SURVEY.md section 8d)."""
+        return self._layers(x, edge_index, e)
+
+
+class GINe(_Backbone):
+    def __init__(self, num_features=1, num_gnn_layers=2, n_hidden=100, edge_updates=False, edge_dim=None,
+                 reverse_mp=False):
+        super().__init__()
+        self.n_hidden = n_hidden
+        self.num_gnn_layers = num_gnn_layers
+        self.edge_updates = edge_updates
+        self.reverse_mp = reverse_mp
+
+        self.node_emb = nn.Linear(num_features, n_hidden)
+        self.edge_emb = nn.Linear(edge_dim, n_hidden)
+
+        self.convs = nn.ModuleList()
+        self.emlps = nn.ModuleList()
+        self.batch_norms = nn.ModuleList()
+        for _ in range(self.num_gnn_layers):
+            net = nn.Sequential(nn.Linear(n_hidden, n_hidden), nn.ReLU(), nn.Linear(n_hidden, n_hidden))
+            conv = GINEConvHetero(net, n_hidden=n_hidden) if reverse_mp else GINEConv(net, edge_dim=n_hidden)
+            if self.edge_updates:
+                self.emlps.append(nn.Sequential(nn.Linear(3 * n_hidden, n_hidden), nn.ReLU(),
+                                                nn.Linear(n_hidden, n_hidden)))
+            self.convs.append(conv)
+            self.batch_norms.append(BatchNorm(n_hidden))
+
+    def forward(self, x, edge_index, edge_attr):
+        x = self.node_emb(x)
+        e = self.edge_emb(edge_attr.view(edge_attr.shape[0], -1))
+        return self._layers(x, edge_index, e)
+
+    def reset_parameters(self):
+        for conv in self.convs:
+            conv.reset_parameters()
+        for emlp in self.emlps:
+            for m in emlp:
+                if hasattr(m, "reset_parameters"):
+                    m.reset_parameters()
+        for bn in self.batch_norms:
+            bn.reset_parameters()
+        self.node_emb.reset_parameters()
+        self.edge_emb.reset_parameters()
+
+
+class PNAS(_Backbone):
+    def __init__(self, num_features, num_gnn_layers, n_classes=2, n_hidden=128, edge_updates=True, edge_dim=None,
+                 dropout=0.0, final_dropout=0.5, deg=None, reverse_mp=False):
+        super().__init__()
+        self.n_hidden = n_hidden
+        self.num_gnn_layers = num_gnn_layers
+        self.edge_updates = edge_updates
+        self.final_dropout = final_dropout
+        self.reverse_mp = reverse_mp
+
+        aggregators = ['mean', 'min', 'max', 'std']
+        scalers = ['identity', 'amplification', 'attenuation']
+
+        self.node_emb = nn.Linear(num_features, n_hidden)
+        self.edge_emb = nn.Linear(edge_dim, n_hidden)
+
+        self.convs = nn.ModuleList()
+        self.emlps = nn.ModuleList()
+        self.batch_norms = nn.ModuleList()
+        for _ in range(self.num_gnn_layers):
+            kw = dict(in_channels=n_hidden, out_channels=n_hidden, aggregators=aggregators, scalers=scalers, deg=deg,
+                      edge_dim=n_hidden, towers=1, pre_layers=1, post_layers=1, divide_input=False)
+            conv = PNAConvHetero(n_hidden=n_hidden, **kw) if reverse_mp else PNAConv(**kw)
+            if self.edge_updates:
+                self.emlps.append(nn.Sequential(nn.Linear(3 * n_hidden, n_hidden), nn.ReLU(),
+                                                nn.Linear(n_hidden, n_hidden)))
+            self.convs.append(conv)
+            self.batch_norms.append(BatchNorm(n_hidden))
+
+    def forward(self, x, edge_index, edge_attr):
+        x = self.node_emb(x.view(x.shape[0], -1))
+        e = self.edge_emb(edge_attr.view(edge_attr.shape[0], -1))
+        return self._layers(x, edge_index, e)

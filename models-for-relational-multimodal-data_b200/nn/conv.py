@@ -1,0 +1,191 @@
+"""Operator-level drop-ins for the torch_geometric classes the reference constructs:
+``GINEConv``, ``PNAConv``, ``BatchNorm``, ``Linear`` (same constructor arguments, forward
+signatures and state_dict keys), plus the edge-update step.
+
+Reference call sites: /root/reference/src/nn/gnn/gine.py:18-19,66-77, src/nn/gnn/pna.py:23-30,
+71-86, src/nn/models/{tabgnn.py:163-172, fused.py:204-214, inteleaved.py:189-199}.
+
+Every conv offers ``forward(x, edge_index, edge_attr)`` (caller edge order, like PyG) and
+``forward_sorted(x, seg, e)`` used by the backbones, which keep ``e`` in CSC storage order for
+all layers so edge tensors stream sequentially.
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional, Sequence, Union
+
+import torch
+import torch.nn.functional as F
+from torch import Tensor, nn
+
+from .. import functional as BF
+from ..graph import EdgeStructure, SegmentIndex, edge_structure
+
+Linear = nn.Linear     # torch_geometric.nn.Linear with known in_channels: same keys (weight, bias)
+
+_AGG_ORDER = ("mean", "min", "max", "std")     # column order the kernel writes
+
+
+class BatchNorm(nn.Module):
+    """torch_geometric.nn.BatchNorm: BatchNorm1d under ``.module`` (keys ``module.*``)."""
+
+    def __init__(self, in_channels: int, eps: float = 1e-5, momentum: float = 0.1, affine: bool = True,
+                 track_running_stats: bool = True):
+        super().__init__()
+        self.module = nn.BatchNorm1d(in_channels, eps, momentum, affine, track_running_stats)
+
+    def reset_parameters(self):
+        self.module.reset_parameters()
+
+    def forward(self, x: Tensor) -> Tensor:
+        return self.module(x)
+
+
+def _resolve(x, edge_index, reverse=False) -> EdgeStructure:
+    xs = x[0] if isinstance(x, (tuple, list)) else x
+    return edge_structure(edge_index, xs.shape[0], reverse=reverse)
+
+
+class GINEConv(nn.Module):
+    """out_i = nn((1+eps) x_i + sum_{j->i} relu(x_j + lin(e_ji)))  (PyG GINEConv)."""
+
+    def __init__(self, nn: nn.Module, eps: float = 0.0, train_eps: bool = False, edge_dim: Optional[int] = None):
+        super().__init__()
+        self.nn = nn
+        self.initial_eps = eps
+        if train_eps:
+            self.eps = torch.nn.Parameter(torch.empty(1))
+        else:
+            self.register_buffer("eps", torch.empty(1))
+        first = nn[0] if isinstance(nn, torch.nn.Sequential) else nn
+        in_channels = first.in_features
+        if edge_dim is None:
+            raise ValueError("b200mp GINEConv needs edge_dim (the reference always passes it: gine.py:18-19,66-70)")
+        self.lin = Linear(edge_dim, in_channels)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        for m in self.nn.modules():
+            if hasattr(m, "reset_parameters") and m is not self.nn:
+                m.reset_parameters()
+        self.eps.data.fill_(self.initial_eps)
+        self.lin.reset_parameters()
+
+    def forward_sorted(self, x: Union[Tensor, tuple], seg: SegmentIndex, e: Tensor) -> Tensor:
+        self_term = True
+        if isinstance(x, (tuple, list)):
+            x, x_dst = x
+            self_term = x_dst is not None
+        if self.lin.weight.shape[0] != self.lin.weight.shape[1] or x.shape[1] != self.lin.weight.shape[0]:
+            raise ValueError("b200mp GINEConv kernels need edge_dim == in_channels")
+        out = BF.gine_aggregate(x, e, self.lin.weight, self.lin.bias, seg)
+        if self_term:
+            out = out + (1 + self.eps) * x
+        return self.nn(out)
+
+    def forward(self, x, edge_index: Tensor, edge_attr: Tensor) -> Tensor:
+        st = _resolve(x, edge_index)
+        return self.forward_sorted(x, st.fwd, BF.gather_rows(edge_attr, st.fwd.perm))
+
+
+class _DegreeScalerBuffers(nn.Module):
+    """Holds ``avg_deg_lin`` / ``avg_deg_log`` under the PyG key prefix ``aggr_module.``."""
+
+    def __init__(self, deg: Tensor):
+        super().__init__()
+        deg = deg.to(torch.float)
+        total = float(deg.sum())
+        bins = torch.arange(deg.numel(), device=deg.device)
+        self.register_buffer("avg_deg_lin", torch.tensor(float((bins * deg).sum()) / total))
+        self.register_buffer("avg_deg_log", torch.tensor(float(((bins + 1).log() * deg).sum()) / total))
+
+
+class PNAConv(nn.Module):
+    """PyG PNAConv for the only configuration the reference builds: towers=1, pre_layers=1,
+    post_layers=1, divide_input=False, edge_dim == in_channels."""
+
+    def __init__(self, in_channels: int, out_channels: int, aggregators: List[str], scalers: List[str], deg: Tensor,
+                 edge_dim: Optional[int] = None, towers: int = 1, pre_layers: int = 1, post_layers: int = 1,
+                 divide_input: bool = False, **kwargs):
+        super().__init__()
+        if towers != 1 or pre_layers != 1 or post_layers != 1 or divide_input:
+            raise ValueError("b200mp PNAConv supports towers=1, pre_layers=1, post_layers=1, divide_input=False "
+                             "(every constructor site of the reference)")
+        if edge_dim is None or edge_dim != in_channels:
+            raise ValueError("b200mp PNAConv needs edge_dim == in_channels (as at pna.py:71-74)")
+        if deg is None:
+            raise ValueError("PNAConv needs the in-degree histogram `deg`")
+        for a in aggregators:
+            if a not in _AGG_ORDER:
+                raise ValueError(f"unsupported aggregator '{a}' (kernels provide {_AGG_ORDER})")
+        for s in scalers:
+            if s not in ("identity", "amplification", "attenuation", "linear", "inverse_linear"):
+                raise ValueError(f"Unknown scaler '{s}'")
+        self.in_channels, self.out_channels = in_channels, out_channels
+        self.aggregators, self.scalers = list(aggregators), list(scalers)
+        self.edge_dim, self.towers, self.divide_input = edge_dim, towers, divide_input
+        self.F_in, self.F_out = in_channels, out_channels
+        self.aggr_module = _DegreeScalerBuffers(deg)
+        self.edge_encoder = Linear(edge_dim, self.F_in)
+        self.pre_nns = nn.ModuleList([nn.Sequential(Linear(3 * self.F_in, self.F_in))])
+        n_in = (len(aggregators) * len(scalers) + 1) * self.F_in
+        self.post_nns = nn.ModuleList([nn.Sequential(Linear(n_in, self.F_out))])
+        self.lin = Linear(out_channels, out_channels)
+
+    def reset_parameters(self):
+        self.edge_encoder.reset_parameters()
+        self.pre_nns[0][0].reset_parameters()
+        self.post_nns[0][0].reset_parameters()
+        self.lin.reset_parameters()
+
+    def forward_sorted(self, x: Tensor, seg: SegmentIndex, e: Tensor) -> Tensor:
+        Fi = self.F_in
+        pre = self.pre_nns[0][0]
+        Wi, Wj, Wc = pre.weight[:, :Fi], pre.weight[:, Fi:2 * Fi], pre.weight[:, 2 * Fi:]
+        # pre_nn is one Linear without activation: hoist the node halves to N rows and fold the
+        # edge encoder into a single H x H matrix (SURVEY.md section 7 "hoisting")
+        A = x @ Wi.t()
+        B = x @ Wj.t()
+        Wp = Wc @ self.edge_encoder.weight
+        bp = Wc @ self.edge_encoder.bias + pre.bias
+        agg4, _ = BF.pna_aggregate(A, B, e, Wp, bp, seg)
+
+        deg = (seg.ptr[1:] - seg.ptr[:-1]).to(x.dtype).unsqueeze(1)
+        post = self.post_nns[0][0]
+        na = len(self.aggregators)
+        cols = [_AGG_ORDER.index(a) for a in self.aggregators]
+        out = x @ post.weight[:, :Fi].t() + post.bias
+        lin_avg, log_avg = self.aggr_module.avg_deg_lin, self.aggr_module.avg_deg_log
+        agg_used = agg4 if cols == [0, 1, 2, 3] else torch.cat([agg4[:, c * Fi:(c + 1) * Fi] for c in cols], dim=1)
+        Ws = post.weight[:, Fi:]                          # [F_out, ns * na * Fi], scaler-major
+        ns = len(self.scalers)
+        # one GEMM for all scalers: Z[:, s*F_out:(s+1)*F_out] = agg_used @ Ws_s^T
+        Z = agg_used @ Ws.reshape(self.F_out, ns, na * Fi).permute(2, 1, 0).reshape(na * Fi, ns * self.F_out)
+        for si, s in enumerate(self.scalers):
+            z = Z[:, si * self.F_out:(si + 1) * self.F_out]
+            if s == "identity":
+                out = out + z
+            elif s == "amplification":
+                out = out + z * (torch.log(deg + 1) / log_avg)
+            elif s == "attenuation":
+                out = out + z * (log_avg / torch.log(deg.clamp(min=1) + 1))
+            elif s == "linear":
+                out = out + z * (deg / lin_avg)
+            else:
+                out = out + z * (lin_avg / deg.clamp(min=1))
+        return self.lin(out)
+
+    def forward(self, x: Tensor, edge_index: Tensor, edge_attr: Tensor) -> Tensor:
+        st = _resolve(x, edge_index)
+        return self.forward_sorted(x, st.fwd, BF.gather_rows(edge_attr, st.fwd.perm))
+
+
+def edge_update_sorted(emlp: nn.Sequential, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float) -> Tensor:
+    """e' = alpha e + beta emlp([x[src], x[dst], e]) with emlp = Sequential(Linear(3H,H), ReLU,
+    Linear(H,H)) (gine.py:71-75,88-89; pna.py:80-84,97-99; models/fused.py:215-219,254)."""
+    l1, l2 = emlp[0], emlp[2]
+    H = x.shape[1]
+    Ws, Wd, We = l1.weight[:, :H], l1.weight[:, H:2 * H], l1.weight[:, 2 * H:]
+    P = x @ Ws.t()
+    Q = x @ Wd.t()
+    return BF.edge_update(P, Q, e, We, l1.bias, l2.weight, l2.bias, st, alpha, beta)

@@ -1,0 +1,127 @@
+"""TEST INFRASTRUCTURE ONLY: a plain-PyTorch emulation of the C-ABI kernels (include/b200mp.h),
+patched in by CPU tests so that the host-side logic of the drop-in modules (weight hoisting,
+coefficient algebra of the PNA backward, permutations, state_dict layout) can be checked against
+the golden fixtures without a GPU.  The product never imports this file; GPU tests run the real
+kernels and additionally compare them with this emulation op by op."""
+from __future__ import annotations
+
+import contextlib
+import math
+
+import torch
+
+import b200mp
+from b200mp import _lib as L
+from b200mp import functional as BF
+from b200mp import graph as G
+
+STD_THR = torch.tensor(math.sqrt(1e-5), dtype=torch.float32)
+
+
+def build_segment_index(key, other_end, num_nodes):
+    perm = torch.argsort(key, stable=True)
+    ptr = torch.zeros(num_nodes + 1, dtype=torch.int64, device=key.device)
+    ptr[1:] = torch.cumsum(torch.bincount(key, minlength=num_nodes), 0)
+    other = other_end[perm]
+    return G.SegmentIndex(int(num_nodes), int(key.numel()), perm, ptr, other, other.to(torch.int32),
+                          key[perm].to(torch.int32))
+
+
+def permute(x, idx, scatter):
+    out = torch.empty_like(x)
+    if scatter:
+        out[idx] = x
+    else:
+        out = x[idx]
+    return out
+
+
+def edge_linear_fwd(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2=None, b2=None, alpha=0.0, beta=0.0):
+    rows = eid.long() if eid is not None else torch.arange(e.shape[0], device=e.device)
+    x = e[rows]
+    z = x @ W1.t() + b1
+    if T1 is not None:
+        z = z + T1[idx1.long()]
+    if T2 is not None:
+        z = z + T2[idx2.long()]
+    if mode >= 1:
+        z = z.relu()
+    out2 = None
+    if mode == 2:
+        out2 = torch.empty_like(e)
+        out2[rows] = alpha * x + beta * (z @ W2.t() + b2)
+    return z, out2
+
+
+def segment_reduce(kind, seg, m, H):
+    N = seg.num_nodes
+    idx = seg.seg32.long()
+    s = torch.zeros((N, H), dtype=m.dtype).index_add_(0, idx, m)
+    if kind == 1:
+        return s, None
+    deg = (seg.ptr[1:] - seg.ptr[:-1]).to(m.dtype).unsqueeze(1)
+    dn = deg.clamp(min=1)
+    q = torch.zeros((N, H), dtype=m.dtype).index_add_(0, idx, m * m)
+    ix = idx.unsqueeze(1).expand_as(m)
+    mn = torch.zeros((N, H), dtype=m.dtype).scatter_reduce_(0, ix, m, "amin", include_self=False)
+    mx = torch.zeros((N, H), dtype=m.dtype).scatter_reduce_(0, ix, m, "amax", include_self=False)
+    cn = torch.zeros((N, H), dtype=m.dtype).index_add_(0, idx, (m == mn[idx]).to(m.dtype))
+    cx = torch.zeros((N, H), dtype=m.dtype).index_add_(0, idx, (m == mx[idx]).to(m.dtype))
+    mean = s / dn
+    var = q / dn - mean * mean
+    std = var.clamp(min=1e-5).sqrt()
+    std = torch.where(std <= STD_THR.to(m.dtype), torch.zeros_like(std), std)
+    has = deg > 0
+    agg = torch.cat([mean, mn, mx, std], 1) * has
+    return agg, torch.cat([cn, cx], 1) * has
+
+
+def message_bwd(kind, seg, m, e, node_in, W, need_T1, N):
+    H = m.shape[1]
+    d = seg.seg32.long()
+    rows = seg.eid32.long() if seg.eid32 is not None else torch.arange(m.shape[0])
+    if kind == 0:
+        c = node_in[d]
+        c0, c1, gmn, mn, gmx, mx, mu = [c[:, i * H:(i + 1) * H] for i in range(7)]
+        Gm = c0 + c1 * (m - mu) + torch.where(m == mn, gmn, torch.zeros_like(m)) + torch.where(m == mx, gmx, torch.zeros_like(m))
+    else:
+        Gm = torch.where(m > 0, node_in[d], torch.zeros_like(m))
+    gT1 = torch.zeros((N, H), dtype=m.dtype).index_add_(0, seg.nbr32.long(), Gm) if need_T1 else None
+    g_e = torch.empty_like(e)
+    g_e[rows] = Gm @ W
+    return g_e, gT1, Gm.t() @ e[rows], Gm.sum(0)
+
+
+def edge_update_bwd(st, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q):
+    N, H = st.num_nodes, e.shape[1]
+    Gout = beta * g_out
+    Gh = (Gout @ W2) * (h > 0).to(e.dtype)
+    gP = torch.zeros((N, H), dtype=e.dtype).index_add_(0, st.src32.long(), Gh) if need_P else None
+    gQ = torch.zeros((N, H), dtype=e.dtype).index_add_(0, st.dst32.long(), Gh) if need_Q else None
+    g_e = alpha * g_out + Gh @ W1
+    return g_e, gP, gQ, Gh.t() @ e, Gh.sum(0), Gout.t() @ h, Gout.sum(0)
+
+
+_PATCHES = [
+    (G, "build_segment_index", build_segment_index),
+    (L, "require_cuda", lambda *a: None),
+    (BF, "_permute", permute),
+    (BF, "_edge_linear_fwd", edge_linear_fwd),
+    (BF, "_segment_reduce", segment_reduce),
+    (BF, "_message_bwd", message_bwd),
+    (BF, "_edge_update_bwd", edge_update_bwd),
+]
+
+
+@contextlib.contextmanager
+def emulated_kernels():
+    saved = [(mod, name, getattr(mod, name)) for mod, name, _ in _PATCHES]
+    for mod, name, fn in _PATCHES:
+        setattr(mod, name, fn)
+    G.clear_cache()
+    try:
+        yield
+    finally:
+        for mod, name, fn in saved:
+            setattr(mod, name, fn)
+        G.clear_cache()
