@@ -273,6 +273,8 @@ def run_b200(args, rank, world, local_rank):
     # end-to-end: pinned host buffers -> device -> CSC build -> fwd+bwd -> loss to host, every step
     e2e = None
     try:
+        if args.no_e2e:
+            raise RuntimeError("skipped by --no-e2e (profiling run)")
         del st
         BG.clear_cache()
         hx, hea, hei = x.detach().cpu().pin_memory(), ea.detach().cpu().pin_memory(), ei.cpu().pin_memory()
@@ -336,6 +338,7 @@ def main():
     ap.add_argument("--model", default="pna", choices=["pna", "gine"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer arm")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
