@@ -129,6 +129,20 @@ int b200mp_edge_update_bwd(int H, int64_t E,
                            float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part,
                            int n_part, void* stream);
 
+/* ------------------------------------------------------------------ tensor-core self test
+ * One-CTA check of the tcgen05 building blocks (csrc/umma.cuh) used by the per-edge kernels:
+ *   mode 0: Y[128,64] = X[128,64] W[64,64]^T     mode 1: Y = X W      (3xTF32)
+ *   mode 2: Y[64,64]  = X[128,64]^T W[128,64]    (weight-gradient form, 3xTF32)
+ *   mode 3: mode 0 with the low-order A operand read from tensor memory
+ *   mode 4: mode 0 in a single TF32 pass (no split)
+ * Test infrastructure only (tests/test_gpu_umma.py); no reference counterpart. */
+int b200mp_umma_selftest(int mode, const float* X, const float* W, float* Y, void* stream);
+/* Raw tensor-core probe (scripts/umma_probe.py): host-built shared-memory images (<= 32 KB each)
+ * and descriptor fields, one TF32 pass of `ksteps` MMAs; D = the 128 x 64 accumulator lanes. */
+int b200mp_umma_probe(const float* a_img, int a_bytes, const float* b_img, int b_bytes,
+                      uint64_t adesc, uint64_t bdesc, int a_kstep, int b_kstep, int ksteps,
+                      uint32_t idesc, float* D, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
