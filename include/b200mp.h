@@ -35,6 +35,8 @@ int b200mp_version(void);
 /* Number of CTAs the persistent edge kernels are launched with (= rows of the per-CTA
  * weight-gradient partial buffers the caller must allocate). */
 int b200mp_partial_rows(int* rows);
+/* The same for hidden width H (the tensor-core kernels for H = 64 run one CTA per SM). */
+int b200mp_partial_rows_for(int H, int* rows);
 /* Edges per tile of the per-edge kernels for hidden width H (callers size n_part with it). */
 int b200mp_tile_edges(int H, int* te);
 

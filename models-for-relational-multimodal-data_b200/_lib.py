@@ -20,6 +20,7 @@ _p, _i, _l, _f, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
 _SIGS = {
     "b200mp_version": [],
     "b200mp_partial_rows": [_p],
+    "b200mp_partial_rows_for": [_i, _p],
     "b200mp_tile_edges": [_i, _p],
     "b200mp_csc_workspace_bytes": [_l, _l, _p],
     "b200mp_csc_build": [_p, _p, _l, _l, _p, _p, _p, _p, _p, _p, _sz, _p],
@@ -89,12 +90,12 @@ def require_cuda(*tensors):
 _cache = {}
 
 
-def partial_rows() -> int:
-    if "pr" not in _cache:
+def partial_rows(H: int = 0) -> int:
+    if ("pr", H) not in _cache:
         v = C.c_int(0)
-        check(lib().b200mp_partial_rows(C.byref(v)), "b200mp_partial_rows")
-        _cache["pr"] = v.value
-    return _cache["pr"]
+        check(lib().b200mp_partial_rows_for(H, C.byref(v)), "b200mp_partial_rows_for")
+        _cache[("pr", H)] = v.value
+    return _cache[("pr", H)]
 
 
 def tile_edges(H: int) -> int:
@@ -108,4 +109,4 @@ def tile_edges(H: int) -> int:
 
 
 def n_part(E: int, H: int) -> int:
-    return max(1, min(partial_rows(), (E + tile_edges(H) - 1) // tile_edges(H)))
+    return max(1, min(partial_rows(H), (E + tile_edges(H) - 1) // tile_edges(H)))

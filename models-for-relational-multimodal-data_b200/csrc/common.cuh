@@ -138,7 +138,9 @@ __device__ __forceinline__ void store_wgrad(float* part /* [H,H] of this CTA */,
 // ------------------------------------------------------------------ host side helpers
 struct DeviceInfo { int sms; int max_smem_optin; };
 const DeviceInfo& device_info();
-int persistent_grid(const void* kernel, size_t smem, int64_t work_items);
+int persistent_grid(const void* kernel, size_t smem, int64_t work_items, int threads = NT);
+// H = 64 runs on the tcgen05 kernels (*_umma.cu) unless B200MP_SIMT=1 (A/B comparison only)
+bool use_tensor_cores();
 
 #define B200MP_LAUNCH_CHECK() do { cudaError_t _e = cudaGetLastError(); if (_e != cudaSuccess) return (int)_e; } while (0)
 #define B200MP_CUDA(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return (int)_e; } while (0)

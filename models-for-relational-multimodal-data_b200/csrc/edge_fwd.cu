@@ -115,6 +115,10 @@ static int dispatch_mode(int mode, const EdgeFwdArgs& a, cudaStream_t st) {
     return B200MP_EINVAL;
 }
 
+int launch_edge_fwd_umma(int mode, int64_t E, const float* e, const int32_t* eid, const float* W1, const float* b1,
+                         const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
+                         const float* W2, const float* b2, float alpha, float beta, float* out1, float* out2, cudaStream_t st);
+
 }  // namespace b200mp
 
 extern "C" int b200mp_edge_linear_fwd(int mode, int H, int64_t E,
@@ -132,6 +136,8 @@ extern "C" int b200mp_edge_linear_fwd(int mode, int H, int64_t E,
     if (mode == 2 && (!W2 || !b2 || !out2)) return B200MP_EINVAL;
     EdgeFwdArgs a{E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2};
     cudaStream_t st = (cudaStream_t)stream;
+    if (H == 64 && use_tensor_cores())
+        return launch_edge_fwd_umma(mode, E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2, st);
     switch (H) {
         case 16: return dispatch_mode<16>(mode, a, st);
         case 32: return dispatch_mode<32>(mode, a, st);

@@ -10,6 +10,7 @@
 #include "common.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <cstdlib>
 
 namespace b200mp {
 
@@ -26,9 +27,14 @@ const DeviceInfo& device_info() {
     return info;
 }
 
-int persistent_grid(const void* kernel, size_t smem, int64_t work_items) {
+bool use_tensor_cores() {
+    static const bool on = [] { const char* v = getenv("B200MP_SIMT"); return !(v && v[0] == '1'); }();
+    return on;
+}
+
+int persistent_grid(const void* kernel, size_t smem, int64_t work_items, int threads) {
     int per_sm = 1;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, NT, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
     int64_t g = (int64_t)device_info().sms * per_sm;
     if (work_items < g) g = work_items;
     return (int)(g < 1 ? 1 : g);
@@ -154,12 +160,18 @@ extern "C" int b200mp_partial_rows(int* rows) {
     return 0;
 }
 
+extern "C" int b200mp_partial_rows_for(int H, int* rows) {
+    if (!rows) return B200MP_EINVAL;
+    *rows = (H == 64 && use_tensor_cores()) ? device_info().sms : device_info().sms * 2;   // tensor-core kernels: one CTA per SM
+    return 0;
+}
+
 extern "C" int b200mp_tile_edges(int H, int* te) {
     if (!te) return B200MP_EINVAL;
     switch (H) {
         case 16: *te = Tile<16>::TE; return 0;
         case 32: *te = Tile<32>::TE; return 0;
-        case 64: *te = Tile<64>::TE; return 0;
+        case 64: *te = use_tensor_cores() ? 128 : Tile<64>::TE; return 0;
         case 128: *te = Tile<128>::TE; return 0;
     }
     return B200MP_EINVAL;
