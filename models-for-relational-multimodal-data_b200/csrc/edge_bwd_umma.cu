@@ -26,7 +26,7 @@ struct UpdBwdUArgs {
 
 __global__ void __launch_bounds__(NTH, 1) edge_update_bwd_umma_kernel(UpdBwdUArgs a) {
     extern __shared__ __align__(128) float smem_raw[];
-    float* smem = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;   // keeps the shared address space
     float* G_hi = smem;                       // g tile, later the e tile
     float* G_lo = G_hi + RT::FLOATS;
     float* H_hi = G_lo + RT::FLOATS;          // h tile, later the Gh tile
@@ -57,11 +57,13 @@ __global__ void __launch_bounds__(NTH, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
     const int64_t ntiles = (a.E + TE - 1) / TE;
     uint32_t it = 0;
     RowRegs R, R2;
-    int nrows_pf = 0;
+    int nrows_pf = 0, drow_pf = 0, srow_pf = 0;
     if ((int64_t)blockIdx.x < ntiles) {
         nrows_pf = (int)min64(TE, a.E - (int64_t)blockIdx.x * TE);
         load_rows(R, a.g_out, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
         load_rows(R2, a.h, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
+        drow_pf = __ldg(a.dst + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
+        srow_pf = __ldg(a.src + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
     }
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
@@ -83,8 +85,8 @@ __global__ void __launch_bounds__(NTH, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
             mma_commit(&sync.bar[0]);
         }
         load_rows(R, a.e, nullptr, row0, nrows, tid);                 // e tile in flight during the MMAs
-        const int drow = valid ? __ldg(a.dst + row0 + t) : -1;
-        const int srow = valid ? __ldg(a.src + row0 + t) : 0;
+        const int drow = valid ? drow_pf : -1;
+        const int srow = srow_pf;
         mbar_wait(&sync.bar[0], par);
         fence_after();
 
@@ -145,6 +147,8 @@ __global__ void __launch_bounds__(NTH, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
             nrows_pf = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
             load_rows(R, a.g_out, nullptr, (tile + gridDim.x) * TE, nrows_pf, tid);
             load_rows(R2, a.h, nullptr, (tile + gridDim.x) * TE, nrows_pf, tid);
+            drow_pf = __ldg(a.dst + (tile + gridDim.x) * TE + min(t, nrows_pf - 1));
+            srow_pf = __ldg(a.src + (tile + gridDim.x) * TE + min(t, nrows_pf - 1));
         }
         mbar_wait(&sync.bar[1], par);
         fence_after();
@@ -209,7 +213,7 @@ struct MsgBwdUArgs {
 template <int KIND>
 __global__ void __launch_bounds__(NTH, 1) message_bwd_umma_kernel(MsgBwdUArgs a) {
     extern __shared__ __align__(128) float smem_raw[];
-    float* smem = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;   // keeps the shared address space
     float* G_hi = smem;                       // first the raw m tile, then G (hi)
     float* G_lo = G_hi + RT::FLOATS;
     float* E_hi = G_lo + RT::FLOATS;
@@ -236,11 +240,13 @@ __global__ void __launch_bounds__(NTH, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
     const int64_t ntiles = (a.E + TE - 1) / TE;
     uint32_t it = 0;
     RowRegs R, R2;
-    int nrows_pf = 0;
+    int nrows_pf = 0, seg_pf = 0, nbr_pf = 0;
     if ((int64_t)blockIdx.x < ntiles) {
         nrows_pf = (int)min64(TE, a.E - (int64_t)blockIdx.x * TE);
         load_rows(R, a.m, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
         load_rows(R2, a.e, a.eid, (int64_t)blockIdx.x * TE, nrows_pf, tid);
+        seg_pf = __ldg(a.seg + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
+        if (a.gT1) nbr_pf = __ldg(a.nbr + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
     }
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
@@ -250,8 +256,8 @@ __global__ void __launch_bounds__(NTH, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
 
         store_rows_raw(R, G_hi, nrows, tid);                           // m tile (prefetched)
         store_rows_split(R2, E_hi, E_lo, nrows, tid);
-        const int64_t d = __ldg(a.seg + row0 + min(t, nrows - 1));
-        const int64_t nrow = a.gT1 ? __ldg(a.nbr + row0 + min(t, nrows - 1)) : 0;
+        const int64_t d = seg_pf;
+        const int64_t nrow = nbr_pf;
         __syncthreads();
 
         // ---- per-edge gradient G (thread = 32 columns of an edge row), in place over the m tile
@@ -306,6 +312,8 @@ __global__ void __launch_bounds__(NTH, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
             nrows_pf = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
             load_rows(R, a.m, nullptr, (tile + gridDim.x) * TE, nrows_pf, tid);
             load_rows(R2, a.e, a.eid, (tile + gridDim.x) * TE, nrows_pf, tid);
+            seg_pf = __ldg(a.seg + (tile + gridDim.x) * TE + min(t, nrows_pf - 1));
+            if (a.gT1) nbr_pf = __ldg(a.nbr + (tile + gridDim.x) * TE + min(t, nrows_pf - 1));
         }
         mbar_wait(&sync.bar[0], it & 1);
         fence_after();

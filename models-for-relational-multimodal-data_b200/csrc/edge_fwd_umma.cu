@@ -25,7 +25,7 @@ struct EdgeFwdUArgs {
 template <int MODE>
 __global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_kernel(EdgeFwdUArgs a) {
     extern __shared__ __align__(128) float smem_raw[];
-    float* smem = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;   // keeps the shared address space
     float* E_hi = smem;                       // e tile; mode 2: later h
     float* E_lo = E_hi + RT::FLOATS;          // modes 0/1: later the gathered node rows
     float* ST = E_lo + RT::FLOATS;            // mode 2 only: gathered node rows, later alpha e
@@ -34,6 +34,7 @@ __global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_k
     float* W2_hi = W1_lo + WT::FLOATS;        // mode 2 only
     float* W2_lo = W2_hi + WT::FLOATS;
     __shared__ TileSync sync;
+    __shared__ int sidx[2][TE];               // gather indices of the tile (clamped rows)
 
     const int tid = threadIdx.x, warp = tid >> 5;
     const int t = tid & (TE - 1), ch = tid >> 7;           // epilogue: row t, columns 32 ch ..
@@ -54,10 +55,12 @@ __global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_k
     const int64_t ntiles = (a.E + TE - 1) / TE;
     uint32_t it = 0;
     RowRegs R;
-    int nrows_pf = 0;
+    int nrows_pf = 0, idx_pf = 0;             // thread tid: index (tid / 128) of row tid % 128, one tile ahead
+    const int32_t* idx_src = ch == 0 ? a.idx1 : a.idx2;
     if ((int64_t)blockIdx.x < ntiles) {
         nrows_pf = (int)min64(TE, a.E - (int64_t)blockIdx.x * TE);
         load_rows(R, a.e, a.eid, (int64_t)blockIdx.x * TE, nrows_pf, tid);
+        if (idx_src) idx_pf = __ldg(idx_src + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
     }
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
@@ -66,6 +69,7 @@ __global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_k
         const uint32_t par = it & 1;
 
         store_rows_split(R, E_hi, E_lo, nrows, tid);
+        sidx[ch][t] = idx_pf;
         fence_async_smem();
         fence_before();
         __syncthreads();
@@ -74,7 +78,7 @@ __global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_k
             gemm3_data(tm, E_hi, E_lo, W1_hi, W1_lo, 0);
             mma_commit(&sync.bar[0]);
         }
-        gather_rows(R, a.T1, a.idx1, a.T2, a.idx2, row0, nrows, tid);   // coalesced, in flight while the MMAs run
+        gather_rows(R, a.T1, sidx[0], a.T2, sidx[1], tid);   // coalesced, in flight while the MMAs run
         if (MODE != 2) {                     // E_lo is still an MMA operand: wait before reusing it
             mbar_wait(&sync.bar[0], par);
             fence_after();
@@ -83,6 +87,7 @@ __global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_k
         if (tile + gridDim.x < ntiles) {     // next tile's e rows in flight
             nrows_pf = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
             load_rows(R, a.e, a.eid, (tile + gridDim.x) * TE, nrows_pf, tid);
+            if (idx_src) idx_pf = __ldg(idx_src + (tile + gridDim.x) * TE + min(t, nrows_pf - 1));
         }
         if (MODE == 2) {
             mbar_wait(&sync.bar[0], par);

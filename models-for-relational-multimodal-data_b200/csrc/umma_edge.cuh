@@ -67,23 +67,17 @@ __device__ __forceinline__ void load_rows(RowRegs& R, const float* __restrict__ 
 #pragma unroll
     for (int i = 0; i < 8; ++i) R.v[i] = ldg4(src + rows[i] * HH + j * 4);
 }
-// R = T1[idx1[row]] + T2[idx2[row]] (either table nullable), same thread mapping as load_rows
-__device__ __forceinline__ void gather_rows(RowRegs& R, const float* __restrict__ T1, const int32_t* __restrict__ idx1,
-                                            const float* __restrict__ T2, const int32_t* __restrict__ idx2,
-                                            int64_t row0, int nrows, int tid) {
+// R = T1[i1[row]] + T2[i2[row]] (either table nullable), same thread mapping as load_rows.  The
+// row indices come from SHARED memory (staged one tile ahead): with the index loads in global
+// memory ptxas serialises index -> address -> row per row and every row pays a DRAM latency.
+__device__ __forceinline__ void gather_rows(RowRegs& R, const float* __restrict__ T1, const int* i1,
+                                            const float* __restrict__ T2, const int* i2, int tid) {
     const int j = tid & 15, r0 = tid >> 4;
-    int i1[8], i2[8];
     float4 t[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        const int rc = min(i * 16 + r0, nrows - 1);
-        i1[i] = T1 ? __ldg(idx1 + row0 + rc) : 0;
-        i2[i] = T2 ? __ldg(idx2 + row0 + rc) : 0;
-    }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        R.v[i] = T1 ? ldg4(T1 + (int64_t)i1[i] * HH + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-        t[i] = T2 ? ldg4(T2 + (int64_t)i2[i] * HH + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        R.v[i] = T1 ? ldg4(T1 + (int64_t)i1[i * 16 + r0] * HH + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        t[i] = T2 ? ldg4(T2 + (int64_t)i2[i * 16 + r0] * HH + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) R.v[i] = R.v[i] + t[i];
