@@ -259,8 +259,8 @@ def run_b200(args, rank, world, local_rank):
         per = total_ms / calls
         kern[name] = {"calls_per_step": calls / args.steps, "ms_per_call": round(per, 4),
                       "share_of_step": round(total_ms / ms, 4),
-                      "achieved_gbs": round(KERNEL_BYTES[name] * e / (per * 1e-3) / 1e9, 1)}
-    top = max(summ.items(), key=lambda kv: kv[1][1])[0]
+                      "achieved_gbs": round(KERNEL_BYTES[name] * e / (per * 1e-3) / 1e9, 1) if name in KERNEL_BYTES else None}
+    top = max(((k, v) for k, v in summ.items() if k in KERNEL_BYTES), key=lambda kv: kv[1][1])[0]
     achieved = kern[top]["achieved_gbs"]
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,

@@ -70,6 +70,12 @@ int b200mp_relabel(const int64_t* ids, int64_t M, int64_t* nodes, int64_t* n_uni
 int b200mp_gather_rows(const float* in, const int64_t* idx, float* out, int64_t n, int H, void* stream);
 int b200mp_scatter_rows(const float* in, const int64_t* idx, float* out, int64_t n, int H, void* stream);
 
+/* x = hi + lo, hi = x rounded to tf32, lo = x - hi (exact); n a multiple of 4.  Operand split of
+ * the node-level 3xTF32 linears (functional.linear3x): three tensor-core library GEMMs
+ * lo*hi + hi*lo + hi*hi reproduce the fp32 product to ~1e-7 (PyG Linear / torch addmm call sites:
+ * pna.py:71-79, gine.py:66-70 through PNAConv.update / GINEConv.nn). */
+int b200mp_split_tf32(const float* x, float* hi, float* lo, int64_t n, void* stream);
+
 /* ------------------------------------------------------------------ per-edge linear (forward)
  * One pass over E edges in segment order k = 0..E-1; H in {16,32,64,128}.
  *   z_k   = e[row(k)] W1^T + b1 + T1[idx1[k]] + T2[idx2[k]]        (T1/T2 nullable)
@@ -101,6 +107,22 @@ int b200mp_segment_reduce_fwd(int kind, int H, int64_t N, const int64_t* ptr, co
                               int64_t n_heavy, const int32_t* heavy_node, const int32_t* heavy_chunk_ptr,
                               int64_t n_chunks, const int32_t* chunk_heavy, const int64_t* chunk_begin,
                               float* partial /* [n_chunks, 6H] */, void* stream);
+
+/* ------------------------------------------------------------------ node-level PNA glue
+ * Degree scalers of PyG DegreeScalerAggregation (constructed at pna.py:71-74)
+ * commuted past post_nn's Linear:  out[N,F] = base + sum_s f_s(deg) Z[:, s*F:(s+1)*F],
+ * deg = ptr[v+1]-ptr[v]; host_codes[s]: 0 identity, 1 amplification log(d+1)/avg_log,
+ * 2 attenuation avg_log/log(max(d,1)+1), 3 linear d/avg_lin, 4 inverse_linear avg_lin/max(d,1).
+ * avg_lin / avg_log are DEVICE scalars (the module's buffers).  _bwd: gZ[:, s] = f_s(deg) g. */
+int b200mp_pna_scale_fwd(int F, int64_t N, const int64_t* ptr, const float* base, const float* Z, int ns,
+                         const int* host_codes, const float* avg_lin, const float* avg_log, float* out, void* stream);
+int b200mp_pna_scale_bwd(int F, int64_t N, const int64_t* ptr, const float* g, int ns, const int* host_codes,
+                         const float* avg_lin, const float* avg_log, float* gZ, void* stream);
+/* Coefficient rows of b200mp_message_bwd kind 0 from the aggregate gradient g_agg[N,4H]
+ * (mean|min|max|std), agg[N,4H] and tie[N,2H]:  coef[N,7H], gA[N,H] = (g_mean+g_min+g_max)[deg>0]
+ * (gA nullable). */
+int b200mp_pna_coef(int H, int64_t N, const int64_t* ptr, const float* g_agg, const float* agg, const float* tie,
+                    float* coef, float* gA, void* stream);
 
 /* ------------------------------------------------------------------ per-edge backward
  * Message backward (autograd of the mode 0 / mode 1 forward + its reduction):

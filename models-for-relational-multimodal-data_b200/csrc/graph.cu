@@ -142,6 +142,20 @@ __global__ void permute_rows_kernel(const float* __restrict__ in, const int64_t*
     }
 }
 
+// x = hi + lo with hi = x rounded to tf32 (low 13 mantissa bits zero), lo = x - hi exactly
+__global__ void split_tf32_kernel(const float4* __restrict__ x, float4* __restrict__ hi, float4* __restrict__ lo, int64_t n4) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = __ldg(x + i);
+        float4 h;
+        h.x = __uint_as_float((__float_as_uint(v.x) + 0x1000u) & 0xffffe000u);
+        h.y = __uint_as_float((__float_as_uint(v.y) + 0x1000u) & 0xffffe000u);
+        h.z = __uint_as_float((__float_as_uint(v.z) + 0x1000u) & 0xffffe000u);
+        h.w = __uint_as_float((__float_as_uint(v.w) + 0x1000u) & 0xffffe000u);
+        hi[i] = h;
+        lo[i] = make_float4(v.x - h.x, v.y - h.y, v.z - h.z, v.w - h.w);
+    }
+}
+
 static inline int grid_for(int64_t n, int block = 256) {
     int64_t g = (n + block - 1) / block;
     int64_t cap = (int64_t)device_info().sms * 16;
@@ -287,6 +301,14 @@ extern "C" int b200mp_scatter_rows(const float* in, const int64_t* idx, float* o
     if (n < 0 || H <= 0 || (H & 3) || (n > 0 && (!in || !idx || !out))) return B200MP_EINVAL;
     if (n == 0) return 0;
     permute_rows_kernel<true><<<grid_for(n * (H / 4)), 256, 0, (cudaStream_t)stream>>>(in, idx, out, n, H / 4);
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int b200mp_split_tf32(const float* x, float* hi, float* lo, int64_t n, void* stream) {
+    if (n < 0 || (n & 3) || (n > 0 && (!x || !hi || !lo))) return B200MP_EINVAL;
+    if (n == 0) return 0;
+    split_tf32_kernel<<<grid_for(n / 4), 256, 0, (cudaStream_t)stream>>>((const float4*)x, (float4*)hi, (float4*)lo, n / 4);
     B200MP_LAUNCH_CHECK();
     return 0;
 }

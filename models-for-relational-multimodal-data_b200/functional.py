@@ -107,6 +107,75 @@ def scatter_rows(x: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     return _PermuteRows.apply(x, idx, True)
 
 
+# ----------------------------------------------------------------------------- node-level linears
+def _split_tf32(x):
+    x = x.contiguous()
+    hi, lo = torch.empty_like(x), torch.empty_like(x)
+    with torch.cuda.device(x.device), _track("split_tf32"):
+        L.check(L.lib().b200mp_split_tf32(L.ptr(x), L.ptr(hi), L.ptr(lo), x.numel(), L.stream()), "b200mp_split_tf32")
+    return hi, lo
+
+
+def _use_mm3(x, W):
+    """3xTF32 pays off only where the fp32 GEMM is FLOP-bound: many rows and a wide contraction
+    (the [N,4H] x [4H,3H] post GEMM of PNAConv); H x H node linears are HBM-bound in plain fp32."""
+    return x.shape[0] >= 4096 and W.shape[1] >= 256 and W.shape[0] % 4 == 0 and W.shape[1] % 4 == 0
+
+
+def _mm3(a, b, ta=False, tb=False):
+    """op(a) @ op(b) in fp32 accuracy on the tensor cores: 3xTF32 (lo*hi + hi*lo + hi*hi) as three
+    TF32 library GEMMs accumulating in fp32.  a, b are (hi, lo) pairs from _split_tf32."""
+    (a_hi, a_lo), (b_hi, b_lo) = a, b
+    if ta:
+        a_hi, a_lo = a_hi.t(), a_lo.t()
+    if tb:
+        b_hi, b_lo = b_hi.t(), b_lo.t()
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        out = torch.mm(a_lo, b_hi)
+        out.addmm_(a_hi, b_lo)
+        out.addmm_(a_hi, b_hi)
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    return out
+
+
+class _Linear3x(torch.autograd.Function):
+    """y = x W^T (+ b) for N-row node tensors; forward and both backward GEMMs as 3xTF32."""
+
+    @staticmethod
+    def forward(ctx, x, W, b):
+        x, W = _f32c(x), _f32c(W)
+        L.require_cuda(x, W)
+        ctx.save_for_backward(x, W)
+        ctx.has_bias = b is not None
+        if not _use_mm3(x, W):
+            return torch.nn.functional.linear(x, W, b)
+        y = _mm3(_split_tf32(x), _split_tf32(W), tb=True)
+        if b is not None:
+            y += b
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        x, W = ctx.saved_tensors
+        g = _f32c(g)
+        gb = g.sum(0) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        if not _use_mm3(x, W):
+            return (g @ W if ctx.needs_input_grad[0] else None), (g.t() @ x if ctx.needs_input_grad[1] else None), gb
+        gs = _split_tf32(g)
+        gx = _mm3(gs, _split_tf32(W)) if ctx.needs_input_grad[0] else None
+        gW = _mm3(gs, _split_tf32(x), ta=True) if ctx.needs_input_grad[1] else None
+        return gx, gW, gb
+
+
+def linear3x(x, W, b=None):
+    """torch.nn.functional.linear(x, W, b) for node-level [N, K] inputs, fp32-accurate on the
+    tensor cores (three TF32 library GEMMs)."""
+    return _Linear3x.apply(x, W, b)
+
+
 # ----------------------------------------------------------------------------- raw launches
 def _edge_linear_fwd(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2=None, b2=None, alpha=0.0, beta=0.0):
     E, H = e.shape
@@ -170,6 +239,64 @@ def _edge_update_bwd(st: EdgeStructure, g_out, h, e, W1, W2, alpha, beta, need_P
     return g_e, gP, gQ, gW1.sum(0), gb1.sum(0), gW2.sum(0), gb2.sum(0)
 
 
+_SCALER_CODE = {"identity": 0, "amplification": 1, "attenuation": 2, "linear": 3, "inverse_linear": 4}
+
+
+def _pna_scale_fwd(ptr, base, Z, codes, avg_lin, avg_log):
+    N, F = base.shape
+    out = torch.empty_like(base)
+    arr = (L.C.c_int * len(codes))(*codes)
+    with torch.cuda.device(base.device), _track("pna_scale_fwd"):
+        L.check(L.lib().b200mp_pna_scale_fwd(F, N, L.ptr(ptr), L.ptr(base), L.ptr(Z), len(codes), arr, L.ptr(avg_lin),
+                                             L.ptr(avg_log), L.ptr(out), L.stream()), "b200mp_pna_scale_fwd")
+    return out
+
+
+def _pna_scale_bwd(ptr, g, codes, avg_lin, avg_log):
+    N, F = g.shape
+    gZ = torch.empty((N, len(codes) * F), dtype=torch.float32, device=g.device)
+    arr = (L.C.c_int * len(codes))(*codes)
+    with torch.cuda.device(g.device), _track("pna_scale_bwd"):
+        L.check(L.lib().b200mp_pna_scale_bwd(F, N, L.ptr(ptr), L.ptr(g), len(codes), arr, L.ptr(avg_lin), L.ptr(avg_log),
+                                             L.ptr(gZ), L.stream()), "b200mp_pna_scale_bwd")
+    return gZ
+
+
+def _pna_coef(ptr, g_agg, agg, tie, need_gA):
+    N, H = agg.shape[0], agg.shape[1] // 4
+    coef = torch.empty((N, 7 * H), dtype=torch.float32, device=agg.device)
+    gA = torch.empty((N, H), dtype=torch.float32, device=agg.device) if need_gA else None
+    with torch.cuda.device(agg.device), _track("pna_coef"):
+        L.check(L.lib().b200mp_pna_coef(H, N, L.ptr(ptr), L.ptr(g_agg), L.ptr(agg), L.ptr(tie), L.ptr(coef), L.ptr(gA),
+                                        L.stream()), "b200mp_pna_coef")
+    return coef, gA
+
+
+class _PNAScale(torch.autograd.Function):
+    """out = base + sum_s f_s(deg) Z_s  (degree scalers commuted past post_nn's Linear)."""
+
+    @staticmethod
+    def forward(ctx, base, Z, ptr, codes, avg_lin, avg_log):
+        base, Z = _f32c(base), _f32c(Z)
+        L.require_cuda(base, Z, ptr)
+        avg_lin = avg_lin.detach().to(torch.float32).reshape(1).contiguous()
+        avg_log = avg_log.detach().to(torch.float32).reshape(1).contiguous()
+        ctx.codes = tuple(codes)
+        ctx.save_for_backward(ptr, avg_lin, avg_log)
+        return _pna_scale_fwd(ptr, base, Z, ctx.codes, avg_lin, avg_log)
+
+    @staticmethod
+    def backward(ctx, g):
+        ptr, avg_lin, avg_log = ctx.saved_tensors
+        g = _f32c(g)
+        gZ = _pna_scale_bwd(ptr, g, ctx.codes, avg_lin, avg_log) if ctx.needs_input_grad[1] else None
+        return (g if ctx.needs_input_grad[0] else None), gZ, None, None, None, None
+
+
+def pna_scale(base, Z, ptr, scalers, avg_lin, avg_log):
+    return _PNAScale.apply(base, Z, ptr, [_SCALER_CODE[s] for s in scalers], avg_lin, avg_log)
+
+
 # ----------------------------------------------------------------------------- PNA aggregation
 class _PNAAggregate(torch.autograd.Function):
     """agg4[N,4H] = [mean|min|max|std] over incoming m_k = A[seg_k] + B[nbr_k] + e_k W^T + b."""
@@ -192,21 +319,9 @@ class _PNAAggregate(torch.autograd.Function):
         seg: SegmentIndex = ctx.seg
         N, H = seg.num_nodes, m.shape[1]
         g_agg = _f32c(g_agg)
-        deg = (seg.ptr[1:] - seg.ptr[:-1]).to(torch.float32).unsqueeze(1)
-        dn = deg.clamp(min=1.0)
-        g_mean, g_min, g_max, g_std = g_agg[:, :H], g_agg[:, H:2 * H], g_agg[:, 2 * H:3 * H], g_agg[:, 3 * H:]
-        mean, mn, mx, std = agg[:, :H], agg[:, H:2 * H], agg[:, 2 * H:3 * H], agg[:, 3 * H:]
-        valid = std > 0
-        c1 = torch.where(valid, g_std / (dn * torch.where(valid, std, torch.ones_like(std))), torch.zeros_like(std))
-        c0 = g_mean / dn
-        gmn = g_min / tie[:, :H].clamp(min=1.0)
-        gmx = g_max / tie[:, H:].clamp(min=1.0)
-        coef = torch.cat([c0, c1, gmn, mn, gmx, mx, mean], dim=1).contiguous()
+        coef, gA = _pna_coef(seg.ptr, g_agg, agg, tie, ctx.needs_input_grad[0])
         need_B = ctx.needs_input_grad[1]
         g_e, gB, gW, gb = _message_bwd(0, seg, m, e, coef, W, need_B, N)
-        gA = None
-        if ctx.needs_input_grad[0]:
-            gA = (g_mean + g_min + g_max) * (deg > 0).to(torch.float32)
         return gA, gB, g_e, gW, gb, None
 
 

@@ -102,7 +102,55 @@ def edge_update_bwd(st, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q):
     return g_e, gP, gQ, Gh.t() @ e, Gh.sum(0), Gout.t() @ h, Gout.sum(0)
 
 
+def split_tf32(x):
+    hi = ((x.contiguous().view(torch.int32) + 0x1000) & ~0x1FFF).view(torch.float32)
+    return hi, x - hi
+
+
+def _scaler(code, d, avg_lin, avg_log):
+    if code == 1:
+        return torch.log(d + 1) / avg_log
+    if code == 2:
+        return avg_log / torch.log(d.clamp(min=1) + 1)
+    if code == 3:
+        return d / avg_lin
+    if code == 4:
+        return avg_lin / d.clamp(min=1)
+    return torch.ones_like(d)
+
+
+def pna_scale_fwd(ptr, base, Z, codes, avg_lin, avg_log):
+    d = (ptr[1:] - ptr[:-1]).to(base.dtype).unsqueeze(1)
+    F = base.shape[1]
+    out = base.clone()
+    for s, c in enumerate(codes):
+        out = out + _scaler(c, d, avg_lin, avg_log) * Z[:, s * F:(s + 1) * F]
+    return out
+
+
+def pna_scale_bwd(ptr, g, codes, avg_lin, avg_log):
+    d = (ptr[1:] - ptr[:-1]).to(g.dtype).unsqueeze(1)
+    return torch.cat([_scaler(c, d, avg_lin, avg_log) * g for c in codes], 1)
+
+
+def pna_coef(ptr, g_agg, agg, tie, need_gA):
+    H = agg.shape[1] // 4
+    deg = (ptr[1:] - ptr[:-1]).to(agg.dtype).unsqueeze(1)
+    dn = deg.clamp(min=1.0)
+    g_mean, g_min, g_max, g_std = [g_agg[:, i * H:(i + 1) * H] for i in range(4)]
+    mean, mn, mx, std = [agg[:, i * H:(i + 1) * H] for i in range(4)]
+    valid = std > 0
+    c1 = torch.where(valid, g_std / (dn * torch.where(valid, std, torch.ones_like(std))), torch.zeros_like(std))
+    coef = torch.cat([g_mean / dn, c1, g_min / tie[:, :H].clamp(min=1.0), mn, g_max / tie[:, H:].clamp(min=1.0), mx, mean], 1)
+    gA = (g_mean + g_min + g_max) * (deg > 0).to(agg.dtype) if need_gA else None
+    return coef.contiguous(), gA
+
+
 _PATCHES = [
+    (BF, "_pna_scale_fwd", pna_scale_fwd),
+    (BF, "_pna_scale_bwd", pna_scale_bwd),
+    (BF, "_pna_coef", pna_coef),
+    (BF, "_split_tf32", split_tf32),
     (G, "build_segment_index", build_segment_index),
     (L, "require_cuda", lambda *a: None),
     (BF, "_permute", permute),
