@@ -190,9 +190,10 @@ def run_reference(args, rank, world):
 def workload_config(args, world):
     n, e, _ = WORKLOADS[args.workload]
     return {"workload": f"{args.model.upper()} backbone ({LAYERS} layers, H={H}, edge updates) fwd+bwd on synthetic "
-                        f"{args.workload} shape: {n} accounts, {e} transactions per GPU",
+                        f"{args.workload} shape: {n} accounts, {e} transactions"
+                        + ("" if world == 1 else f", ONE graph partitioned by destination range over {world} GPUs"),
             "nodes": n, "edges": e, "layers": LAYERS, "hidden": H, "model": "PNAS" if args.model == "pna" else "GINe",
-            "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (one graph per GPU; dst-range partition + halo all-gather not built yet)",
+            "parallelism": "single GPU" if world == 1 else f"dst-range partition x{world}: per layer NCCL all-gather of source-side node tables, all-reduce of BatchNorm sums; backward reduce-scatter + weight-gradient all-reduce",
             "l2": "inputs exceed L2 (every [E,H] tensor >> 126 MB)"}
 
 
@@ -203,22 +204,38 @@ def run_b200(args, rank, world, local_rank):
     from b200mp import functional as BF
     from b200mp import graph as BG
 
+    from b200mp import parallel as PL
+
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     n, e, seed = WORKLOADS[args.workload]
-    ei = synth_graph(n, e, seed + rank, dev)
-    st = b200mp.edge_structure(ei, n)
-    _, deg_hist = b200mp.degree_histogram(st.fwd.ptr)
+    ei = synth_graph(n, e, seed, dev)            # every rank generates the same graph, keeps its shard
+    part = None
+    if world > 1:
+        part = PL.partition_graph(ei, n, rank, world)
+        deg = torch.bincount(ei[1], minlength=n)
+        deg_hist = torch.bincount(deg)
+        st = None
+        n_loc, e_loc = part.n_local, part.st.num_edges
+    else:
+        st = b200mp.edge_structure(ei, n)
+        _, deg_hist = b200mp.degree_histogram(st.fwd.ptr)
+        n_loc, e_loc = n, e
     model = make_model(args.model, deg_hist.cpu(), dev)
-    g = torch.Generator(device=dev).manual_seed(seed)
-    x = torch.randn(n, H, generator=g, device=dev).requires_grad_(True)
-    ea = torch.randn(e, H, generator=g, device=dev).requires_grad_(True)
-    gx = torch.randn(n, H, generator=g, device=dev)
-    ge = torch.randn(e, H, generator=g, device=dev)
+    g = torch.Generator(device=dev).manual_seed(seed + rank)
+    x = torch.randn(n_loc, H, generator=g, device=dev).requires_grad_(True)
+    ea = torch.randn(e_loc, H, generator=g, device=dev).requires_grad_(True)
+    gx = torch.randn(n_loc, H, generator=g, device=dev)
+    ge = torch.randn(e_loc, H, generator=g, device=dev)
 
     def step():
-        ox, oe = model.message_passing(x, ei, ea)
+        if part is None:
+            ox, oe = model.message_passing(x, ei, ea)
+        else:
+            ox, oe = model.message_passing_partitioned(x, ea, part)
         torch.autograd.backward([ox, oe], [gx, ge])
+        if part is not None:
+            PL.all_reduce_gradients(model, part)
         x.grad = None
         ea.grad = None
         model.zero_grad(set_to_none=True)
@@ -249,7 +266,7 @@ def run_b200(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     ms_step = ms / args.steps
-    value = world * e / (ms_step * 1e-3)
+    value = e / (ms_step * 1e-3)                 # N > 1: ONE graph partitioned over the ranks (strong scaling)
 
     # per-kernel accounting -> roofline of the dominant kernel
     summ = stats.summary()
@@ -259,13 +276,13 @@ def run_b200(args, rank, world, local_rank):
         per = total_ms / calls
         kern[name] = {"calls_per_step": calls / args.steps, "ms_per_call": round(per, 4),
                       "share_of_step": round(total_ms / ms, 4),
-                      "achieved_gbs": round(KERNEL_BYTES[name] * e / (per * 1e-3) / 1e9, 1) if name in KERNEL_BYTES else None}
+                      "achieved_gbs": round(KERNEL_BYTES[name] * e_loc / (per * 1e-3) / 1e9, 1) if name in KERNEL_BYTES else None}
     top = max(((k, v) for k, v in summ.items() if k in KERNEL_BYTES), key=lambda kv: kv[1][1])[0]
     achieved = kern[top]["achieved_gbs"]
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": KERNEL_BYTES[top] * e}
-    step_bytes = LAYERS * (e * algorithmic_bytes_per_edge(args.model) + n * 12 * 4 * H)
+                "algorithmic_bytes_per_launch": KERNEL_BYTES[top] * e_loc}
+    step_bytes = LAYERS * (e_loc * algorithmic_bytes_per_edge(args.model) + n_loc * 12 * 4 * H)
     step_roofline = {"algorithmic_bytes_per_step": step_bytes, "achieved_gbs": round(step_bytes / (ms_step * 1e-3) / 1e9, 1),
                      "frac": round(step_bytes / (ms_step * 1e-3) / 1e9 / peak, 4),
                      "formula": "L*(E*(22*s*H+64) + N*12*s*H), SURVEY.md 8(d)"}
@@ -278,7 +295,7 @@ def run_b200(args, rank, world, local_rank):
         del st
         BG.clear_cache()
         hx, hea, hei = x.detach().cpu().pin_memory(), ea.detach().cpu().pin_memory(), ei.cpu().pin_memory()
-        del ea, ge
+        del ea, ge, part
         torch.cuda.empty_cache()
         h2d = hx.numel() * 4 + hea.numel() * 4 + hei.numel() * 8
         e2e_steps = max(1, min(args.steps, 3))
@@ -288,9 +305,15 @@ def run_b200(args, rank, world, local_rank):
             dx = hx.to(dev, non_blocking=True).requires_grad_(True)
             dea = hea.to(dev, non_blocking=True).requires_grad_(True)
             dei = hei.to(dev, non_blocking=True)
-            ox, oe = model.message_passing(dx, dei, dea)
+            if world == 1:
+                ox, oe = model.message_passing(dx, dei, dea)
+            else:
+                p2 = PL.partition_graph(dei, n, rank, world)
+                ox, oe = model.message_passing_partitioned(dx, dea, p2)
             loss = ox.square().mean() + oe.square().mean()
             loss.backward()
+            if world > 1:
+                PL.all_reduce_gradients(model, p2)
             model.zero_grad(set_to_none=True)
             return float(loss.item())          # D2H read of the step's result
 
@@ -307,7 +330,7 @@ def run_b200(args, rank, world, local_rank):
             t = torch.tensor([ems], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ems = float(t.item())
-        e2e = {"value": world * e / (ems / e2e_steps * 1e-3), "unit": "edges/s", "h2d_bytes_per_step": h2d,
+        e2e = {"value": e / (ems / e2e_steps * 1e-3), "unit": "edges/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 4, "steps": e2e_steps, "ms_per_step": ems / e2e_steps,
                "includes": "H2D of x, edge_index, edge features from pinned host memory; CSC build; fwd+bwd; loss D2H"}
     except Exception as ex:          # reported, never silently dropped
@@ -321,7 +344,8 @@ def run_b200(args, rank, world, local_rank):
         cpu = {"value": eps, "unit": "edges/s", "cores": cores, "kind": "port", "sample": sample}
     line = {
         "metric": "message-passing edges/sec (fwd+bwd)", "value": value, "unit": "edges/s", "n_gpus": world,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak" if world == 1 else "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
         "clocks": clk, "e2e": e2e, "gpu_launches": stats.launches, "roofline": roofline, "step_roofline": step_roofline,
         "kernels": kern, "cpu_baseline": cpu,

@@ -6,7 +6,7 @@ valid Python identifier; ``b200mp/__init__.py`` at the repo root aliases it).
 Host code is Python/PyTorch (device memory, streams, autograd plumbing) over hand-written CUDA
 kernels behind the C ABI in ``include/b200mp.h``; there is no CPU / PyTorch fallback.
 """
-from . import _lib, functional, graph            # noqa: F401
+from . import _lib, functional, graph, parallel   # noqa: F401
 from .graph import (EdgeStructure, SegmentIndex, degree, degree_histogram, edge_structure,   # noqa: F401
                     relabel, to_csc)
 from .nn import (BatchNorm, GINe, GINEConv, GINEConvHetero, Linear, PNAConv, PNAConvHetero, PNAS)   # noqa: F401

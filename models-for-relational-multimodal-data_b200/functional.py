@@ -219,12 +219,12 @@ def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N):
     return g_e, gT1, gW.sum(0), gb.sum(0)
 
 
-def _edge_update_bwd(st: EdgeStructure, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q):
+def _edge_update_bwd(st: EdgeStructure, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q, nP=None, nQ=None):
     E, H = e.shape
     dev = e.device
     g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
-    gP = torch.zeros((st.num_nodes, H), dtype=torch.float32, device=dev) if need_P else None
-    gQ = torch.zeros((st.num_nodes, H), dtype=torch.float32, device=dev) if need_Q else None
+    gP = torch.zeros((nP or st.num_nodes, H), dtype=torch.float32, device=dev) if need_P else None
+    gQ = torch.zeros((nQ or st.num_nodes, H), dtype=torch.float32, device=dev) if need_Q else None
     npart = L.n_part(E, H)
     gW1 = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
     gW2 = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
@@ -308,7 +308,7 @@ class _PNAAggregate(torch.autograd.Function):
         H = _H(e)
         m, _ = _edge_linear_fwd(0, e, seg.eid32, W, b, B, seg.nbr32, A, seg.seg32)
         agg, tie = _segment_reduce(0, seg, m, H)
-        ctx.seg = seg
+        ctx.seg, ctx.nB = seg, B.shape[0]
         ctx.save_for_backward(m, e, W, agg, tie)
         ctx.mark_non_differentiable(tie)
         return agg, tie
@@ -317,11 +317,10 @@ class _PNAAggregate(torch.autograd.Function):
     def backward(ctx, g_agg, _g_tie):
         m, e, W, agg, tie = ctx.saved_tensors
         seg: SegmentIndex = ctx.seg
-        N, H = seg.num_nodes, m.shape[1]
         g_agg = _f32c(g_agg)
         coef, gA = _pna_coef(seg.ptr, g_agg, agg, tie, ctx.needs_input_grad[0])
         need_B = ctx.needs_input_grad[1]
-        g_e, gB, gW, gb = _message_bwd(0, seg, m, e, coef, W, need_B, N)
+        g_e, gB, gW, gb = _message_bwd(0, seg, m, e, coef, W, need_B, ctx.nB)
         return gA, gB, g_e, gW, gb, None
 
 
@@ -341,7 +340,7 @@ class _GINEAggregate(torch.autograd.Function):
         H = _H(e)
         m, _ = _edge_linear_fwd(1, e, seg.eid32, W, b, x, seg.nbr32, None, None)
         agg, _ = _segment_reduce(1, seg, m, H)
-        ctx.seg = seg
+        ctx.seg, ctx.nx = seg, x.shape[0]
         ctx.save_for_backward(m, e, W)
         return agg
 
@@ -349,7 +348,7 @@ class _GINEAggregate(torch.autograd.Function):
     def backward(ctx, g_agg):
         m, e, W = ctx.saved_tensors
         seg: SegmentIndex = ctx.seg
-        g_e, gx, gW, gb = _message_bwd(1, seg, m, e, _f32c(g_agg), W, ctx.needs_input_grad[0], seg.num_nodes)
+        g_e, gx, gW, gb = _message_bwd(1, seg, m, e, _f32c(g_agg), W, ctx.needs_input_grad[0], ctx.nx)
         return gx, g_e, gW, gb, None
 
 
@@ -367,7 +366,7 @@ class _EdgeUpdate(torch.autograd.Function):
         L.require_cuda(P, Q, e, W1, b1, W2, b2)
         _H(e)
         h, out = _edge_linear_fwd(2, e, None, W1, b1, P, st.src32, Q, st.dst32, W2, b2, float(alpha), float(beta))
-        ctx.st, ctx.alpha, ctx.beta = st, float(alpha), float(beta)
+        ctx.st, ctx.alpha, ctx.beta, ctx.nP, ctx.nQ = st, float(alpha), float(beta), P.shape[0], Q.shape[0]
         ctx.save_for_backward(h, e, W1, W2)
         return out
 
@@ -375,7 +374,7 @@ class _EdgeUpdate(torch.autograd.Function):
     def backward(ctx, g_out):
         h, e, W1, W2 = ctx.saved_tensors
         g_e, gP, gQ, gW1, gb1, gW2, gb2 = _edge_update_bwd(ctx.st, _f32c(g_out), h, e, W1, W2, ctx.alpha, ctx.beta,
-                                                           ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+                                                           ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.nP, ctx.nQ)
         return gP, gQ, g_e, gW1, gb1, gW2, gb2, None, None, None
 
 

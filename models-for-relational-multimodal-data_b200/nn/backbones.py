@@ -80,6 +80,21 @@ class _Backbone(nn.Module):
                 e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5)
         return x, BF.scatter_rows(e, st.fwd.perm)               # back to caller order
 
+    def message_passing_partitioned(self, x_local, e_local, part):
+        """The same loop on one rank of a destination-range partition (parallel.Partition):
+        x_local = owned node rows, e_local = owned edges in local CSC order (part.shard_*)."""
+        from .. import parallel as PL
+        if self.reverse_mp:
+            raise NotImplementedError("reverse_mp is not supported on a partitioned graph")
+        st, x, e = part.st, x_local, e_local
+        gather = lambda t: PL.all_gather_rows(t, part)
+        for i in range(self.num_gnn_layers):
+            c = self.convs[i].forward_sorted(x, st.fwd, e, gather=gather)
+            x = (x + F.relu(PL.sync_batch_norm(self.batch_norms[i].module, c, part))) / 2
+            if self.edge_updates:
+                e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, gather=gather)
+        return x, e
+
     def message_passing(self, x, edge_index, e):
         """The L-layer loop on already embedded x[N,H], e[E,H] (the region BASELINE.json's metric
         times: SURVEY.md section 8d)."""

@@ -71,14 +71,16 @@ class GINEConv(nn.Module):
         self.eps.data.fill_(self.initial_eps)
         self.lin.reset_parameters()
 
-    def forward_sorted(self, x: Union[Tensor, tuple], seg: SegmentIndex, e: Tensor) -> Tensor:
+    def forward_sorted(self, x: Union[Tensor, tuple], seg: SegmentIndex, e: Tensor, gather=None) -> Tensor:
+        """`gather` (multi-GPU, parallel.py): maps the owned rows of the source-side node table to
+        the table of all ranks; the self term and the output stay on the owned rows."""
         self_term = True
         if isinstance(x, (tuple, list)):
             x, x_dst = x
             self_term = x_dst is not None
         if self.lin.weight.shape[0] != self.lin.weight.shape[1] or x.shape[1] != self.lin.weight.shape[0]:
             raise ValueError("b200mp GINEConv kernels need edge_dim == in_channels")
-        out = BF.gine_aggregate(x, e, self.lin.weight, self.lin.bias, seg)
+        out = BF.gine_aggregate(gather(x) if gather is not None else x, e, self.lin.weight, self.lin.bias, seg)
         if self_term:
             out = out + (1 + self.eps) * x
         return self.nn(out)
@@ -138,7 +140,7 @@ class PNAConv(nn.Module):
         self.post_nns[0][0].reset_parameters()
         self.lin.reset_parameters()
 
-    def forward_sorted(self, x: Tensor, seg: SegmentIndex, e: Tensor) -> Tensor:
+    def forward_sorted(self, x: Tensor, seg: SegmentIndex, e: Tensor, gather=None) -> Tensor:
         Fi = self.F_in
         pre = self.pre_nns[0][0]
         Wi, Wj, Wc = pre.weight[:, :Fi], pre.weight[:, Fi:2 * Fi], pre.weight[:, 2 * Fi:]
@@ -146,6 +148,8 @@ class PNAConv(nn.Module):
         # edge encoder into a single H x H matrix (SURVEY.md section 7 "hoisting")
         A = BF.linear3x(x, Wi)
         B = BF.linear3x(x, Wj)
+        if gather is not None:            # multi-GPU: source rows of every rank (parallel.py)
+            B = gather(B)
         Wp = Wc @ self.edge_encoder.weight
         bp = Wc @ self.edge_encoder.bias + pre.bias
         agg4, _ = BF.pna_aggregate(A, B, e, Wp, bp, seg)
@@ -168,12 +172,15 @@ class PNAConv(nn.Module):
         return self.forward_sorted(x, st.fwd, BF.gather_rows(edge_attr, st.fwd.perm))
 
 
-def edge_update_sorted(emlp: nn.Sequential, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float) -> Tensor:
+def edge_update_sorted(emlp: nn.Sequential, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float,
+                       gather=None) -> Tensor:
     """e' = alpha e + beta emlp([x[src], x[dst], e]) with emlp = Sequential(Linear(3H,H), ReLU,
     Linear(H,H)) (gine.py:71-75,88-89; pna.py:80-84,97-99; models/fused.py:215-219,254)."""
     l1, l2 = emlp[0], emlp[2]
     H = x.shape[1]
     Ws, Wd, We = l1.weight[:, :H], l1.weight[:, H:2 * H], l1.weight[:, 2 * H:]
     P = BF.linear3x(x, Ws)
+    if gather is not None:
+        P = gather(P)
     Q = BF.linear3x(x, Wd)
     return BF.edge_update(P, Q, e, We, l1.bias, l2.weight, l2.bias, st, alpha, beta)

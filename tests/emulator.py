@@ -92,12 +92,12 @@ def message_bwd(kind, seg, m, e, node_in, W, need_T1, N):
     return g_e, gT1, Gm.t() @ e[rows], Gm.sum(0)
 
 
-def edge_update_bwd(st, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q):
+def edge_update_bwd(st, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q, nP=None, nQ=None):
     N, H = st.num_nodes, e.shape[1]
     Gout = beta * g_out
     Gh = (Gout @ W2) * (h > 0).to(e.dtype)
-    gP = torch.zeros((N, H), dtype=e.dtype).index_add_(0, st.src32.long(), Gh) if need_P else None
-    gQ = torch.zeros((N, H), dtype=e.dtype).index_add_(0, st.dst32.long(), Gh) if need_Q else None
+    gP = torch.zeros((nP or N, H), dtype=e.dtype).index_add_(0, st.src32.long(), Gh) if need_P else None
+    gQ = torch.zeros((nQ or N, H), dtype=e.dtype).index_add_(0, st.dst32.long(), Gh) if need_Q else None
     g_e = alpha * g_out + Gh @ W1
     return g_e, gP, gQ, Gh.t() @ e, Gh.sum(0), Gout.t() @ h, Gout.sum(0)
 
