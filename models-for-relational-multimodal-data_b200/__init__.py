@@ -9,6 +9,7 @@ kernels behind the C ABI in ``include/b200mp.h``; there is no CPU / PyTorch fall
 from . import _lib, functional, graph, parallel   # noqa: F401
 from .graph import (EdgeStructure, SegmentIndex, degree, degree_histogram, edge_structure,   # noqa: F401
                     relabel, to_csc)
-from .nn import (BatchNorm, GINe, GINEConv, GINEConvHetero, Linear, PNAConv, PNAConvHetero, PNAS)   # noqa: F401
+from .nn import (BatchNorm, GINe, GINEConv, GINEConvHetero, Linear, PNAConv, PNAConvHetero, PNAS,   # noqa: F401
+                 TABGNN, TABGNNFused, TABGNNInterleaved)
 
 __version__ = "0.1.0"

@@ -1,2 +1,4 @@
 from .conv import BatchNorm, GINEConv, Linear, PNAConv, edge_update_sorted    # noqa: F401
 from .backbones import GINe, GINEConvHetero, PNAConvHetero, PNAS              # noqa: F401
+from .tab import (TABGNN, TABGNNFused, TABGNNInterleaved, FTTransformerLayer, PNALayer,            # noqa: F401
+                  FTTransformerPNAFusedLayer, FTTransformerPNAInterleavedLayer)

@@ -1,0 +1,314 @@
+"""Drop-ins for the tabular+graph backbones: ``TABGNN`` (/root/reference/src/nn/models/tabgnn.py:27-219),
+``TABGNNInterleaved`` (src/nn/models/inteleaved.py:28-228) and ``TABGNNFused``
+(src/nn/models/fused.py:31-269).  Same constructors, forward signatures, state_dict keys
+ and residual conventions (note the differing parenthesisation of the column
+attention residual: tabgnn.py:219 vs fused.py:249 / inteleaved.py:219).
+
+Graph side (PNAConv -> BatchNorm -> ReLU -> residual, edge update) runs on the b200mp CUDA kernels
+with the edge tensors held in CSC storage order for all layers.  The column attention over the
+S = K + 1 tokens of a row is torch's post-norm TransformerEncoderLayer (library kernels) behind the
+same attribute names (``tab_conv`` / ``tab_norm``); it is row-wise, hence order-independent.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+from torch import Tensor, nn
+
+from .. import functional as BF
+from ..graph import EdgeStructure, edge_structure
+from .backbones import PNAConvHetero
+from .conv import BatchNorm, PNAConv, edge_update_sorted
+
+_AGGR = ['mean', 'max', 'min', 'std']
+_SCAL = ['identity', 'amplification', 'attenuation']
+
+
+def _xavier(module: nn.Module):
+    for p in module.parameters():
+        if p.dim() > 1:
+            nn.init.xavier_uniform_(p)
+
+
+class _ColumnAttention(nn.Module):
+    """``tab_norm(tab_conv(t))`` over [rows, S, C] tokens."""
+
+    def _init_attention(self, channels, nhead, feedforward_channels, dropout, activation):
+        self.tab_conv = nn.TransformerEncoderLayer(d_model=channels, nhead=nhead,
+                                                   dim_feedforward=feedforward_channels or channels, dropout=dropout,
+                                                   activation=activation, batch_first=True)
+        self.tab_norm = nn.LayerNorm(channels)
+
+    def attend(self, t: Tensor) -> Tensor:
+        return self.tab_norm(self.tab_conv(t))
+
+    def _reset_attention(self):
+        _xavier(self.tab_conv)
+        self.tab_norm.reset_parameters()
+
+
+class _GraphStep(nn.Module):
+    """gnn_conv / gnn_norm / gnn_edge_update of one layer, on sorted (CSC-order) edge tensors."""
+
+    def _init_graph(self, nhidden, deg, reverse_mp):
+        kw = dict(in_channels=nhidden, out_channels=nhidden, aggregators=_AGGR, scalers=_SCAL, deg=deg, edge_dim=nhidden,
+                  towers=1, pre_layers=1, post_layers=1, divide_input=False)
+        self.gnn_conv = PNAConvHetero(n_hidden=nhidden, **kw) if reverse_mp else PNAConv(**kw)
+        self.gnn_norm = BatchNorm(nhidden)
+        self.gnn_edge_update = nn.Sequential(nn.Linear(3 * nhidden, nhidden), nn.ReLU(), nn.Linear(nhidden, nhidden))
+
+    def _reset_graph(self):
+        self.gnn_conv.reset_parameters()
+        self.gnn_norm.reset_parameters()
+        _xavier(self.gnn_edge_update)
+
+    def graph_step(self, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float):
+        c = self.gnn_conv.forward_sorted(x, st, e) if isinstance(self.gnn_conv, PNAConvHetero) \
+            else self.gnn_conv.forward_sorted(x, st.fwd, e)
+        x = (x + F.relu(self.gnn_norm(c))) / 2
+        return x, edge_update_sorted(self.gnn_edge_update, x, st, e, alpha, beta)
+
+
+class _SharedParams:
+    def zero_grad_shared_params(self):
+        for p in self.get_shared_params():
+            if p.grad is not None:
+                p.grad.data.zero_()
+
+
+# ----------------------------------------------------------------------------- TABGNN
+class FTTransformerLayer(_ColumnAttention):
+    def __init__(self, channels, nhead, feedforward_channels=None, dropout=0.5, activation='relu', nhidden=128):
+        super().__init__()
+        self.channels, self.nhidden = channels, nhidden
+        self._init_attention(channels, nhead, feedforward_channels, dropout, activation)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        self._reset_attention()
+
+    def forward(self, x_tab):
+        return (x_tab + self.attend(x_tab)) / 2
+
+
+class PNALayer(_GraphStep):
+    def __init__(self, channels, nhidden=128, deg=None, reverse_mp=False):
+        super().__init__()
+        self.channels, self.nhidden, self.reverse_mp = channels, nhidden, reverse_mp
+        self._init_graph(nhidden, deg, reverse_mp)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        self._reset_graph()
+
+    def forward_sorted(self, x, st, e):
+        return self.graph_step(x, st, e, 1.0, 0.5)                  # e + emlp(.)/2  (tabgnn.py:190)
+
+    def forward(self, x_gnn, edge_index, edge_attr):
+        st = edge_structure(edge_index, x_gnn.shape[0], reverse=self.reverse_mp)
+        x, e = self.forward_sorted(x_gnn, st, BF.gather_rows(edge_attr, st.fwd.perm))
+        return x, BF.scatter_rows(e, st.fwd.perm)
+
+
+class TABGNN(_SharedParams, nn.Module):
+    def __init__(self, channels: int, num_layers: int, deg=None, node_dim: int = 1, nhidden: int = 128,
+                 edge_dim: int = None, reverse_mp: bool = False, feedforward_channels: Optional[int] = None,
+                 nhead: int = 8, dropout: float = 0.5, activation: str = 'relu') -> None:
+        super().__init__()
+        if num_layers <= 0:
+            raise ValueError(f"num_layers must be a positive integer (got {num_layers})")
+        self.channels, self.nhidden, self.reverse_mp = channels, nhidden, reverse_mp
+        self.node_dim, self.edge_dim = node_dim + channels, edge_dim + channels
+        self.cls_embedding = nn.Parameter(torch.empty(channels))
+        self.node_emb = nn.Linear(self.node_dim, nhidden)
+        self.edge_emb = nn.Linear(self.edge_dim, nhidden)
+        self.tabular_backbone = nn.ModuleList(
+            FTTransformerLayer(channels, nhead, feedforward_channels, dropout, activation, nhidden) for _ in range(num_layers))
+        self.gnn_backbone = nn.ModuleList(PNALayer(channels, nhidden, deg, reverse_mp) for _ in range(num_layers))
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        nn.init.normal_(self.cls_embedding, std=0.01)
+        self.node_emb.reset_parameters()
+        self.edge_emb.reset_parameters()
+        for layer in list(self.tabular_backbone) + list(self.gnn_backbone):
+            layer.reset_parameters()
+
+    def get_shared_params(self):
+        return [self.cls_embedding, *self.node_emb.parameters(), *self.edge_emb.parameters(),
+                *self.tabular_backbone.parameters(), *self.gnn_backbone.parameters()]
+
+    def _with_cls(self, t: Tensor) -> Tensor:
+        return torch.cat([self.cls_embedding.expand(t.shape[0], 1, -1), t], dim=1)
+
+    def forward(self, x, edge_index, edge_attr):
+        x, e = self._with_cls(x), self._with_cls(edge_attr)
+        tx, te = x, e
+        for layer in self.tabular_backbone:          # the same layer serves node and edge tokens
+            tx, te = layer(tx), layer(te)
+        x = self.node_emb(((x + tx) / 2).reshape(x.shape[0], -1))
+        e = self.edge_emb(((e + te) / 2).reshape(e.shape[0], -1))
+        st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
+        e = BF.gather_rows(e, st.fwd.perm)
+        for layer in self.gnn_backbone:
+            x, e = layer.forward_sorted(x, st, e)
+        return x, BF.scatter_rows(e, st.fwd.perm)
+
+
+# ----------------------------------------------------------------------------- shared top level of the two mixed models
+class _TabGraphModel(_SharedParams, _ColumnAttention):
+    """cls_embedding, node_emb, edge_emb, top-level tab_conv / tab_norm, backbone[...]."""
+
+    def _init_top(self, layer_cls, channels, num_layers, encoder, deg, node_dim, nhidden, edge_dim, reverse_mp,
+                  feedforward_channels, nhead, dropout, activation):
+        if num_layers <= 0:
+            raise ValueError(f"num_layers must be a positive integer (got {num_layers})")
+        self.channels, self.nhidden, self.node_dim = channels, nhidden, node_dim
+        self.edge_dim, self.encoder, self.reverse_mp = edge_dim + channels, encoder, reverse_mp
+        self.cls_embedding = nn.Parameter(torch.empty(channels))
+        self.node_emb = nn.Linear(node_dim, nhidden)
+        self.edge_emb = nn.Linear(self.edge_dim, nhidden)
+        self._init_attention(channels, nhead, feedforward_channels, dropout, activation)
+        self.backbone = nn.ModuleList(
+            layer_cls(channels, nhead, feedforward_channels, dropout, activation, nhidden, deg, reverse_mp)
+            for _ in range(num_layers))
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        nn.init.normal_(self.cls_embedding, std=0.01)
+        self.node_emb.reset_parameters()
+        self.edge_emb.reset_parameters()
+        self._reset_attention()
+        for layer in self.backbone:
+            layer.reset_parameters()
+
+    def get_shared_params(self):
+        enc = list(self.encoder.parameters()) if isinstance(self.encoder, nn.Module) else []
+        return [*enc, *self.tab_conv.parameters(), *self.tab_norm.parameters(), self.cls_embedding,
+                *self.node_emb.parameters(), *self.edge_emb.parameters(), *self.backbone.parameters()]
+
+    def _with_cls(self, t: Tensor) -> Tensor:
+        return torch.cat([self.cls_embedding.expand(t.shape[0], 1, -1), t], dim=1)
+
+
+class _MixedLayer(_ColumnAttention, _GraphStep):
+    def _init_mixed(self, channels, nhead, feedforward_channels, dropout, activation, nhidden, deg, reverse_mp):
+        self.channels, self.nhidden = channels, nhidden
+        self._init_attention(channels, nhead, feedforward_channels, dropout, activation)
+        self._init_graph(nhidden, deg, reverse_mp)
+
+
+# ----------------------------------------------------------------------------- TABGNNInterleaved
+class FTTransformerPNAInterleavedLayer(_MixedLayer):
+    def __init__(self, channels, nhead, feedforward_channels=None, dropout=0.5, activation='relu', nhidden=128,
+                 deg=None, reverse_mp=False):
+        super().__init__()
+        self._init_mixed(channels, nhead, feedforward_channels, dropout, activation, nhidden, deg, reverse_mp)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        self._reset_attention()
+        self._reset_graph()
+
+    def forward_sorted(self, x, st, tok):
+        """tok [E,S,C] in CSC order; the CLS token is the edge feature of the PNA step."""
+        tok = tok + self.attend(tok) / 2                              # inteleaved.py:219
+        x, cls = self.graph_step(x, st, tok[:, 0, :].contiguous(), 0.5, 0.5)   # (e + emlp(.))/2, :225
+        return x, torch.cat([cls.unsqueeze(1), tok[:, 1:, :]], dim=1)
+
+    def forward(self, x_gnn, edge_index, edge_attr):
+        st = edge_structure(edge_index, x_gnn.shape[0], reverse=isinstance(self.gnn_conv, PNAConvHetero))
+        E, S, C = edge_attr.shape
+        tok = BF.gather_rows(edge_attr.reshape(E, S * C), st.fwd.perm).view(E, S, C)
+        x, tok = self.forward_sorted(x_gnn, st, tok)
+        return x, BF.scatter_rows(tok.reshape(E, S * C), st.fwd.perm).view(E, S, C)
+
+
+class TABGNNInterleaved(_TabGraphModel):
+    def __init__(self, channels: int, num_layers: int, encoder=None, deg=None, node_dim: int = 1, nhidden: int = 128,
+                 edge_dim: int = None, reverse_mp: bool = False, feedforward_channels: Optional[int] = None,
+                 nhead: int = 8, dropout: float = 0.5, activation: str = 'relu') -> None:
+        super().__init__()
+        if channels != nhidden:
+            raise ValueError("TABGNNInterleaved feeds the [E, channels] CLS token to a PNAConv with edge_dim=nhidden: "
+                             "channels must equal nhidden")
+        self._init_top(FTTransformerPNAInterleavedLayer, channels, num_layers, encoder, deg, node_dim, nhidden, edge_dim,
+                       reverse_mp, feedforward_channels, nhead, dropout, activation)
+
+    def forward(self, x, edge_index, edge_attr):
+        x = self.node_emb(x.reshape(-1, self.node_dim))
+        tok0 = self._with_cls(edge_attr)
+        tok0 = (tok0 + self.attend(tok0)) / 2                         # inteleaved.py:155
+        st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
+        E, S, C = tok0.shape
+        tok0 = BF.gather_rows(tok0.reshape(E, S * C), st.fwd.perm).view(E, S, C)
+        tok = tok0
+        for layer in self.backbone:
+            x, tok = layer.forward_sorted(x, st, tok)
+        cls = ((tok + tok0) / 2)[:, 0, :].contiguous()               # :161-162
+        return x, BF.scatter_rows(cls, st.fwd.perm)
+
+
+# ----------------------------------------------------------------------------- TABGNNFused
+class FTTransformerPNAFusedLayer(_MixedLayer):
+    def __init__(self, channels, nhead, feedforward_channels=None, dropout=0.5, activation='relu', nhidden=128,
+                 deg=None, reverse_mp=False):
+        super().__init__()
+        self._init_mixed(channels, nhead, feedforward_channels, dropout, activation, nhidden, deg, reverse_mp)
+        D = channels + 2 * nhidden
+        self.fuse = nn.Sequential(nn.LayerNorm(D), nn.Linear(D, 4 * D), nn.LeakyReLU(), nn.Dropout(dropout),
+                                  nn.Linear(4 * D, 4 * D), nn.LeakyReLU(), nn.Dropout(dropout), nn.Linear(4 * D, D))
+        self.fuse_norm = nn.LayerNorm(D)
+        self.reset_parameters()
+
+    def reset_parameters(self):
+        self._reset_attention()
+        self._reset_graph()
+        _xavier(self.fuse)
+        self.fuse_norm.reset_parameters()
+
+    def forward_sorted(self, x_tab, x, st, e, target_edge_index, lp):
+        C, H = self.channels, self.nhidden
+        x_tab = x_tab + self.attend(x_tab) / 2                        # fused.py:249
+        x, e = self.graph_step(x, st, e, 0.5, 0.5)                    # :252-254
+        if not lp:                                                    # :256-268, restated without unique / in-place
+            cls = x_tab[:, 0, :]
+            z = torch.cat([cls, x[target_edge_index[0]], x[target_edge_index[1]]], dim=-1)
+            z = (z + self.fuse_norm(self.fuse(z))) / 2
+            x_tab = torch.cat([((cls + z[:, :C]) / 2).unsqueeze(1), x_tab[:, 1:, :]], dim=1)
+            index = target_edge_index.reshape(-1)
+            emb = torch.cat([z[:, C:C + H], z[:, C + H:]], dim=0)
+            summed = torch.zeros_like(x).index_add_(0, index, emb)
+            count = torch.bincount(index, minlength=x.shape[0]).to(x.dtype).unsqueeze(1)
+            x = torch.where(count > 0, (x + summed / count.clamp(min=1)) / 2, x)
+        return x_tab, x, e
+
+    def forward(self, x_tab, x_gnn, edge_index, edge_attr, target_edge_index, lp=False):
+        st = edge_structure(edge_index, x_gnn.shape[0], reverse=isinstance(self.gnn_conv, PNAConvHetero))
+        x_tab, x, e = self.forward_sorted(x_tab, x_gnn, st, BF.gather_rows(edge_attr, st.fwd.perm), target_edge_index, lp)
+        return x_tab, x, BF.scatter_rows(e, st.fwd.perm)
+
+
+class TABGNNFused(_TabGraphModel):
+    def __init__(self, channels: int, num_layers: int, encoder=None, deg=None, node_dim: int = 1, nhidden: int = 128,
+                 edge_dim: int = None, reverse_mp: bool = False, feedforward_channels: Optional[int] = None,
+                 nhead: int = 8, dropout: float = 0.5, activation: str = 'relu') -> None:
+        super().__init__()
+        self._init_top(FTTransformerPNAFusedLayer, channels, num_layers, encoder, deg, node_dim, nhidden, edge_dim,
+                       reverse_mp, feedforward_channels, nhead, dropout, activation)
+
+    def forward(self, x, edge_index, edge_attr, target_edge_index, target_edge_attr, lp=False):
+        x = self.node_emb(x.reshape(-1, self.node_dim))
+        tgt0 = self.attend(self._with_cls(target_edge_attr))          # fused.py:160 (no residual)
+        tok = self._with_cls(edge_attr)
+        tok = (tok + self.attend(tok)) / 2                            # :164
+        e = self.edge_emb(tok.reshape(tok.shape[0], -1))
+        st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
+        e = BF.gather_rows(e, st.fwd.perm)
+        x_tab = tgt0
+        for layer in self.backbone:
+            x_tab, x, e = layer.forward_sorted(x_tab, x, st, e, target_edge_index, lp)
+        tgt = self.edge_emb(((x_tab + tgt0) / 2).reshape(tgt0.shape[0], -1))   # :172-174
+        return x, BF.scatter_rows(e, st.fwd.perm), tgt

@@ -34,9 +34,21 @@ def build_module(meta, rec):
         deg = torch.bincount(torch.bincount(ei[1], minlength=n))
         m = b200mp.PNAS(num_features=H, num_gnn_layers=Lyr, n_hidden=H, edge_updates=meta["edge_updates"],
                         edge_dim=K * H, deg=deg, reverse_mp=meta["reverse_mp"])
+    elif kind in ("TABGNN", "TABGNNInterleaved", "TABGNNFused"):
+        ei = rec["in"]["edge_index"]
+        n = rec["in"]["x"].shape[0]
+        deg = torch.bincount(torch.bincount(ei[1], minlength=n))
+        C = meta["C"]
+        kw = dict(channels=C, num_layers=Lyr, deg=deg, nhidden=H, edge_dim=K * C, nhead=meta["nhead"], dropout=0.0)
+        if kind == "TABGNN":
+            m = b200mp.TABGNN(node_dim=rec["in"]["x"].shape[1] * C, **kw)
+        elif kind == "TABGNNInterleaved":
+            m = b200mp.TABGNNInterleaved(node_dim=meta["node_dim"], **kw)
+        else:
+            m = b200mp.TABGNNFused(node_dim=meta["node_dim"], **kw)
     else:
         raise KeyError(kind)
-    missing, unexpected = m.load_state_dict(rec["sd"], strict=True), None
+    m.load_state_dict(rec["sd"], strict=True)
     return m
 
 
@@ -45,6 +57,13 @@ def oracle_fn(meta):
         return lambda p, i: OM.gine(p, i["x"], i["edge_index"], i["edge_attr"], meta["L"], meta["edge_updates"], meta["reverse_mp"])
     if meta["model"] == "PNAS":
         return lambda p, i: OM.pnas(p, i["x"], i["edge_index"], i["edge_attr"], meta["L"], meta["edge_updates"], meta["reverse_mp"])
+    if meta["model"] == "TABGNN":
+        return lambda p, i: OM.tabgnn(p, i["x"], i["edge_index"], i["edge_attr"], meta["L"], meta["nhead"])
+    if meta["model"] == "TABGNNInterleaved":
+        return lambda p, i: OM.tabgnn_interleaved(p, i["x"], i["edge_index"], i["edge_attr"], meta["L"], meta["node_dim"], meta["nhead"])
+    if meta["model"] == "TABGNNFused":
+        return lambda p, i: OM.tabgnn_fused(p, i["x"], i["edge_index"], i["edge_attr"], i["target_edge_index"],
+                                            i["target_edge_attr"], meta["L"], meta["node_dim"], lp=meta["lp"], nhead=meta["nhead"])
     raise KeyError(meta["model"])
 
 
@@ -80,7 +99,11 @@ def run_dropin(rec, device):
     ins = {k: v.clone().to(device) for k, v in rec["in"].items()}
     for k in rec["gin"]:
         ins[k].requires_grad_(True)
-    outs = m(ins["x"], ins["edge_index"], ins["edge_attr"])
+    if rec["meta"]["model"] == "TABGNNFused":
+        outs = m(ins["x"], ins["edge_index"], ins["edge_attr"], ins["target_edge_index"], ins["target_edge_attr"],
+                 lp=rec["meta"]["lp"])
+    else:
+        outs = m(ins["x"], ins["edge_index"], ins["edge_attr"])
     loss = sum((o * rec["w"][str(i)].to(device)).sum() for i, o in enumerate(outs))
     loss.backward()
     gin = {k: ins[k].grad for k in rec["gin"]}
