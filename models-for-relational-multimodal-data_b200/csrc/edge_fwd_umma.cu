@@ -22,13 +22,25 @@ struct EdgeFwdUArgs {
     float* out1; float* out2;
 };
 
+// threads per CTA: the message modes fit two CTAs of 256 per SM; the update's tiles fill shared
+// memory (one CTA per SM), so it runs 512 threads
+template <int MODE> struct FwdCfg { static constexpr int NTH = MODE == 2 ? 512 : 256; };
+
+// Two thread mappings per tile (umma_edge.cuh): the tensor-memory side is row-per-thread
+// (thread (t, ch) reads CW accumulator columns of edge row t and drops them into a staging tile);
+// everything that touches global memory -- e rows, gathered node rows, h / e' / m rows -- runs in
+// the coalesced mapping (thread (g, j): 16-byte chunk j of NP adjacent rows), with the gathered
+// rows and the residual e rows kept in registers instead of shared memory.
 template <int MODE>
-__global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_kernel(EdgeFwdUArgs a) {
+__global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_kernel(EdgeFwdUArgs a) {
+    constexpr int NTH = FwdCfg<MODE>::NTH;
+    constexpr int CW = HH / (NTH / TE);       // accumulator columns per tensor-memory thread
+    constexpr int NP = RowRegs<NTH>::NP;
     extern __shared__ __align__(128) float smem_raw[];
     float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;   // keeps the shared address space
-    float* E_hi = smem;                       // e tile; mode 2: later h
-    float* E_lo = E_hi + RT::FLOATS;          // modes 0/1: later the gathered node rows
-    float* ST = E_lo + RT::FLOATS;            // mode 2 only: gathered node rows, later alpha e
+    float* E_hi = smem;                       // e tile; mode 2: later h.  Modes 0/1: staging tile once the MMAs are done
+    float* E_lo = E_hi + RT::FLOATS;
+    float* ST = E_lo + RT::FLOATS;            // mode 2 only: staging tile
     float* W1_hi = MODE == 2 ? ST + RT::FLOATS : ST;
     float* W1_lo = W1_hi + WT::FLOATS;
     float* W2_hi = W1_lo + WT::FLOATS;        // mode 2 only
@@ -37,26 +49,29 @@ __global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_k
     __shared__ int sidx[2][TE];               // gather indices of the tile (clamped rows)
 
     const int tid = threadIdx.x, warp = tid >> 5;
-    const int t = tid & (TE - 1), ch = tid >> 7;           // epilogue: row t, columns 32 ch ..
+    const int t = tid & (TE - 1), ch = tid >> 7;           // tensor-memory side: row t, columns CW ch ..
+    const int j = tid & 15, g = tid >> 4;                  // global-memory side: chunk j of rows g NP ..
     constexpr uint32_t NCOLS = MODE == 2 ? 128 : 64;
     if (warp == 0) tmem_alloc(&sync.tmem_base, NCOLS);
     if (tid == 0) { mbar_init(&sync.bar[0], 1); mbar_init(&sync.bar[1], 1); mbar_fence_init(); }
-    load_weight_tiles<false>(W1_hi, W1_lo, a.W1, tid);
-    if (MODE == 2) load_weight_tiles<false>(W2_hi, W2_lo, a.W2, tid);
+    load_weight_tiles<false, NTH>(W1_hi, W1_lo, a.W1, tid);
+    if (MODE == 2) load_weight_tiles<false, NTH>(W2_hi, W2_lo, a.W2, tid);
     fence_async_smem();
     fence_before();
     __syncthreads();
     fence_after();
     const uint32_t tm = sync.tmem_base;
     const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
-    const uint32_t T_Z = tm + lane_off + ch * 32, T_U = tm + 64 + lane_off + ch * 32;
-    float* gath = MODE == 2 ? ST : E_lo;
+    const uint32_t T_Z = tm + lane_off + ch * CW, T_U = tm + 64 + lane_off + ch * CW;
+    float* stage = MODE == 2 ? ST : E_hi;
+    const float4 bias1 = ldg4(a.b1 + j * 4);
+    const float4 bias2 = MODE == 2 ? ldg4(a.b2 + j * 4) : f4(0.f, 0.f, 0.f, 0.f);
 
     const int64_t ntiles = (a.E + TE - 1) / TE;
     uint32_t it = 0;
-    RowRegs R;
-    int nrows_pf = 0, idx_pf = 0;             // thread tid: index (tid / 128) of row tid % 128, one tile ahead
-    const int32_t* idx_src = ch == 0 ? a.idx1 : a.idx2;
+    RowRegs<NTH> R, G;
+    int nrows_pf = 0, idx_pf = 0;             // thread tid < 256: index (tid / 128) of row tid % 128, one tile ahead
+    const int32_t* idx_src = ch == 0 ? a.idx1 : ch == 1 ? a.idx2 : nullptr;
     if ((int64_t)blockIdx.x < ntiles) {
         nrows_pf = (int)min64(TE, a.E - (int64_t)blockIdx.x * TE);
         load_rows(R, a.e, a.eid, (int64_t)blockIdx.x * TE, nrows_pf, tid);
@@ -69,7 +84,7 @@ __global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_k
         const uint32_t par = it & 1;
 
         store_rows_split(R, E_hi, E_lo, nrows, tid);
-        sidx[ch][t] = idx_pf;
+        if (ch < 2) sidx[ch][t] = idx_pf;
         fence_async_smem();
         fence_before();
         __syncthreads();
@@ -78,48 +93,32 @@ __global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_k
             gemm3_data(tm, E_hi, E_lo, W1_hi, W1_lo, 0);
             mma_commit(&sync.bar[0]);
         }
-        gather_rows(R, a.T1, sidx[0], a.T2, sidx[1], tid);   // coalesced, in flight while the MMAs run
-        if (MODE != 2) {                     // E_lo is still an MMA operand: wait before reusing it
-            mbar_wait(&sync.bar[0], par);
-            fence_after();
-        }
-        store_rows_raw(R, gath, nrows, tid);
+        gather_rows(G, a.T1, sidx[0], a.T2, sidx[1], tid);   // coalesced, in flight while the MMAs run
+        RowRegs<NTH> Rn;                     // mode 2 keeps this tile's e rows for the residual
+        int nrows_next = 0;
         if (tile + gridDim.x < ntiles) {     // next tile's e rows in flight
-            nrows_pf = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
-            load_rows(R, a.e, a.eid, (tile + gridDim.x) * TE, nrows_pf, tid);
-            if (idx_src) idx_pf = __ldg(idx_src + (tile + gridDim.x) * TE + min(t, nrows_pf - 1));
+            nrows_next = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
+            load_rows(MODE == 2 ? Rn : R, a.e, a.eid, (tile + gridDim.x) * TE, nrows_next, tid);
+            if (idx_src) idx_pf = __ldg(idx_src + (tile + gridDim.x) * TE + min(t, nrows_next - 1));
         }
-        if (MODE == 2) {
-            mbar_wait(&sync.bar[0], par);
-            fence_after();
-        }
-        __syncthreads();                     // gathered rows visible to their row threads
+        mbar_wait(&sync.bar[0], par);
+        fence_after();
+        stage_from_tmem<NTH>(T_Z, stage, t, ch);
+        __syncthreads();
 
-        // ---- epilogue 1: thread (t, ch) = columns 32 ch .. 32 ch + 31 of edge row t
-        {
-            const bool valid = t < nrows;
-            float* o1 = a.out1 + (row0 + t) * HH + ch * 32;
+        // ---- z rows in the coalesced mapping: + bias + gathered node rows (registers)
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                float z[16];
-                tmem_ld16(T_Z + q * 16, z);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int o = RT::off(t, ch * 8 + q * 4 + j);
-                    const int c = q * 16 + j * 4;
-                    float4 v = f4(z[4 * j], z[4 * j + 1], z[4 * j + 2], z[4 * j + 3]) + ldg4(a.b1 + ch * 32 + c) + lds4(gath + o);
-                    if (MODE >= 1) v = relu4(v);
-                    if (!valid) v = f4(0.f, 0.f, 0.f, 0.f);
-                    if (valid) st4(o1 + c, v);
-                    if (MODE == 2) {
-                        const float4 ev = lds4(E_hi + o) + lds4(E_lo + o);
-                        st4(ST + o, a.alpha * ev);
-                        float4 hh, hl;
-                        split4(v, hh, hl);
-                        st4(E_hi + o, hh);
-                        st4(E_lo + o, hl);
-                    }
-                }
+        for (int i = 0; i < NP; ++i) {
+            const int r = g * NP + i;
+            float4 v = lds4(stage + stage_off(r, j)) + bias1 + G.v[i];
+            if (MODE >= 1) v = relu4(v);
+            if (r < nrows) st4(a.out1 + (row0 + r) * HH + j * 4, v);
+            if (MODE == 2) {                 // h -> MMA operand (the e tile is dead: its MMAs are done)
+                float4 hh, hl;
+                split4(r < nrows ? v : f4(0.f, 0.f, 0.f, 0.f), hh, hl);
+                const int o = RT::off(r, j);
+                st4(E_hi + o, hh);
+                st4(E_lo + o, hl);
             }
         }
         if (MODE == 2) {
@@ -131,26 +130,26 @@ __global__ void __launch_bounds__(NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_k
                 gemm3_data(tm + 64, E_hi, E_lo, W2_hi, W2_lo, 0);
                 mma_commit(&sync.bar[1]);
             }
-            int64_t row = row0 + t;
-            if (a.eid && t < nrows) row = __ldg(a.eid + row0 + t);
-            float* o2 = a.out2 + row * HH + ch * 32;
+            int64_t orow[NP];
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
+                const int r = g * NP + i;
+                orow[i] = (a.eid && r < nrows) ? (int64_t)__ldg(a.eid + row0 + r) : row0 + r;
+            }
             mbar_wait(&sync.bar[1], par);
             fence_after();
+            stage_from_tmem<NTH>(T_U, stage, t, ch);
+            __syncthreads();
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                float u[16];
-                tmem_ld16(T_U + q * 16, u);
-                if (t < nrows) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int c = q * 16 + j * 4;
-                        const float4 r4 = lds4(ST + RT::off(t, ch * 8 + q * 4 + j)) +
-                                          a.beta * (f4(u[4 * j], u[4 * j + 1], u[4 * j + 2], u[4 * j + 3]) + ldg4(a.b2 + ch * 32 + c));
-                        st4(o2 + c, r4);
-                    }
-                }
+            for (int i = 0; i < NP; ++i) {
+                const int r = g * NP + i;
+                const float4 v = a.alpha * R.v[i] + a.beta * (lds4(stage + stage_off(r, j)) + bias2);
+                if (r < nrows) st4(a.out2 + orow[i] * HH + j * 4, v);
             }
+#pragma unroll
+            for (int i = 0; i < NP; ++i) R.v[i] = Rn.v[i];
         }
+        nrows_pf = nrows_next;
         fence_before();
         __syncthreads();
         fence_after();
@@ -164,6 +163,7 @@ template <int MODE>
 static int launch_fwd_umma_mode(const EdgeFwdUArgs& a, cudaStream_t st) {
     const size_t smem = (MODE == 2 ? 3 * RT::BYTES + 4 * WT::BYTES : 2 * RT::BYTES + 2 * WT::BYTES) + 1024;
     auto kern = edge_linear_fwd_umma_kernel<MODE>;
+    constexpr int NTH = FwdCfg<MODE>::NTH;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ntiles = (a.E + TE - 1) / TE;
     int grid = persistent_grid((const void*)kern, smem, ntiles, NTH);

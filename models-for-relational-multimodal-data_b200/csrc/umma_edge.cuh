@@ -1,11 +1,16 @@
 // Shared pieces of the tensor-core (tcgen05, 3xTF32) per-edge kernels for H = 64.
 //
-// One CTA = 256 threads = one tile of TE = 128 consecutive edges (segment order) at a time:
+// One CTA = NTH threads (256 or 512) = one tile of TE = 128 consecutive edges (segment order) at a
+// time:
 //   - the threads load [TE x 64] fp32 rows coalesced (16 lanes per 256-byte row), split them into
 //     tf32 hi / lo and store them as row32 tiles (umma.cuh) in shared memory;
 //   - one thread issues the MMAs (accumulators in tensor memory), tcgen05.commit -> mbarrier;
-//   - in every epilogue thread (t, ch) = (tid % 128, tid / 128) owns columns 32 ch .. 32 ch + 31 of
-//     edge row t (tensor-memory lane t; warps w and w + 4 share a lane quarter).
+//   - in every epilogue thread (t, ch) = (tid % 128, tid / 128) owns the CW = 64 / (NTH / 128)
+//     columns CW ch .. CW ch + CW - 1 of edge row t (tensor-memory lane t; warps w, w + 4, ...
+//     share a lane quarter).
+// The kernels whose tiles fill shared memory (one CTA per SM) run 512 threads: their SIMT phases
+// are latency bound (shared-memory round trips, tensor-memory loads, shuffles) and 16 warps hide
+// twice as much of it as 8.
 // Weights sit in shared memory for the CTA's lifetime as interleaved K-major [N x K] tiles.
 #pragma once
 #include "common.cuh"
@@ -16,7 +21,6 @@ namespace ue {
 using namespace umma;
 
 constexpr int TE = 128;          // edges per tile = MMA M
-constexpr int NTH = 256;         // threads per CTA
 constexpr int HH = 64;           // hidden width these kernels are written for
 using RT = RowFmt<TE, HH>;       // activation tile, 32 KB
 using WT = TileFmt<HH, HH>;      // weight tile, 16 KB
@@ -38,7 +42,7 @@ __device__ __forceinline__ void gemm3_wgrad(uint32_t d, const float* g_hi, const
 
 // Weight [64 x 64] row-major in global -> interleaved K-major B tile (hi / lo).
 // TRANSPOSE = false: B[n][k] = W[n][k]   (out = X W^T);   true: B[n][k] = W[k][n]   (out = X W)
-template <bool TRANSPOSE>
+template <bool TRANSPOSE, int NTH>
 __device__ __forceinline__ void load_weight_tiles(float* w_hi, float* w_lo, const float* __restrict__ W, int tid) {
     for (int i = tid; i < HH * HH; i += NTH) {
         const int a = i / HH, b = i % HH;            // W[a][b]
@@ -50,43 +54,58 @@ __device__ __forceinline__ void load_weight_tiles(float* w_hi, float* w_lo, cons
     }
 }
 
-// Coalesced tile rows -> registers: 256 threads, thread handles the 16-byte chunk j = tid % 16 of
-// rows r0 + 16 i (r0 = tid / 16, i < 8).  Loads are branch-free (row index clamped) so that all
-// eight stay in flight; rows >= nrows are zeroed when the registers are stored to shared memory,
-// not here (a select right after the load would wait for it and defeat the prefetch).
-struct RowRegs { float4 v[8]; };
-__device__ __forceinline__ void load_rows(RowRegs& R, const float* __restrict__ src, const int32_t* __restrict__ rowmap,
+// Coalesced tile rows -> registers: thread (g, j) = (tid / 16, tid % 16) handles the 16-byte chunk j
+// of the NP = 16 TE / NTH ADJACENT rows g NP + i (i < NP); the 16 lanes of a group read one whole
+// 256-byte row per access whatever the row is, so global loads, stores and REDs issued in this
+// mapping are coalesced (4 lines per warp request; the row-per-thread mapping of the tensor-memory
+// epilogues would touch 32 lines per request and saturates the L1 pipe).  Adjacent rows of one
+// thread mostly share their segment, which lets per-row node data be reused.  Loads are branch-free
+// (row index clamped) so that all of them stay in flight; rows >= nrows are zeroed when the
+// registers are stored to shared memory, not here (a select right after the load would wait for
+// it and defeat the prefetch).
+template <int NTH>
+struct RowRegs {
+    static constexpr int NP = TE * 16 / NTH;
+    float4 v[NP];
+};
+template <int NTH>
+__device__ __forceinline__ void load_rows(RowRegs<NTH>& R, const float* __restrict__ src, const int32_t* __restrict__ rowmap,
                                           int64_t row0, int nrows, int tid) {
+    constexpr int NP = RowRegs<NTH>::NP;
     const int j = tid & 15, r0 = tid >> 4;
-    int64_t rows[8];
+    int64_t rows[NP];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int rc = min(i * 16 + r0, nrows - 1);
+    for (int i = 0; i < NP; ++i) {
+        const int rc = min(r0 * NP + i, nrows - 1);
         rows[i] = rowmap ? (int64_t)__ldg(rowmap + row0 + rc) : row0 + rc;
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) R.v[i] = ldg4(src + rows[i] * HH + j * 4);
+    for (int i = 0; i < NP; ++i) R.v[i] = ldg4(src + rows[i] * HH + j * 4);
 }
 // R = T1[i1[row]] + T2[i2[row]] (either table nullable), same thread mapping as load_rows.  The
 // row indices come from SHARED memory (staged one tile ahead): with the index loads in global
 // memory ptxas serialises index -> address -> row per row and every row pays a DRAM latency.
-__device__ __forceinline__ void gather_rows(RowRegs& R, const float* __restrict__ T1, const int* i1,
+template <int NTH>
+__device__ __forceinline__ void gather_rows(RowRegs<NTH>& R, const float* __restrict__ T1, const int* i1,
                                             const float* __restrict__ T2, const int* i2, int tid) {
+    constexpr int NP = RowRegs<NTH>::NP;
     const int j = tid & 15, r0 = tid >> 4;
-    float4 t[8];
+    float4 t[NP];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        R.v[i] = T1 ? ldg4(T1 + (int64_t)i1[i * 16 + r0] * HH + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-        t[i] = T2 ? ldg4(T2 + (int64_t)i2[i * 16 + r0] * HH + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = 0; i < NP; ++i) {
+        R.v[i] = T1 ? ldg4(T1 + (int64_t)i1[r0 * NP + i] * HH + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        t[i] = T2 ? ldg4(T2 + (int64_t)i2[r0 * NP + i] * HH + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) R.v[i] = R.v[i] + t[i];
+    for (int i = 0; i < NP; ++i) R.v[i] = R.v[i] + t[i];
 }
-__device__ __forceinline__ void store_rows_split(const RowRegs& R, float* hi, float* lo, int nrows, int tid) {
+template <int NTH>
+__device__ __forceinline__ void store_rows_split(const RowRegs<NTH>& R, float* hi, float* lo, int nrows, int tid) {
+    constexpr int NP = RowRegs<NTH>::NP;
     const int j = tid & 15, r0 = tid >> 4;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int r = i * 16 + r0;
+    for (int i = 0; i < NP; ++i) {
+        const int r = r0 * NP + i;
         float4 h, l;
         split4(r < nrows ? R.v[i] : make_float4(0.f, 0.f, 0.f, 0.f), h, l);
         const int o = RT::off(r, j);
@@ -94,21 +113,42 @@ __device__ __forceinline__ void store_rows_split(const RowRegs& R, float* hi, fl
         st4(lo + o, l);
     }
 }
-__device__ __forceinline__ void store_rows_raw(const RowRegs& R, float* dst, int nrows, int tid) {
+template <int NTH>
+__device__ __forceinline__ void store_rows_raw(const RowRegs<NTH>& R, float* dst, int nrows, int tid) {
+    constexpr int NP = RowRegs<NTH>::NP;
     const int j = tid & 15, r0 = tid >> 4;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int r = i * 16 + r0;
+    for (int i = 0; i < NP; ++i) {
+        const int r = r0 * NP + i;
         st4(dst + RT::off(r, j), r < nrows ? R.v[i] : make_float4(0.f, 0.f, 0.f, 0.f));
     }
 }
 
-// Column sums over the 32 rows of a warp: v[i] = this row's value in column i (i < 32).  Returns
-// in lane L the sum of column L over the warp's rows (31 shuffles: each step halves the columns
-// a lane is responsible for).
-__device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
+// Staging tile for accumulator rows on their way from tensor memory (row-per-thread) to the
+// coalesced row mapping above: [TE][64] fp32, 256-byte rows, 16-byte chunk index XOR-ed with
+// (row % 8) -- conflict free for both sides.  Not an MMA operand.
+__device__ __forceinline__ int stage_off(int r, int c) { return r * HH + (((c ^ r) & 7) << 2) + ((c & 8) << 2); }
+// thread (t, ch): its CW = 64 / (NTH / TE) accumulator columns of row t -> staging tile
+template <int NTH>
+__device__ __forceinline__ void stage_from_tmem(uint32_t taddr, float* S, int t, int ch) {
+    constexpr int CW = HH / (NTH / TE);
 #pragma unroll
-    for (int s = 16; s >= 1; s >>= 1) {
+    for (int q = 0; q < CW / 16; ++q) {
+        float v[16];
+        tmem_ld16(taddr + q * 16, v);
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj)
+            st4(S + stage_off(t, ch * (CW / 4) + q * 4 + jj), f4(v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]));
+    }
+}
+
+// Column sums over the 32 rows of a warp: v[i] = this row's value in column i (i < W, W = 16 or
+// 32).  Returns in lane L the sum of column L % W over the warp's rows (W - 1 shuffles: each step
+// halves the columns a lane is responsible for; W = 16 adds one shuffle across the half warps).
+template <int W>
+__device__ __forceinline__ float warp_column_sums(float (&v)[W], int lane) {
+#pragma unroll
+    for (int s = W / 2; s >= 1; s >>= 1) {
         const bool up = (lane & s) != 0;
 #pragma unroll
         for (int i = 0; i < s; ++i) {
@@ -117,7 +157,16 @@ __device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
             v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
         }
     }
+    if (W == 16) v[0] += __shfl_xor_sync(0xffffffffu, v[0], 16);
     return v[0];
+}
+// Cross-warp finish of per-warp column sums: bsum[warp][32] holds warp_column_sums results of
+// every warp (column group ch = warp / 4, CW columns per group); returns column c (c < 64).
+template <int NTH>
+__device__ __forceinline__ float column_total(const float* bsum, int c) {
+    constexpr int CW = HH / (NTH / TE);
+    const int w0 = (c / CW) * 4, l = c % CW;
+    return bsum[w0 * 32 + l] + bsum[(w0 + 1) * 32 + l] + bsum[(w0 + 2) * 32 + l] + bsum[(w0 + 3) * 32 + l];
 }
 
 // The M = 64 accumulator (weight gradient [64 x 64]) -> this CTA's partial in global memory.
