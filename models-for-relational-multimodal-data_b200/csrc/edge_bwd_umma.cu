@@ -25,26 +25,65 @@ struct UpdBwdUArgs {
 };
 
 constexpr int NTB = 512;                  // threads per CTA of the backward kernels (one CTA per SM)
-constexpr int CWB = HH / (NTB / TE);      // 16 columns per epilogue thread
+constexpr int CWB = HH / (NTB / TE);      // 16 accumulator columns per tensor-memory thread
+constexpr int NPB = RowRegs<NTB>::NP;     // 4 adjacent rows per thread in the coalesced mapping
 
-// g_e rows of a finished tile: ACC2 (tensor memory) -> global.  Runs one tile late, while the next
-// tile's phase A MMAs execute.
-__device__ __forceinline__ void upd_bwd_store_ge(float* __restrict__ g_e, uint32_t T_ACC2, int64_t row0, int nrows, int t, int ch) {
-    float v[16];
-    tmem_ld16(T_ACC2, v);
-    if (t < nrows) {
-        float* o = g_e + (row0 + t) * HH + ch * CWB;
+// One RED per run of equal node ids among a thread's adjacent rows (edges are sorted by
+// destination, so runs are the rule on that side); when the whole warp (8 adjacent rows) is one
+// run the two half warps are combined first.  v[i] must be zero for rows past the tile's end.
+__device__ __forceinline__ void red_runs(float* __restrict__ table, const int (&node)[NPB], const float4 (&v)[NPB], int j, int lane) {
+    bool one = true;
 #pragma unroll
-        for (int c = 0; c < 16; c += 4) st4(o + c, f4(v[c], v[c + 1], v[c + 2], v[c + 3]));
+    for (int i = 1; i < NPB; ++i) one = one && node[i] == node[0];
+    const int n0 = __shfl_sync(0xffffffffu, node[0], 0);
+    if (__all_sync(0xffffffffu, one && node[0] == n0)) {
+        float4 sum = v[0];
+#pragma unroll
+        for (int i = 1; i < NPB; ++i) sum = sum + v[i];
+        sum.x += __shfl_xor_sync(0xffffffffu, sum.x, 16);
+        sum.y += __shfl_xor_sync(0xffffffffu, sum.y, 16);
+        sum.z += __shfl_xor_sync(0xffffffffu, sum.z, 16);
+        sum.w += __shfl_xor_sync(0xffffffffu, sum.w, 16);
+        if (lane < 16) red_add4(table + (int64_t)n0 * HH + j * 4, sum);
+        return;
+    }
+    float4 run = v[0];
+    int cur = node[0];
+#pragma unroll
+    for (int i = 1; i < NPB; ++i) {
+        if (node[i] == cur) {
+            run = run + v[i];
+        } else {
+            red_add4(table + (int64_t)cur * HH + j * 4, run);
+            run = v[i];
+            cur = node[i];
+        }
+    }
+    red_add4(table + (int64_t)cur * HH + j * 4, run);
+}
+
+// Per-thread column partials (thread (g, j): 4 columns of chunk j summed over its rows of all
+// tiles) -> per-CTA column sums; red = [NTB / 16][64] floats of shared memory.
+__device__ __forceinline__ void cta_column_sums(float* red, float4 acc, float* __restrict__ out, float scale, int tid) {
+    __syncthreads();
+    st4(red + (tid >> 4) * HH + (tid & 15) * 4, acc);
+    __syncthreads();
+    if (tid < HH) {
+        float sum = 0.f;
+#pragma unroll 8
+        for (int g = 0; g < NTB / 16; ++g) sum += red[g * HH + tid];
+        out[tid] = scale * sum;
     }
 }
 
+// Thread mappings as in edge_fwd_umma.cu: tensor memory is read row-per-thread into a staging tile;
+// loads, stores, REDs and all element-wise math run in the coalesced mapping (thread (g, j) =
+// 16-byte chunk j of 4 adjacent rows) with the g / h / e rows held in registers.
 __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArgs a) {
-    constexpr int NTH = NTB, CW = CWB;
-    static_assert(CW == 16, "epilogues below read one 16-column tensor-memory group per thread");
+    constexpr int NTH = NTB, CW = CWB, NP = NPB;
     extern __shared__ __align__(128) float smem_raw[];
     float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;   // keeps the shared address space
-    float* G_hi = smem;                       // g tile, later the e tile
+    float* G_hi = smem;                       // g tile; staging tile once its MMAs are done; then the e tile
     float* G_lo = G_hi + RT::FLOATS;
     float* H_hi = G_lo + RT::FLOATS;          // h tile, later the Gh tile
     float* H_lo = H_hi + RT::FLOATS;
@@ -52,11 +91,12 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
     float* W2_lo = W2_hi + WT::FLOATS;
     float* W1_hi = W2_lo + WT::FLOATS;        // B[n=k][K=j] = W1[j][k]   (g_e = Gh W1)
     float* W1_lo = W1_hi + WT::FLOATS;
-    float* bsum = W1_lo + WT::FLOATS;         // [2][NTH / 32 warps][32] bias-gradient partials (kernel end)
     __shared__ TileSync sync;
+    __shared__ int sidx[2][TE];               // src / dst ids of the tile's rows (clamped rows)
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int t = tid & (TE - 1), ch = tid >> 7;
+    const int t = tid & (TE - 1), ch = tid >> 7;           // tensor-memory side
+    const int j = tid & 15, g = tid >> 4;                  // global-memory side
     if (warp == 0) tmem_alloc(&sync.tmem_base, 256);
     if (tid == 0) { mbar_init(&sync.bar[0], 1); mbar_init(&sync.bar[1], 1); mbar_fence_init(); }
     load_weight_tiles<true, NTH>(W2_hi, W2_lo, a.W2, tid);
@@ -69,32 +109,30 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
     const uint32_t T_GW2 = tm + 128, T_GW1 = tm + 192;
     const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t T_U = tm + lane_off + ch * CW, T_ACC2 = tm + 64 + lane_off + ch * CW;
+    float* stage = G_hi;
 
-    float accb1 = 0.f, accb2 = 0.f;           // lane L: column CW ch + L % CW summed over this warp's rows
+    float4 accb1 = f4(0.f, 0.f, 0.f, 0.f), accb2 = f4(0.f, 0.f, 0.f, 0.f);   // columns 4 j .. 4 j + 3 over this thread's rows
     const int64_t ntiles = (a.E + TE - 1) / TE;
     uint32_t it = 0;
-    RowRegs<NTH> R, R2;
-    int nrows_pf = 0, drow_pf = 0, srow_pf = 0;
+    RowRegs<NTH> Rg, Rh, Re;
+    int nrows_pf = 0, idx_pf = 0;
+    const int32_t* idx_src = ch == 0 ? a.src : ch == 1 ? a.dst : nullptr;
     if ((int64_t)blockIdx.x < ntiles) {
         nrows_pf = (int)min64(TE, a.E - (int64_t)blockIdx.x * TE);
-        load_rows(R, a.g_out, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
-        load_rows(R2, a.h, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
-        drow_pf = __ldg(a.dst + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
-        srow_pf = __ldg(a.src + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
+        load_rows(Rg, a.g_out, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
+        load_rows(Rh, a.h, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
+        if (idx_src) idx_pf = __ldg(idx_src + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
     }
-    int64_t prev_row0 = 0;
-    int prev_nrows = 0;
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         const int64_t row0 = tile * TE;
         const int nrows = nrows_pf;
         const uint32_t par = it & 1;
-        const bool valid = t < nrows;
 
-        // ---- phase A: g and h tiles (prefetched) -> shared memory; U = g W2; GW2 += g^T h
-        // (the previous tile's phase B MMAs, which read these buffers, were waited for below)
-        store_rows_split(R, G_hi, G_lo, nrows, tid);
-        store_rows_split(R2, H_hi, H_lo, nrows, tid);
+        // ---- phase A: g and h tiles (prefetched, kept in registers too) -> shared memory; U = g W2; GW2 += g^T h
+        store_rows_split(Rg, G_hi, G_lo, nrows, tid);
+        store_rows_split(Rh, H_hi, H_lo, nrows, tid);
+        if (ch < 2) sidx[ch][t] = idx_pf;
         fence_async_smem();
         fence_before();
         __syncthreads();
@@ -104,89 +142,84 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
             gemm3_wgrad(T_GW2, G_hi, G_lo, H_hi, H_lo, it > 0);
             mma_commit(&sync.bar[0]);
         }
-        load_rows(R, a.e, nullptr, row0, nrows, tid);                 // e tile in flight during the MMAs
-        const int drow = valid ? drow_pf : -1;
-        const int srow = srow_pf;
-        // the previous tile's g_e rows leave ACC2 while this tile's phase A runs on the tensor core
-        if (it > 0) upd_bwd_store_ge(a.g_e, T_ACC2, prev_row0, prev_nrows, t, ch);
+        load_rows(Re, a.e, nullptr, row0, nrows, tid);                // e tile in flight during the MMAs
+        int srow[NP], drow[NP];
+#pragma unroll
+        for (int i = 0; i < NP; ++i) { srow[i] = sidx[0][g * NP + i]; drow[i] = sidx[1][g * NP + i]; }
         mbar_wait(&sync.bar[0], par);
         fence_after();
+        stage_from_tmem<NTH>(T_U, stage, t, ch);                      // the g tile is dead: U rows take its place
+        __syncthreads();
 
-        // ---- epilogue 1 (thread = CW columns of an edge row): Gh, gP[src], gQ[dst], alpha g -> ACC2
+        // ---- Gh = beta U [h > 0] in the coalesced mapping; gP[src], gQ[dst], bias partials; Gh -> MMA operand
         {
-            float gcol[CW], ghcol[CW];
-            float u[16], ag[16];
-            tmem_ld16(T_U, u);
+            float4 Gh[NP];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int o = RT::off(t, ch * (CW / 4) + j);
-                const float4 hv = lds4(H_hi + o) + lds4(H_lo + o);
-                const float4 gv = lds4(G_hi + o) + lds4(G_lo + o);
-                const int c = 4 * j;
-                gcol[c] = gv.x; gcol[c + 1] = gv.y; gcol[c + 2] = gv.z; gcol[c + 3] = gv.w;
-                ag[c] = a.alpha * gv.x; ag[c + 1] = a.alpha * gv.y; ag[c + 2] = a.alpha * gv.z; ag[c + 3] = a.alpha * gv.w;
-                const float4 G = f4(hv.x > 0.f ? a.beta * u[c] : 0.f, hv.y > 0.f ? a.beta * u[c + 1] : 0.f,
-                                    hv.z > 0.f ? a.beta * u[c + 2] : 0.f, hv.w > 0.f ? a.beta * u[c + 3] : 0.f);
-                ghcol[c] = G.x; ghcol[c + 1] = G.y; ghcol[c + 2] = G.z; ghcol[c + 3] = G.w;
-                if (valid && a.gP) red_add4(a.gP + (int64_t)srow * HH + ch * CW + c, G);
+            for (int i = 0; i < NP; ++i) {
+                const int r = g * NP + i;
+                const float4 u = lds4(stage + stage_off(r, j));
+                const float4 hv = Rh.v[i];
+                const bool valid = r < nrows;
+                Gh[i] = f4(valid && hv.x > 0.f ? a.beta * u.x : 0.f, valid && hv.y > 0.f ? a.beta * u.y : 0.f,
+                           valid && hv.z > 0.f ? a.beta * u.z : 0.f, valid && hv.w > 0.f ? a.beta * u.w : 0.f);
+                accb1 = accb1 + Gh[i];
+                if (valid) accb2 = accb2 + Rg.v[i];
+                if (valid && a.gP) red_add4(a.gP + (int64_t)srow[i] * HH + j * 4, Gh[i]);
                 float4 gh, gl;
-                split4(G, gh, gl);
+                split4(Gh[i], gh, gl);
+                const int o = RT::off(r, j);
                 st4(H_hi + o, gh);
                 st4(H_lo + o, gl);
             }
-            tmem_st16(T_ACC2, ag);
-            tmem_st_wait();
-            // grad Q[dst]: a warp whose 32 rows share one destination reduces first (hubs), else per-row REDs
-            const int d0 = __shfl_sync(0xffffffffu, drow, 0);
-            const bool uniform = __all_sync(0xffffffffu, drow == d0) && d0 >= 0;
-            if (!uniform && valid && a.gQ) {
-#pragma unroll
-                for (int c = 0; c < CW; c += 4)
-                    red_add4(a.gQ + (int64_t)drow * HH + ch * CW + c, f4(ghcol[c], ghcol[c + 1], ghcol[c + 2], ghcol[c + 3]));
-            }
-            accb2 += warp_column_sums(gcol, lane);
-            const float s1 = warp_column_sums(ghcol, lane);
-            accb1 += s1;
-            if (uniform && a.gQ && lane < CW) atomicAdd(a.gQ + (int64_t)d0 * HH + ch * CW + lane, s1);
+            if (a.gQ) red_runs(a.gQ, drow, Gh, j, lane);
         }
-        __syncthreads();                                 // every thread is done reading the g tile
-        store_rows_split(R, G_hi, G_lo, nrows, tid);     // e tile replaces it
+        __syncthreads();                                 // every thread is done reading the staged U rows
+        store_rows_split(Re, G_hi, G_lo, nrows, tid);    // e tile replaces them
         fence_async_smem();
         fence_before();
         __syncthreads();
         fence_after();
 
-        // ---- phase B: ACC2 += Gh W1; GW1 += Gh^T e
+        // ---- phase B: ACC2 = Gh W1; GW1 += Gh^T e
         if (tid == 0) {
-            gemm3_data(tm + 64, H_hi, H_lo, W1_hi, W1_lo, 1);
+            gemm3_data(tm + 64, H_hi, H_lo, W1_hi, W1_lo, 0);
             gemm3_wgrad(T_GW1, H_hi, H_lo, G_hi, G_lo, it > 0);
             mma_commit(&sync.bar[1]);
         }
-        if (tile + gridDim.x < ntiles) {                 // next tile's g and h in flight
-            nrows_pf = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
-            load_rows(R, a.g_out, nullptr, (tile + gridDim.x) * TE, nrows_pf, tid);
-            load_rows(R2, a.h, nullptr, (tile + gridDim.x) * TE, nrows_pf, tid);
-            drow_pf = __ldg(a.dst + (tile + gridDim.x) * TE + min(t, nrows_pf - 1));
-            srow_pf = __ldg(a.src + (tile + gridDim.x) * TE + min(t, nrows_pf - 1));
+        int nrows_next = 0;
+        if (tile + gridDim.x < ntiles) {                 // next tile's h in flight (g follows once this tile's g is used)
+            nrows_next = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
+            load_rows(Rh, a.h, nullptr, (tile + gridDim.x) * TE, nrows_next, tid);
+            load_rows(Re, a.g_out, nullptr, (tile + gridDim.x) * TE, nrows_next, tid);
+            if (idx_src) idx_pf = __ldg(idx_src + (tile + gridDim.x) * TE + min(t, nrows_next - 1));
         }
-        prev_row0 = row0;
-        prev_nrows = nrows;
-        mbar_wait(&sync.bar[1], par);                    // both tile buffers are free again; ACC2 is final
+        mbar_wait(&sync.bar[1], par);
+        fence_after();
+        stage_from_tmem<NTH>(T_ACC2, stage, t, ch);      // the e tile is dead too
+        __syncthreads();
+
+        // ---- g_e = alpha g + Gh W1, coalesced rows
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            const int r = g * NP + i;
+            const float4 v = a.alpha * Rg.v[i] + lds4(stage + stage_off(r, j));
+            if (r < nrows) st4(a.g_e + (row0 + r) * HH + j * 4, v);
+        }
+#pragma unroll
+        for (int i = 0; i < NP; ++i) Rg.v[i] = Re.v[i];
+        nrows_pf = nrows_next;
+        fence_before();
+        __syncthreads();
         fence_after();
     }
-    if (it > 0) upd_bwd_store_ge(a.g_e, T_ACC2, prev_row0, prev_nrows, t, ch);
 
     const bool any = it > 0;
     store_wgrad_partial(T_GW1, a.gW1_part + (int64_t)blockIdx.x * HH * HH, 1.f, any, tid);
     store_wgrad_partial(T_GW2, a.gW2_part + (int64_t)blockIdx.x * HH * HH, a.beta, any, tid);
-    bsum[warp * 32 + lane] = accb1;
-    bsum[NTH + warp * 32 + lane] = accb2;
+    cta_column_sums(G_hi, accb1, a.gb1_part + (int64_t)blockIdx.x * HH, 1.f, tid);
+    cta_column_sums(G_hi, accb2, a.gb2_part + (int64_t)blockIdx.x * HH, a.beta, tid);
     fence_before();
     __syncthreads();
-    if (tid < HH) {
-        a.gb1_part[(int64_t)blockIdx.x * HH + tid] = column_total<NTH>(bsum, tid);
-        a.gb2_part[(int64_t)blockIdx.x * HH + tid] = a.beta * column_total<NTH>(bsum + NTH, tid);
-    }
     if (warp == 0) tmem_dealloc(tm, 256);
 }
 
@@ -194,7 +227,7 @@ int launch_upd_bwd_umma(int64_t E, const float* g_out, const float* h, const flo
                         const float* W1, const float* W2, float alpha, float beta, float* g_e, float* gP, float* gQ,
                         float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part, cudaStream_t st) {
     UpdBwdUArgs a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part};
-    const size_t smem = 4 * RT::BYTES + 4 * WT::BYTES + 2 * NTB * sizeof(float) + 1024;
+    const size_t smem = 4 * RT::BYTES + 4 * WT::BYTES + 1024;
     B200MP_CUDA(cudaFuncSetAttribute(edge_update_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     edge_update_bwd_umma_kernel<<<n_part, NTB, smem, st>>>(a);
     B200MP_LAUNCH_CHECK();
@@ -213,22 +246,33 @@ struct MsgBwdUArgs {
     float* gW_part; float* gb_part;
 };
 
+// PNA per-edge gradient from the saved message and the destination's coefficient rows
+// (c0, c1, g_min, min, g_max, max, mean; node_ops.cu / edge_bwd.cu have the rules)
+struct PnaCoef { float4 c0, c1, gmn, mn, gmx, mx, mu; };
+__device__ __forceinline__ void load_coef(PnaCoef& c, const float* __restrict__ q) {
+    c.c0 = ldg4(q); c.c1 = ldg4(q + HH); c.gmn = ldg4(q + 2 * HH); c.mn = ldg4(q + 3 * HH);
+    c.gmx = ldg4(q + 4 * HH); c.mx = ldg4(q + 5 * HH); c.mu = ldg4(q + 6 * HH);
+}
+__device__ __forceinline__ float pna_g(float m, float c0, float c1, float gmn, float mn, float gmx, float mx, float mu) {
+    return fmaf(c1, m - mu, c0) + (m == mn ? gmn : 0.f) + (m == mx ? gmx : 0.f);
+}
+
 template <int KIND>
 __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a) {
-    constexpr int NTH = NTB, CW = CWB;
+    constexpr int NTH = NTB, CW = CWB, NP = NPB;
     extern __shared__ __align__(128) float smem_raw[];
     float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;   // keeps the shared address space
-    float* G_hi = smem;                       // first the raw m tile, then G (hi)
+    float* G_hi = smem;                       // per-edge gradient G
     float* G_lo = G_hi + RT::FLOATS;
-    float* E_hi = G_lo + RT::FLOATS;
+    float* E_hi = G_lo + RT::FLOATS;          // e tile; staging tile once the MMAs are done
     float* E_lo = E_hi + RT::FLOATS;
     float* W_hi = E_lo + RT::FLOATS;          // B[n=k][K=j] = W[j][k]   (g_e = G W)
     float* W_lo = W_hi + WT::FLOATS;
-    float* bsum = W_lo + WT::FLOATS;          // [NTH / 32 warps][32]
     __shared__ TileSync sync;
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int t = tid & (TE - 1), ch = tid >> 7;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int t = tid & (TE - 1), ch = tid >> 7;           // tensor-memory side
+    const int j = tid & 15, g = tid >> 4;                  // global-memory side
     if (warp == 0) tmem_alloc(&sync.tmem_base, 128);
     if (tid == 0) { mbar_init(&sync.bar[0], 1); mbar_fence_init(); }
     load_weight_tiles<true, NTH>(W_hi, W_lo, a.W, tid);
@@ -239,61 +283,69 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
     const uint32_t tm = sync.tmem_base;
     const uint32_t T_GW = tm + 64;
     const uint32_t T_ACC = tm + ((uint32_t)((warp & 3) * 32) << 16) + ch * CW;
+    float* stage = E_hi;
 
-    float accb = 0.f;
+    float4 accb = f4(0.f, 0.f, 0.f, 0.f);     // columns 4 j .. 4 j + 3 over this thread's rows
     const int64_t ntiles = (a.E + TE - 1) / TE;
     uint32_t it = 0;
-    RowRegs<NTH> R, R2;
-    int nrows_pf = 0, seg_pf = 0, nbr_pf = 0;
-    if ((int64_t)blockIdx.x < ntiles) {
-        nrows_pf = (int)min64(TE, a.E - (int64_t)blockIdx.x * TE);
-        load_rows(R, a.m, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
-        load_rows(R2, a.e, a.eid, (int64_t)blockIdx.x * TE, nrows_pf, tid);
-        seg_pf = __ldg(a.seg + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
-        if (a.gT1) nbr_pf = __ldg(a.nbr + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
-    }
+    RowRegs<NTH> Rm, Re;
+    int nrows_pf = 0, seg_pf[NP], nbr_pf[NP];
+#pragma unroll
+    for (int i = 0; i < NP; ++i) { seg_pf[i] = 0; nbr_pf[i] = 0; }
+    auto prefetch = [&](int64_t tile_) {
+        const int64_t r0_ = tile_ * TE;
+        nrows_pf = (int)min64(TE, a.E - r0_);
+        load_rows(Rm, a.m, nullptr, r0_, nrows_pf, tid);
+        load_rows(Re, a.e, a.eid, r0_, nrows_pf, tid);
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            const int rc = min(g * NP + i, nrows_pf - 1);
+            seg_pf[i] = __ldg(a.seg + r0_ + rc);
+            if (a.gT1) nbr_pf[i] = __ldg(a.nbr + r0_ + rc);
+        }
+    };
+    if ((int64_t)blockIdx.x < ntiles) prefetch(blockIdx.x);
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         const int64_t row0 = tile * TE;
         const int nrows = nrows_pf;
-        const bool valid = t < nrows;
 
-        store_rows_raw(R, G_hi, nrows, tid);                           // m tile (prefetched)
-        store_rows_split(R2, E_hi, E_lo, nrows, tid);
-        const int64_t d = seg_pf;
-        const int64_t nrow = nbr_pf;
-        __syncthreads();
-
-        // ---- per-edge gradient G (thread = CW columns of an edge row), in place over the m tile
+        store_rows_split(Re, E_hi, E_lo, nrows, tid);
+        // ---- per-edge gradient G in the coalesced mapping (m rows and ids are in registers)
         {
-            float gcol[CW];
+            float4 Gv[NP];
+            PnaCoef cf;
+            float4 ga = f4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int j = 0; j < CW / 4; ++j) {
-                const int o = RT::off(t, ch * (CW / 4) + j);
-                const int c = ch * CW + j * 4;
-                const float4 mv = lds4(G_hi + o);
+            for (int i = 0; i < NP; ++i) {
+                const int r = g * NP + i;
+                const float4 mv = Rm.v[i];
+                const int64_t d = seg_pf[i];
+                const bool fresh = i == 0 || seg_pf[i] != seg_pf[i - 1];      // adjacent rows mostly share their segment
                 float4 G;
                 if (KIND == 0) {
-                    const float* q = a.node_in + d * 7 * HH + c;
-                    const float4 c0 = ldg4(q), c1 = ldg4(q + HH), gmn = ldg4(q + 2 * HH), mn = ldg4(q + 3 * HH),
-                                 gmx = ldg4(q + 4 * HH), mx = ldg4(q + 5 * HH), mu = ldg4(q + 6 * HH);
-                    G.x = fmaf(c1.x, mv.x - mu.x, c0.x) + (mv.x == mn.x ? gmn.x : 0.f) + (mv.x == mx.x ? gmx.x : 0.f);
-                    G.y = fmaf(c1.y, mv.y - mu.y, c0.y) + (mv.y == mn.y ? gmn.y : 0.f) + (mv.y == mx.y ? gmx.y : 0.f);
-                    G.z = fmaf(c1.z, mv.z - mu.z, c0.z) + (mv.z == mn.z ? gmn.z : 0.f) + (mv.z == mx.z ? gmx.z : 0.f);
-                    G.w = fmaf(c1.w, mv.w - mu.w, c0.w) + (mv.w == mn.w ? gmn.w : 0.f) + (mv.w == mx.w ? gmx.w : 0.f);
+                    if (fresh) load_coef(cf, a.node_in + d * 7 * HH + j * 4);
+                    G.x = pna_g(mv.x, cf.c0.x, cf.c1.x, cf.gmn.x, cf.mn.x, cf.gmx.x, cf.mx.x, cf.mu.x);
+                    G.y = pna_g(mv.y, cf.c0.y, cf.c1.y, cf.gmn.y, cf.mn.y, cf.gmx.y, cf.mx.y, cf.mu.y);
+                    G.z = pna_g(mv.z, cf.c0.z, cf.c1.z, cf.gmn.z, cf.mn.z, cf.gmx.z, cf.mx.z, cf.mu.z);
+                    G.w = pna_g(mv.w, cf.c0.w, cf.c1.w, cf.gmn.w, cf.mn.w, cf.gmx.w, cf.mx.w, cf.mu.w);
                 } else {
-                    const float4 ga = ldg4(a.node_in + d * HH + c);
+                    if (fresh) ga = ldg4(a.node_in + d * HH + j * 4);
                     G = f4(mv.x > 0.f ? ga.x : 0.f, mv.y > 0.f ? ga.y : 0.f, mv.z > 0.f ? ga.z : 0.f, mv.w > 0.f ? ga.w : 0.f);
                 }
-                if (!valid) G = f4(0.f, 0.f, 0.f, 0.f);
-                if (valid && a.gT1) red_add4(a.gT1 + nrow * HH + c, G);
-                gcol[4 * j] = G.x; gcol[4 * j + 1] = G.y; gcol[4 * j + 2] = G.z; gcol[4 * j + 3] = G.w;
+                if (r >= nrows) G = f4(0.f, 0.f, 0.f, 0.f);
+                if (r < nrows && a.gT1) red_add4(a.gT1 + (int64_t)nbr_pf[i] * HH + j * 4, G);
+                accb = accb + G;
+                Gv[i] = G;
+            }
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
                 float4 gh, gl;
-                split4(G, gh, gl);
+                split4(Gv[i], gh, gl);
+                const int o = RT::off(g * NP + i, j);
                 st4(G_hi + o, gh);
                 st4(G_lo + o, gl);
             }
-            accb += warp_column_sums(gcol, lane);
         }
         fence_async_smem();
         fence_before();
@@ -304,37 +356,31 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
             gemm3_wgrad(T_GW, G_hi, G_lo, E_hi, E_lo, it > 0);
             mma_commit(&sync.bar[0]);
         }
-        int64_t row = row0 + t;
-        if (a.eid && valid) row = __ldg(a.eid + row0 + t);
-        float* o = a.g_e + row * HH + ch * CW;
-        float4 prev[CW / 4];
-        if (a.accumulate && valid) {
+        int64_t orow[NP];
+        float4 prev[NP];
 #pragma unroll
-            for (int c = 0; c < CW / 4; ++c) prev[c] = *reinterpret_cast<const float4*>(o + c * 4);
+        for (int i = 0; i < NP; ++i) {
+            const int r = g * NP + i;
+            orow[i] = (a.eid && r < nrows) ? (int64_t)__ldg(a.eid + row0 + r) : row0 + r;
         }
-        if (tile + gridDim.x < ntiles) {                 // next tile's m and e in flight
-            nrows_pf = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
-            load_rows(R, a.m, nullptr, (tile + gridDim.x) * TE, nrows_pf, tid);
-            load_rows(R2, a.e, a.eid, (tile + gridDim.x) * TE, nrows_pf, tid);
-            seg_pf = __ldg(a.seg + (tile + gridDim.x) * TE + min(t, nrows_pf - 1));
-            if (a.gT1) nbr_pf = __ldg(a.nbr + (tile + gridDim.x) * TE + min(t, nrows_pf - 1));
+        if (a.accumulate) {
+#pragma unroll
+            for (int i = 0; i < NP; ++i)
+                prev[i] = (g * NP + i < nrows) ? *reinterpret_cast<const float4*>(a.g_e + orow[i] * HH + j * 4) : f4(0.f, 0.f, 0.f, 0.f);
         }
+        if (tile + gridDim.x < ntiles) prefetch(tile + gridDim.x);    // next tile's m, e and ids in flight
         mbar_wait(&sync.bar[0], it & 1);
         fence_after();
+        stage_from_tmem<NTH>(T_ACC, stage, t, ch);        // the e tile is dead: g_e rows take its place
+        __syncthreads();
 
-        // ---- epilogue: g_e rows (row(k) = eid ? eid[k] : k)
+        // ---- g_e rows, coalesced (row(k) = eid ? eid[k] : k)
 #pragma unroll
-        for (int q = 0; q < CW / 16; ++q) {
-            float v[16];
-            tmem_ld16(T_ACC + q * 16, v);
-            if (valid) {
-#pragma unroll
-                for (int c = 0; c < 16; c += 4) {
-                    float4 r4 = f4(v[c], v[c + 1], v[c + 2], v[c + 3]);
-                    if (a.accumulate) r4 = r4 + prev[q * 4 + c / 4];
-                    st4(o + q * 16 + c, r4);
-                }
-            }
+        for (int i = 0; i < NP; ++i) {
+            const int r = g * NP + i;
+            float4 v = lds4(stage + stage_off(r, j));
+            if (a.accumulate) v = v + prev[i];
+            if (r < nrows) st4(a.g_e + orow[i] * HH + j * 4, v);
         }
         fence_before();
         __syncthreads();
@@ -342,10 +388,9 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
     }
 
     store_wgrad_partial(T_GW, a.gW_part + (int64_t)blockIdx.x * HH * HH, 1.f, it > 0, tid);
-    bsum[warp * 32 + lane] = accb;
+    cta_column_sums(G_hi, accb, a.gb_part + (int64_t)blockIdx.x * HH, 1.f, tid);
     fence_before();
     __syncthreads();
-    if (tid < HH) a.gb_part[(int64_t)blockIdx.x * HH + tid] = column_total<NTH>(bsum, tid);
     if (warp == 0) tmem_dealloc(tm, 128);
 }
 
@@ -353,7 +398,7 @@ int launch_msg_bwd_umma(int kind, int64_t E, const float* m, const float* e, con
                         const int32_t* seg, const int32_t* nbr, const float* W, float* g_e, int accumulate, float* gT1,
                         float* gW_part, float* gb_part, int n_part, cudaStream_t st) {
     MsgBwdUArgs a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part};
-    const size_t smem = 4 * RT::BYTES + 2 * WT::BYTES + NTB * sizeof(float) + 1024;
+    const size_t smem = 4 * RT::BYTES + 2 * WT::BYTES + 1024;
     auto kern = kind == 0 ? message_bwd_umma_kernel<0> : message_bwd_umma_kernel<1>;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<n_part, NTB, smem, st>>>(a);
