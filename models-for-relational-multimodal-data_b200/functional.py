@@ -203,17 +203,36 @@ def _segment_reduce(kind, seg: SegmentIndex, m, H):
     return agg, tie
 
 
-def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N):
+class EdgeGradSink:
+    """Lets the two consumers of one edge tensor (the conv's message and the edge update of the
+    same layer) produce ONE gradient buffer: the edge update's backward, which autograd always
+    runs first (its node inputs depend on the conv output), deposits its g_e here instead of
+    returning it, and the message backward accumulates into that buffer inside the kernel --
+    autograd would otherwise add the two [E,H] tensors in a separate pass over HBM.  Armed only
+    by the backbones' layer loop, where that structure is guaranteed."""
+    __slots__ = ("buf",)
+
+    def __init__(self):
+        self.buf = None
+
+    def take(self):
+        b, self.buf = self.buf, None
+        return b
+
+
+def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N, g_e=None):
     E, H = m.shape
     dev = m.device
-    g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
+    accumulate = 0 if g_e is None else 1
+    if g_e is None:
+        g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
     gT1 = torch.zeros((N, H), dtype=torch.float32, device=dev) if need_T1 else None
     npart = L.n_part(E, H)
     gW = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
     gb = torch.empty((npart, H), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev), _track("pna_message_bwd" if kind == 0 else "gine_message_bwd"):
         L.check(L.lib().b200mp_message_bwd(kind, H, E, L.ptr(m), L.ptr(e), L.ptr(seg.eid32), L.ptr(node_in),
-                                           L.ptr(seg.seg32), L.ptr(seg.nbr32), L.ptr(W), L.ptr(g_e), 0, L.ptr(gT1),
+                                           L.ptr(seg.seg32), L.ptr(seg.nbr32), L.ptr(W), L.ptr(g_e), accumulate, L.ptr(gT1),
                                            L.ptr(gW), L.ptr(gb), npart, L.stream()),
                 "b200mp_message_bwd")
     return g_e, gT1, gW.sum(0), gb.sum(0)
@@ -302,13 +321,13 @@ class _PNAAggregate(torch.autograd.Function):
     """agg4[N,4H] = [mean|min|max|std] over incoming m_k = A[seg_k] + B[nbr_k] + e_k W^T + b."""
 
     @staticmethod
-    def forward(ctx, A, B, e, W, b, seg: SegmentIndex):
+    def forward(ctx, A, B, e, W, b, seg: SegmentIndex, sink=None):
         A, B, e, W, b = map(_f32c, (A, B, e, W, b))
         L.require_cuda(A, B, e, W, b)
         H = _H(e)
         m, _ = _edge_linear_fwd(0, e, seg.eid32, W, b, B, seg.nbr32, A, seg.seg32)
         agg, tie = _segment_reduce(0, seg, m, H)
-        ctx.seg, ctx.nB = seg, B.shape[0]
+        ctx.seg, ctx.nB, ctx.sink = seg, B.shape[0], sink
         ctx.save_for_backward(m, e, W, agg, tie)
         ctx.mark_non_differentiable(tie)
         return agg, tie
@@ -320,13 +339,14 @@ class _PNAAggregate(torch.autograd.Function):
         g_agg = _f32c(g_agg)
         coef, gA = _pna_coef(seg.ptr, g_agg, agg, tie, ctx.needs_input_grad[0])
         need_B = ctx.needs_input_grad[1]
-        g_e, gB, gW, gb = _message_bwd(0, seg, m, e, coef, W, need_B, ctx.nB)
-        return gA, gB, g_e, gW, gb, None
+        acc = ctx.sink.take() if (ctx.sink is not None and seg.eid32 is None) else None
+        g_e, gB, gW, gb = _message_bwd(0, seg, m, e, coef, W, need_B, ctx.nB, acc)
+        return gA, gB, g_e, gW, gb, None, None
 
 
-def pna_aggregate(A, B, e, W, b, seg: SegmentIndex):
+def pna_aggregate(A, B, e, W, b, seg: SegmentIndex, sink=None):
     """Returns (agg4 [N,4H] in the order mean,min,max,std, tie counts [N,2H])."""
-    return _PNAAggregate.apply(A, B, e, W, b, seg)
+    return _PNAAggregate.apply(A, B, e, W, b, seg, sink)
 
 
 # ----------------------------------------------------------------------------- GINE aggregation
@@ -334,13 +354,13 @@ class _GINEAggregate(torch.autograd.Function):
     """agg[N,H] = sum over incoming relu(x[nbr_k] + e_k W^T + b)."""
 
     @staticmethod
-    def forward(ctx, x, e, W, b, seg: SegmentIndex):
+    def forward(ctx, x, e, W, b, seg: SegmentIndex, sink=None):
         x, e, W, b = map(_f32c, (x, e, W, b))
         L.require_cuda(x, e, W, b)
         H = _H(e)
         m, _ = _edge_linear_fwd(1, e, seg.eid32, W, b, x, seg.nbr32, None, None)
         agg, _ = _segment_reduce(1, seg, m, H)
-        ctx.seg, ctx.nx = seg, x.shape[0]
+        ctx.seg, ctx.nx, ctx.sink = seg, x.shape[0], sink
         ctx.save_for_backward(m, e, W)
         return agg
 
@@ -348,12 +368,13 @@ class _GINEAggregate(torch.autograd.Function):
     def backward(ctx, g_agg):
         m, e, W = ctx.saved_tensors
         seg: SegmentIndex = ctx.seg
-        g_e, gx, gW, gb = _message_bwd(1, seg, m, e, _f32c(g_agg), W, ctx.needs_input_grad[0], ctx.nx)
-        return gx, g_e, gW, gb, None
+        acc = ctx.sink.take() if (ctx.sink is not None and seg.eid32 is None) else None
+        g_e, gx, gW, gb = _message_bwd(1, seg, m, e, _f32c(g_agg), W, ctx.needs_input_grad[0], ctx.nx, acc)
+        return gx, g_e, gW, gb, None, None
 
 
-def gine_aggregate(x, e, W, b, seg: SegmentIndex):
-    return _GINEAggregate.apply(x, e, W, b, seg)
+def gine_aggregate(x, e, W, b, seg: SegmentIndex, sink=None):
+    return _GINEAggregate.apply(x, e, W, b, seg, sink)
 
 
 # ----------------------------------------------------------------------------- edge update
@@ -361,12 +382,12 @@ class _EdgeUpdate(torch.autograd.Function):
     """e' = alpha e + beta (relu(P[src] + Q[dst] + e W1^T + b1) W2^T + b2), e-storage order."""
 
     @staticmethod
-    def forward(ctx, P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha, beta):
+    def forward(ctx, P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha, beta, sink=None):
         P, Q, e, W1, b1, W2, b2 = map(_f32c, (P, Q, e, W1, b1, W2, b2))
         L.require_cuda(P, Q, e, W1, b1, W2, b2)
         _H(e)
         h, out = _edge_linear_fwd(2, e, None, W1, b1, P, st.src32, Q, st.dst32, W2, b2, float(alpha), float(beta))
-        ctx.st, ctx.alpha, ctx.beta, ctx.nP, ctx.nQ = st, float(alpha), float(beta), P.shape[0], Q.shape[0]
+        ctx.st, ctx.alpha, ctx.beta, ctx.nP, ctx.nQ, ctx.sink = st, float(alpha), float(beta), P.shape[0], Q.shape[0], sink
         ctx.save_for_backward(h, e, W1, W2)
         return out
 
@@ -375,8 +396,11 @@ class _EdgeUpdate(torch.autograd.Function):
         h, e, W1, W2 = ctx.saved_tensors
         g_e, gP, gQ, gW1, gb1, gW2, gb2 = _edge_update_bwd(ctx.st, _f32c(g_out), h, e, W1, W2, ctx.alpha, ctx.beta,
                                                            ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.nP, ctx.nQ)
-        return gP, gQ, g_e, gW1, gb1, gW2, gb2, None, None, None
+        if ctx.sink is not None and ctx.needs_input_grad[2]:
+            ctx.sink.buf = g_e            # the same layer's message backward accumulates into it and returns it
+            g_e = None
+        return gP, gQ, g_e, gW1, gb1, gW2, gb2, None, None, None, None
 
 
-def edge_update(P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha: float, beta: float):
-    return _EdgeUpdate.apply(P, Q, e, W1, b1, W2, b2, st, alpha, beta)
+def edge_update(P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha: float, beta: float, sink=None):
+    return _EdgeUpdate.apply(P, Q, e, W1, b1, W2, b2, st, alpha, beta, sink)

@@ -31,8 +31,8 @@ class GINEConvHetero(_HeteroMixin, nn.Module):
         self.conv_back = GINEConv(network, edge_dim=n_hidden)      # same `network` object, as in the reference
         self.lin = Linear(n_hidden * 3, n_hidden)
 
-    def forward_sorted(self, x, st: EdgeStructure, e):
-        a_in = self.conv_forw.forward_sorted((x, None), st.fwd, e)
+    def forward_sorted(self, x, st: EdgeStructure, e, sink=None):
+        a_in = self.conv_forw.forward_sorted((x, None), st.fwd, e, sink=sink)
         a_out = self.conv_back.forward_sorted((x, None), st.rev, e)
         return self.lin(torch.cat([x, a_in, a_out], dim=1))
 
@@ -52,8 +52,8 @@ class PNAConvHetero(_HeteroMixin, nn.Module):
         self.conv_back = PNAConv(**kw)
         self.lin = Linear(n_hidden * 3, n_hidden)
 
-    def forward_sorted(self, x, st: EdgeStructure, e):
-        a_in = self.conv_forw.forward_sorted(x, st.fwd, e)
+    def forward_sorted(self, x, st: EdgeStructure, e, sink=None):
+        a_in = self.conv_forw.forward_sorted(x, st.fwd, e, sink=sink)
         a_out = self.conv_back.forward_sorted(x, st.rev, e)
         return self.lin(torch.cat([x, a_in, a_out], dim=1))
 
@@ -62,10 +62,10 @@ class PNAConvHetero(_HeteroMixin, nn.Module):
         return self.forward_sorted(x, st, BF.gather_rows(edge_attr, st.fwd.perm))
 
 
-def _conv_sorted(conv, x, st: EdgeStructure, e):
+def _conv_sorted(conv, x, st: EdgeStructure, e, sink=None):
     if isinstance(conv, (GINEConvHetero, PNAConvHetero)):
-        return conv.forward_sorted(x, st, e)
-    return conv.forward_sorted(x, st.fwd, e)
+        return conv.forward_sorted(x, st, e, sink=sink)
+    return conv.forward_sorted(x, st.fwd, e, sink=sink)
 
 
 class _Backbone(nn.Module):
@@ -75,9 +75,11 @@ class _Backbone(nn.Module):
         st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
         e = BF.gather_rows(e, st.fwd.perm)                      # caller order -> CSC storage order
         for i in range(self.num_gnn_layers):
-            x = (x + F.relu(self.batch_norms[i](_conv_sorted(self.convs[i], x, st, e)))) / 2
+            # conv and edge update of a layer read the same e: one gradient buffer for both
+            sink = BF.EdgeGradSink() if (self.edge_updates and e.requires_grad and torch.is_grad_enabled()) else None
+            x = (x + F.relu(self.batch_norms[i](_conv_sorted(self.convs[i], x, st, e, sink)))) / 2
             if self.edge_updates:
-                e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5)
+                e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, sink=sink)
         return x, BF.scatter_rows(e, st.fwd.perm)               # back to caller order
 
     def message_passing_partitioned(self, x_local, e_local, part):
@@ -89,10 +91,11 @@ class _Backbone(nn.Module):
         st, x, e = part.st, x_local, e_local
         gather = lambda t: PL.all_gather_rows(t, part)
         for i in range(self.num_gnn_layers):
-            c = self.convs[i].forward_sorted(x, st.fwd, e, gather=gather)
+            sink = BF.EdgeGradSink() if (self.edge_updates and e.requires_grad and torch.is_grad_enabled()) else None
+            c = self.convs[i].forward_sorted(x, st.fwd, e, gather=gather, sink=sink)
             x = (x + F.relu(PL.sync_batch_norm(self.batch_norms[i].module, c, part))) / 2
             if self.edge_updates:
-                e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, gather=gather)
+                e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, gather=gather, sink=sink)
         return x, e
 
     def message_passing(self, x, edge_index, e):

@@ -76,8 +76,9 @@ def segment_reduce(kind, seg, m, H):
     return agg, torch.cat([cn, cx], 1) * has
 
 
-def message_bwd(kind, seg, m, e, node_in, W, need_T1, N):
+def message_bwd(kind, seg, m, e, node_in, W, need_T1, N, g_e=None):
     H = m.shape[1]
+    acc = g_e
     d = seg.seg32.long()
     rows = seg.eid32.long() if seg.eid32 is not None else torch.arange(m.shape[0])
     if kind == 0:
@@ -89,6 +90,9 @@ def message_bwd(kind, seg, m, e, node_in, W, need_T1, N):
     gT1 = torch.zeros((N, H), dtype=m.dtype).index_add_(0, seg.nbr32.long(), Gm) if need_T1 else None
     g_e = torch.empty_like(e)
     g_e[rows] = Gm @ W
+    if acc is not None:                      # kernel contract: accumulate into the given buffer and return it
+        acc += g_e
+        g_e = acc
     return g_e, gT1, Gm.t() @ e[rows], Gm.sum(0)
 
 
