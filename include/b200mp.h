@@ -76,6 +76,18 @@ int b200mp_scatter_rows(const float* in, const int64_t* idx, float* out, int64_t
  * pna.py:71-79, gine.py:66-70 through PNAConv.update / GINEConv.nn). */
 int b200mp_split_tf32(const float* x, float* hi, float* lo, int64_t n, void* stream);
 
+/* Node-level linear on the tensor cores (tcgen05, 3xTF32; fp32 accuracy ~1e-7), one pass over HBM:
+ *   Y[N, NO] = X[N, K] W^T (+ bias)         X rows at stride ldx floats; K % 32 == 0; NO in {128,192,256}
+ * Wimg is the weight pre-split and pre-tiled by the caller (tiny): [K/32][2 (hi, lo)][8][NO][4] floats,
+ * Wimg[c][p][q][n][i] = part_p(W[n][32 c + 4 q + i]) with hi = W rounded to tf32, lo = W - hi.
+ * Replaces torch addmm at PyG PNAConv.update's post_nn (pna.py:71-79) and, with W^T, its data gradient. */
+int b200mp_node_linear(const float* X, int64_t N, int K, int ldx, const float* Wimg, int NO, const float* bias,
+                       float* Y, void* stream);
+/* Weight gradient of the above: part[p][k][n] = sum over the rows handled by CTA p of X[r][k] Y[r][n]
+ * (K % 128 == 0, NO in {64,128,192,256}); the caller sums the n_part partials (deterministic). */
+int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const float* Y, int ldy, int NO, int64_t N,
+                             float* part, int n_part, void* stream);
+
 /* ------------------------------------------------------------------ per-edge linear (forward)
  * One pass over E edges in segment order k = 0..E-1; H in {16,32,64,128}.
  *   z_k   = e[row(k)] W1^T + b1 + T1[idx1[k]] + T2[idx2[k]]        (T1/T2 nullable)

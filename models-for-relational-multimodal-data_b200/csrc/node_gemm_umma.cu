@@ -1,0 +1,296 @@
+// Node-level linears on the tensor cores (tcgen05, 3xTF32), fp32 in and out, ONE pass over HBM:
+//
+//   b200mp_node_linear      Y[N, NO]  = X[N, K] W^T (+ b)        PNAConv post_nn over [N, 4H] aggregates
+//                                                                (pna.py:71-79 -> PyG PNAConv.update) and
+//                                                                its data gradient (W passed transposed)
+//   b200mp_node_linear_wgrad  G[K, NO] = X[N, K]^T Y[N, NO]      its weight gradient (reduction over N)
+//
+// The library path these replace is split(x) + three TF32 GEMMs, each re-reading an [N, K]
+// operand and read-modify-writing the output: ~6K + 5NO floats of HBM traffic per node row against
+// K + NO here.
+//
+// Data kernel: one CTA = 256 threads = one tile of 128 node rows, two CTAs per SM (their phases
+// overlap each other).  K is walked in chunks of 32 columns: the X chunk [128 x 32] is loaded
+// coalesced (8 lanes per 128-byte row piece), split into tf32 hi / lo and stored as one row32 panel
+// each (umma.cuh); the matching weight chunk [NO x 32] hi / lo arrives as ONE bulk copy
+// (cp.async.bulk -> mbarrier) of a pre-formatted image (interleaved K-major tile, built once per
+// call on the host side from the tiny weight matrix).  Accumulator [128 x NO] in tensor memory.
+#include "umma_edge.cuh"
+
+namespace b200mp {
+using namespace ue;
+
+namespace ng {
+constexpr int NT2 = 256;                  // threads per CTA
+constexpr int KCH = 32;                   // K columns per chunk = one row32 panel
+using XP = RowFmt<TE, KCH>;               // 16 KB panel
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+struct NodeLinArgs {
+    int64_t N; int K; int ldx;
+    const float* X; const float* Wimg; const float* bias; float* Y;
+};
+}  // namespace ng
+using namespace ng;
+
+// Wimg: [K / 32][2 (hi, lo)][8 (16-byte k chunk)][NO][4] floats
+template <int NO>
+__global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a) {
+    constexpr int W_PART = NO * KCH;                       // floats per hi (or lo) weight chunk
+    extern __shared__ __align__(128) float smem_raw[];
+    float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;
+    float* X_hi = smem;
+    float* X_lo = X_hi + XP::FLOATS;
+    float* W_hi = X_lo + XP::FLOATS;          // weight chunk; staging tile in the epilogue (needs 32 KB: NO >= 128)
+    float* W_lo = W_hi + W_PART;
+    __shared__ uint64_t bar_w, bar_m;
+    __shared__ uint32_t tmem_base;
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int t = tid & (TE - 1), ch = tid >> 7;           // tensor-memory side: row t, 32 columns
+    const int j8 = tid & 7, g8 = tid >> 3;                 // chunk loads: 16-byte piece j8 of rows 4 g8 .. 4 g8 + 3
+    const int j = tid & 15, g = tid >> 4;                  // output rows: 16-byte chunk j of rows 8 g .. 8 g + 7
+    constexpr uint32_t NCOLS = NO <= 128 ? 128 : 256;
+    if (warp == 0) tmem_alloc(&tmem_base, NCOLS);
+    if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_m, 1); mbar_fence_init(); }
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const uint32_t tm = tmem_base;
+    const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
+    const int nchunks = a.K / KCH;
+    const int64_t ntiles = (a.N + TE - 1) / TE;
+    uint32_t phase = 0;                        // both barriers complete once per chunk
+
+    float4 xr[4];
+    auto load_chunk = [&](int64_t tile_, int c_) {
+        const int64_t r0 = tile_ * TE;
+        const int nr = (int)min64(TE, a.N - r0);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int rc = min(g8 * 4 + i, nr - 1);
+            xr[i] = ldg4(a.X + (r0 + rc) * a.ldx + c_ * KCH + j8 * 4);
+        }
+    };
+    if ((int64_t)blockIdx.x < ntiles) load_chunk(blockIdx.x, 0);
+
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int64_t row0 = tile * TE;
+        const int nrows = (int)min64(TE, a.N - row0);
+        for (int c = 0; c < nchunks; ++c, phase ^= 1) {
+            if (tid == 0) {                    // the previous chunk's MMAs (readers of W_hi / W_lo) are done
+                mbar_expect_tx(&bar_w, 2 * W_PART * 4);
+                bulk_g2s(W_hi, a.Wimg + (size_t)c * 2 * W_PART, 2 * W_PART * 4, &bar_w);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int r = g8 * 4 + i;
+                float4 h, l;
+                split4(r < nrows ? xr[i] : f4(0.f, 0.f, 0.f, 0.f), h, l);
+                const int o = XP::off(r, j8);
+                st4(X_hi + o, h);
+                st4(X_lo + o, l);
+            }
+            if (c + 1 < nchunks) load_chunk(tile, c + 1);
+            else if (tile + gridDim.x < ntiles) load_chunk(tile + gridDim.x, 0);
+            fence_async_smem();
+            fence_before();
+            __syncthreads();
+            fence_after();
+            if (tid == 0) {
+                mbar_wait(&bar_w, phase);
+                issue_data_gemm_row32<TE, NO, KCH>(tm, smem_u32(X_lo), smem_u32(W_hi), c > 0);
+                issue_data_gemm_row32<TE, NO, KCH>(tm, smem_u32(X_hi), smem_u32(W_lo), 1);
+                issue_data_gemm_row32<TE, NO, KCH>(tm, smem_u32(X_hi), smem_u32(W_hi), 1);
+                mma_commit(&bar_m);
+            }
+            mbar_wait(&bar_m, phase);
+            fence_after();
+        }
+        // ---- epilogue: 64 output columns at a time through the staging tile, coalesced rows out
+        float* stage = W_hi;
+#pragma unroll 1
+        for (int grp = 0; grp < NO / 64; ++grp) {
+            stage_from_tmem<NT2>(tm + lane_off + grp * 64 + ch * 32, stage, t, ch);
+            __syncthreads();
+            const float4 b4 = a.bias ? ldg4(a.bias + grp * 64 + j * 4) : f4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int r = g * 8 + i;
+                if (r < nrows) st4(a.Y + (row0 + r) * NO + grp * 64 + j * 4, lds4(stage + stage_off(r, j)) + b4);
+            }
+            __syncthreads();
+        }
+        fence_async_smem();                    // generic-proxy use of the weight buffer ends before the next bulk copy
+        fence_before();
+        __syncthreads();
+        fence_after();
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tm, NCOLS);
+}
+
+template <int NO>
+static int launch_node_linear(const NodeLinArgs& a, cudaStream_t st) {
+    const size_t smem = 2 * XP::BYTES + 2 * NO * KCH * 4 + 1024;
+    auto kern = node_linear_umma_kernel<NO>;
+    B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t ntiles = (a.N + TE - 1) / TE;
+    const int grid = persistent_grid((const void*)kern, smem, ntiles, NT2);
+    kern<<<grid, NT2, smem, st>>>(a);
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------ weight gradient
+// G[K, NO] = X[N, K]^T Y[N, NO]: CTA (bx, kb) accumulates rows 128 kb .. 128 kb + 127 of G over the
+// 32-row tiles bx, bx + gridDim.x, ... in tensor memory (M = 128, N = NO) and writes one partial
+// [128 x NO] at the end (summed by the caller: deterministic).  Both operands are read through the
+// MN-major views of row32 panels (umma.cuh), the reduction runs over the node rows of the tile.
+namespace ng {
+constexpr int RW = 32;                    // node rows per tile
+using WP = RowFmt<RW, 32>;                // 4 KB panel [32 rows x 32 columns]
+struct NodeWgArgs {
+    int64_t N; int ldx; int ldy;
+    const float* X; const float* Y; float* part;   // part: [gridDim.x][K][NO]
+    int K;
+};
+}  // namespace ng
+
+template <int NO>
+__global__ void __launch_bounds__(NT2, 2) node_wgrad_umma_kernel(NodeWgArgs a) {
+    constexpr int XPN = 4, YPN = NO / 32;                  // panels per tile: X part (128 columns), Y
+    extern __shared__ __align__(128) float smem_raw[];
+    float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;
+    float* X_hi = smem;
+    float* X_lo = X_hi + XPN * WP::FLOATS;
+    float* Y_hi = X_lo + XPN * WP::FLOATS;
+    float* Y_lo = Y_hi + YPN * WP::FLOATS;
+    __shared__ uint64_t bar_m;
+    __shared__ uint32_t tmem_base;
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int piece = tid & 7, row = tid >> 3;             // 16-byte piece of one 128-byte panel row
+    const int kb = blockIdx.y;
+    if (warp == 0) tmem_alloc(&tmem_base, 256);
+    if (tid == 0) { mbar_init(&bar_m, 1); mbar_fence_init(); }
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const uint32_t tm = tmem_base;
+    const int64_t ntiles = (a.N + RW - 1) / RW;
+    uint32_t it = 0;
+
+    float4 xr[XPN], yr[YPN];
+    bool ok_pf = false;
+    auto prefetch = [&](int64_t tile_) {
+        const int64_t r = tile_ * RW + row;
+        ok_pf = r < a.N;
+        const int64_t rc = ok_pf ? r : a.N - 1;
+#pragma unroll
+        for (int p = 0; p < XPN; ++p) xr[p] = ldg4(a.X + rc * a.ldx + kb * 128 + p * 32 + piece * 4);
+#pragma unroll
+        for (int p = 0; p < YPN; ++p) yr[p] = ldg4(a.Y + rc * a.ldy + p * 32 + piece * 4);
+    };
+    if ((int64_t)blockIdx.x < ntiles) prefetch(blockIdx.x);
+
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int o = WP::off(row, piece);
+        const bool ok = ok_pf;
+#pragma unroll
+        for (int p = 0; p < XPN; ++p) {
+            float4 h, l;
+            split4(ok ? xr[p] : f4(0.f, 0.f, 0.f, 0.f), h, l);
+            st4(X_hi + p * WP::FLOATS + o, h);
+            st4(X_lo + p * WP::FLOATS + o, l);
+        }
+#pragma unroll
+        for (int p = 0; p < YPN; ++p) {
+            float4 h, l;
+            split4(ok ? yr[p] : f4(0.f, 0.f, 0.f, 0.f), h, l);
+            st4(Y_hi + p * WP::FLOATS + o, h);
+            st4(Y_lo + p * WP::FLOATS + o, l);
+        }
+        if (tile + gridDim.x < ntiles) prefetch(tile + gridDim.x);
+        fence_async_smem();
+        fence_before();
+        __syncthreads();
+        fence_after();
+        if (tid == 0) {
+            issue_wgrad_gemm_row32<RW, 128, NO>(tm, smem_u32(X_lo), smem_u32(Y_hi), it > 0);
+            issue_wgrad_gemm_row32<RW, 128, NO>(tm, smem_u32(X_hi), smem_u32(Y_lo), 1);
+            issue_wgrad_gemm_row32<RW, 128, NO>(tm, smem_u32(X_hi), smem_u32(Y_hi), 1);
+            mma_commit(&bar_m);
+        }
+        mbar_wait(&bar_m, it & 1);
+        fence_after();
+    }
+    // ---- partial [128 x NO] of this CTA: thread (t, ch) = row 128 kb + t, columns 32 ch + 64 q ..
+    {
+        const int t = tid & (TE - 1), ch = tid >> 7;
+        float* out = a.part + ((int64_t)blockIdx.x * a.K + kb * 128 + t) * NO;
+        const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
+#pragma unroll 1
+        for (int c0 = ch * 16; c0 < NO; c0 += 32) {
+            float v[16];
+            if (it > 0) tmem_ld16(tm + lane_off + c0, v);
+#pragma unroll
+            for (int c = 0; c < 16; c += 4)
+                st4(out + c0 + c, it > 0 ? f4(v[c], v[c + 1], v[c + 2], v[c + 3]) : f4(0.f, 0.f, 0.f, 0.f));
+        }
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tm, 256);
+}
+
+template <int NO>
+static int launch_node_wgrad(const NodeWgArgs& a, int n_part, cudaStream_t st) {
+    const size_t smem = 2 * (4 + NO / 32) * WP::BYTES + 1024;
+    auto kern = node_wgrad_umma_kernel<NO>;
+    B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<dim3(n_part, a.K / 128), NT2, smem, st>>>(a);
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace b200mp
+
+extern "C" int b200mp_node_linear(const float* X, int64_t N, int K, int ldx, const float* Wimg, int NO, const float* bias,
+                                  float* Y, void* stream) {
+    using namespace b200mp;
+    if (N < 0 || K <= 0 || K % 32 || ldx < K || ldx % 4 || !X || !Wimg || !Y) return B200MP_EINVAL;
+    if (N == 0) return 0;
+    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y};
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (NO) {
+        case 128: return launch_node_linear<128>(a, st);
+        case 192: return launch_node_linear<192>(a, st);
+        case 256: return launch_node_linear<256>(a, st);
+    }
+    return B200MP_EINVAL;
+}
+
+extern "C" int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const float* Y, int ldy, int NO, int64_t N,
+                                        float* part, int n_part, void* stream) {
+    using namespace b200mp;
+    if (N <= 0 || K <= 0 || K % 128 || ldx < K || ldx % 4 || ldy < NO || ldy % 4 || n_part <= 0 || !X || !Y || !part)
+        return B200MP_EINVAL;
+    NodeWgArgs a{N, ldx, ldy, X, Y, part, K};
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (NO) {
+        case 64: return launch_node_wgrad<64>(a, n_part, st);
+        case 128: return launch_node_wgrad<128>(a, n_part, st);
+        case 192: return launch_node_wgrad<192>(a, n_part, st);
+        case 256: return launch_node_wgrad<256>(a, n_part, st);
+    }
+    return B200MP_EINVAL;
+}

@@ -141,8 +141,53 @@ def _mm3(a, b, ta=False, tb=False):
     return out
 
 
+def _w_image(W):
+    """[NO, K] weight -> the pre-split, pre-tiled operand image b200mp_node_linear expects:
+    [K/32][2 (hi, lo)][8][NO][4], hi = W rounded to tf32 (same rounding as the kernels), lo = W - hi."""
+    W = W.contiguous()
+    NO, K = W.shape
+    hi = ((W.view(torch.int32) + 0x1000) & -8192).view(torch.float32)
+    lo = W - hi
+    tile = lambda P: P.view(NO, K // 32, 8, 4).permute(1, 2, 0, 3)
+    return torch.stack([tile(hi), tile(lo)], dim=1).contiguous()
+
+
+def _node_kernel_ok(rows, K, NO):
+    """Y[rows, NO] = X[rows, K] W^T on the tcgen05 node kernel (node_gemm_umma.cu)."""
+    return rows >= 4096 and K % 32 == 0 and K >= 128 and NO in (128, 192, 256)
+
+
+def _node_linear(x, W, b):
+    N, K = x.shape
+    NO = W.shape[0]
+    y = torch.empty((N, NO), dtype=torch.float32, device=x.device)
+    img = _w_image(W)
+    with torch.cuda.device(x.device), _track("node_linear"):
+        L.check(L.lib().b200mp_node_linear(L.ptr(x), N, K, K, L.ptr(img), NO, L.ptr(b), L.ptr(y), L.stream()),
+                "b200mp_node_linear")
+    return y
+
+
+def _node_wgrad_ok(rows, K, NO):
+    return rows >= 4096 and K % 128 == 0 and NO in (64, 128, 192, 256)
+
+
+def _node_wgrad(x, y):
+    """x^T y  ([K, NO]) over the N rows, per-CTA partials summed here."""
+    N, K = x.shape
+    NO = y.shape[1]
+    npart = torch.cuda.get_device_properties(x.device).multi_processor_count
+    part = torch.empty((npart, K, NO), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device), _track("node_linear_wgrad"):
+        L.check(L.lib().b200mp_node_linear_wgrad(L.ptr(x), K, K, L.ptr(y), NO, NO, N, L.ptr(part), npart, L.stream()),
+                "b200mp_node_linear_wgrad")
+    return part.sum(0)
+
+
 class _Linear3x(torch.autograd.Function):
-    """y = x W^T (+ b) for N-row node tensors; forward and both backward GEMMs as 3xTF32."""
+    """y = x W^T (+ b) for N-row node tensors with fp32 accuracy on the tensor cores: the wide
+    post linear runs on the hand-written tcgen05 kernels (one pass over HBM per product); shapes
+    they do not cover fall back to three TF32 library GEMMs, narrow ones to plain fp32."""
 
     @staticmethod
     def forward(ctx, x, W, b):
@@ -150,6 +195,8 @@ class _Linear3x(torch.autograd.Function):
         L.require_cuda(x, W)
         ctx.save_for_backward(x, W)
         ctx.has_bias = b is not None
+        if _node_kernel_ok(x.shape[0], W.shape[1], W.shape[0]):
+            return _node_linear(x, W, None if b is None else _f32c(b))
         if not _use_mm3(x, W):
             return torch.nn.functional.linear(x, W, b)
         y = _mm3(_split_tf32(x), _split_tf32(W), tb=True)
@@ -161,12 +208,28 @@ class _Linear3x(torch.autograd.Function):
     def backward(ctx, g):
         x, W = ctx.saved_tensors
         g = _f32c(g)
+        N, (NO, K) = x.shape[0], W.shape
         gb = g.sum(0) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
-        if not _use_mm3(x, W):
-            return (g @ W if ctx.needs_input_grad[0] else None), (g.t() @ x if ctx.needs_input_grad[1] else None), gb
-        gs = _split_tf32(g)
-        gx = _mm3(gs, _split_tf32(W)) if ctx.needs_input_grad[0] else None
-        gW = _mm3(gs, _split_tf32(x), ta=True) if ctx.needs_input_grad[1] else None
+        gx = gW = None
+        mm3 = _use_mm3(x, W)
+        gs = None
+        if ctx.needs_input_grad[0]:
+            if _node_kernel_ok(N, NO, K):
+                gx = _node_linear(g, W.t(), None)
+            elif mm3:
+                gs = _split_tf32(g)
+                gx = _mm3(gs, _split_tf32(W))
+            else:
+                gx = g @ W
+        if ctx.needs_input_grad[1]:
+            if _node_wgrad_ok(N, K, NO):
+                gW = _node_wgrad(x, g).t()
+            elif _node_wgrad_ok(N, NO, K):
+                gW = _node_wgrad(g, x)
+            elif mm3:
+                gW = _mm3(gs if gs is not None else _split_tf32(g), _split_tf32(x), ta=True)
+            else:
+                gW = g.t() @ x
         return gx, gW, gb
 
 

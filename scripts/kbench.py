@@ -58,6 +58,7 @@ def main():
     npart = L.n_part(E, H)
     gW1, gW2 = torch.empty(npart, H, H, device=dev), torch.empty(npart, H, H, device=dev)
     gb1, gb2 = torch.empty(npart, H, device=dev), torch.empty(npart, H, device=dev)
+    X4, Z3, Wz = rn(n, 4 * H), rn(n, 3 * H), rn(3 * H, 4 * H) / 16
     lib, p, s = L.lib(), L.ptr, L.stream
     res = {}
 
@@ -91,6 +92,10 @@ def main():
         "msg_bwd_gine(gx)": lambda: msgb(1, T1, gP),
         "seg_reduce_pna": segr,
         "permute_rows": lambda: BF._permute(ea, seg.perm, False),
+        "node_linear(256->192)": lambda: BF._node_linear(X4, Wz, None),
+        "node_linear(192->256)": lambda: BF._node_linear(Z3, Wz.t(), None),
+        "node_wgrad(256x192)": lambda: BF._node_wgrad(X4, Z3),
+        "mm3 lib (256->192)": lambda: BF._mm3(BF._split_tf32(X4), BF._split_tf32(Wz), tb=True),
     }
     for name, fn in cases.items():
         if args.only and args.only not in name:

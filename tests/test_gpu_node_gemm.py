@@ -1,0 +1,53 @@
+"""-m gpu: the tcgen05 node-level linear kernels (csrc/node_gemm_umma.cu) against fp64: forward,
+data gradient (transposed weight) and weight gradient, at ragged row counts and every supported
+width; tolerance = fp32 round-off level (3xTF32), far below the 1e-5 the path needs."""
+import pytest
+import torch
+
+from b200mp import functional as BF
+from tests.util import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("N,K,NO", [(4096, 256, 192), (5000, 192, 256), (4097, 128, 128), (9999, 256, 256)])
+def test_node_linear(N, K, NO):
+    g = torch.Generator(device="cuda").manual_seed(N + K)
+    X = torch.randn(N, K, device="cuda", generator=g) * torch.logspace(-2, 2, K, device="cuda")
+    W = torch.randn(NO, K, device="cuda", generator=g)
+    b = torch.randn(NO, device="cuda", generator=g)
+    Y = BF._node_linear(X, W, b)
+    T = X.double() @ W.double().t() + b.double()
+    err, err32 = rel_err(Y, T), rel_err(torch.nn.functional.linear(X, W, b), T)
+    print(f"node_linear N={N} K={K} NO={NO}: rel err {err:.2e} (torch fp32 {err32:.2e})")
+    assert err < 2e-6
+
+
+@pytest.mark.parametrize("N,K,NO", [(4096, 256, 192), (5001, 128, 64), (7777, 256, 256)])
+def test_node_wgrad(N, K, NO):
+    g = torch.Generator(device="cuda").manual_seed(N + NO)
+    X = torch.randn(N, K, device="cuda", generator=g)
+    Y = torch.randn(N, NO, device="cuda", generator=g) * torch.logspace(-1, 1, NO, device="cuda")
+    G = BF._node_wgrad(X, Y)
+    T = X.double().t() @ Y.double()
+    err, err32 = rel_err(G, T), rel_err(X.t() @ Y, T)
+    print(f"node_wgrad N={N} K={K} NO={NO}: rel err {err:.2e} (torch fp32 {err32:.2e})")
+    assert err < 2e-6
+
+
+def test_linear3x_autograd_matches_fp64():
+    g = torch.Generator(device="cuda").manual_seed(5)
+    N, K, NO = 6000, 256, 192
+    x = torch.randn(N, K, device="cuda", generator=g, requires_grad=True)
+    W = (torch.randn(NO, K, device="cuda", generator=g) / 16).requires_grad_(True)
+    b = torch.randn(NO, device="cuda", generator=g, requires_grad=True)
+    gy = torch.randn(N, NO, device="cuda", generator=g)
+    y = BF.linear3x(x, W, b)
+    y.backward(gy)
+    xd, Wd, bd = (t.detach().double().requires_grad_(True) for t in (x, W, b))
+    yd = torch.nn.functional.linear(xd, Wd, bd)
+    yd.backward(gy.double())
+    for name, a, t in (("y", y, yd), ("gx", x.grad, xd.grad), ("gW", W.grad, Wd.grad), ("gb", b.grad, bd.grad)):
+        err = rel_err(a, t)
+        print(f"linear3x {name}: rel err {err:.2e}")
+        assert err < 1e-5
