@@ -94,17 +94,20 @@ int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const float* Y, int
  *   mode 0: out1[k] = z_k                      PNAConv message with hoisted node terms
  *                                              (pna.py:71-74 -> PyG PNAConv.message)
  *   mode 1: out1[k] = relu(z_k)                GINEConv message (gine.py:66-70)
- *   mode 2: out1[k] = h_k = relu(z_k);  out2[row(k)] = alpha e[row(k)] + beta (h_k W2^T + b2)
+ *   mode 2: out1[k] = h_k = relu(z_k);  out2[orow(k)] = alpha e[row(k)] + beta (h_k W2^T + b2)
  *                                              edge update (gine.py:88-89, pna.py:97-99,
  *                                              models/fused.py:254)
- * row(k) = eid ? eid[k] : k  (eid maps segment order -> e-storage row; null = identity). */
+ * row(k) = eid ? eid[k] : k  (eid maps segment order -> e-storage row; null = identity);
+ * orow(k) = out_eid ? out_eid[k] : k.  The two maps let the first layer read the caller's edge
+ * order and the last one write it, with no separate permutation pass
+ * (the backward row maps g_eid / e_eid / g_acc exist on the tensor-core path, H = 64, only). */
 int b200mp_edge_linear_fwd(int mode, int H, int64_t E,
                            const float* e, const int32_t* eid,
                            const float* W1, const float* b1,
                            const float* T1, const int32_t* idx1,
                            const float* T2, const int32_t* idx2,
                            const float* W2, const float* b2, float alpha, float beta,
-                           float* out1, float* out2, void* stream);
+                           float* out1, float* out2, const int32_t* out_eid, void* stream);
 
 /* ------------------------------------------------------------------ segmented reductions
  * Replaces PyG DegreeScalerAggregation's scatter kernels (mean/min/max/std; App. A.2 of
@@ -145,15 +148,18 @@ int b200mp_pna_coef(int H, int64_t N, const int64_t* ptr, const float* g_agg, co
  *   kind 1 (GINE): G_k = node_in[d] [m_k > 0],  node_in = grad_agg[N,H]
  *   d = seg[k].  Then
  *     gT1[nbr[k]] += G_k                  (vector atomics)
- *     g_e[row(k)] (+)= G_k W              (accumulate != 0 adds to the existing value)
+ *     g_e[row(k)] (+)= G_k W (+ g_acc[k])  (accumulate != 0 adds to the existing value; g_acc:
+ *                                          optional [E,H] in segment order, H = 64 only -- the
+ *                                          gradient the same layer's edge update left for e)
  *     gW_part[cta]  = sum_k G_k^T e_k ,  gb_part[cta] = sum_k G_k     (per-CTA partials) */
 int b200mp_message_bwd(int kind, int H, int64_t E,
                        const float* m, const float* e, const int32_t* eid,
                        const float* node_in, const int32_t* seg, const int32_t* nbr,
                        const float* W, float* g_e, int accumulate, float* gT1,
-                       float* gW_part, float* gb_part, int n_part, void* stream);
+                       float* gW_part, float* gb_part, int n_part, const float* g_acc, void* stream);
 
-/* Edge-update backward (mode 2).  g_out = dL/d out2 [E,H] (e-storage order = segment order).
+/* Edge-update backward (mode 2).  g_out = dL/d out2 [E,H]; row k of the segment order is read at
+ * g_eid ? g_eid[k] : k, e at e_eid ? e_eid[k] : k (maps: H = 64 only); h and g_e are in segment order.
  *   g_e = alpha g_out + Gh W1 ,  Gh = (beta g_out W2) * [h>0]
  *   gP[src[k]] += Gh_k ,  gQ[dst[k]] += Gh_k  (run-length reduced over equal consecutive dst)
  *   partials of grad W1, b1, W2, b2 per CTA. */
@@ -163,7 +169,7 @@ int b200mp_edge_update_bwd(int H, int64_t E,
                            const float* W1, const float* W2, float alpha, float beta,
                            float* g_e, float* gP, float* gQ,
                            float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part,
-                           int n_part, void* stream);
+                           int n_part, const int32_t* g_eid, const int32_t* e_eid, void* stream);
 
 /* ------------------------------------------------------------------ tensor-core self test
  * One-CTA check of the tcgen05 building blocks (csrc/umma.cuh) used by the per-edge kernels:

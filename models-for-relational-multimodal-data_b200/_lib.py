@@ -30,9 +30,9 @@ _SIGS = {
     "b200mp_relabel": [_p, _l, _p, _p, _p, _p, _sz, _p],
     "b200mp_gather_rows": [_p, _p, _p, _l, _i, _p],
     "b200mp_scatter_rows": [_p, _p, _p, _l, _i, _p],
-    "b200mp_edge_linear_fwd": [_i, _i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p],
+    "b200mp_edge_linear_fwd": [_i, _i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p],
     "b200mp_segment_reduce_fwd": [_i, _i, _l, _p, _p, _p, _p, _l, _l, _l, _p, _p, _l, _p, _p, _p, _p],
-    "b200mp_message_bwd": [_i, _i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p],
+    "b200mp_message_bwd": [_i, _i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p, _p],
     "b200mp_pna_scale_fwd": [_i, _l, _p, _p, _p, _i, _p, _p, _p, _p, _p],
     "b200mp_pna_scale_bwd": [_i, _l, _p, _p, _i, _p, _p, _p, _p, _p],
     "b200mp_pna_coef": [_i, _l, _p, _p, _p, _p, _p, _p, _p],
@@ -41,7 +41,7 @@ _SIGS = {
     "b200mp_node_linear_wgrad": [_p, _i, _i, _p, _i, _i, _l, _p, _i, _p],
     "b200mp_umma_selftest": [_i, _p, _p, _p, _p],
     "b200mp_umma_probe": [_p, _i, _p, _i, C.c_uint64, C.c_uint64, _i, _i, _i, C.c_uint32, _p, _p],
-    "b200mp_edge_update_bwd": [_i, _l, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p, _i, _p],
+    "b200mp_edge_update_bwd": [_i, _l, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p],
 }
 
 

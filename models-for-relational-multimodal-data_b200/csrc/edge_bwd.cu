@@ -242,10 +242,11 @@ static int launch_upd_bwd(const UpdBwdArgs& a, int n_part, cudaStream_t st) {
 
 int launch_msg_bwd_umma(int kind, int64_t E, const float* m, const float* e, const int32_t* eid, const float* node_in,
                         const int32_t* seg, const int32_t* nbr, const float* W, float* g_e, int accumulate, float* gT1,
-                        float* gW_part, float* gb_part, int n_part, cudaStream_t st);
+                        float* gW_part, float* gb_part, int n_part, const float* g_acc, cudaStream_t st);
 int launch_upd_bwd_umma(int64_t E, const float* g_out, const float* h, const float* e, const int32_t* src, const int32_t* dst,
                         const float* W1, const float* W2, float alpha, float beta, float* g_e, float* gP, float* gQ,
-                        float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part, cudaStream_t st);
+                        float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part,
+                        const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st);
 
 }  // namespace b200mp
 
@@ -253,7 +254,7 @@ extern "C" int b200mp_message_bwd(int kind, int H, int64_t E,
                                   const float* m, const float* e, const int32_t* eid,
                                   const float* node_in, const int32_t* seg, const int32_t* nbr,
                                   const float* W, float* g_e, int accumulate, float* gT1,
-                                  float* gW_part, float* gb_part, int n_part, void* stream) {
+                                  float* gW_part, float* gb_part, int n_part, const float* g_acc, void* stream) {
     using namespace b200mp;
     if (E < 0 || n_part <= 0 || !W || !gW_part || !gb_part) return B200MP_EINVAL;
     if (E > 0 && (!g_e || !m || !e || !node_in || !seg || (gT1 && !nbr))) return B200MP_EINVAL;
@@ -262,7 +263,8 @@ extern "C" int b200mp_message_bwd(int kind, int H, int64_t E,
 #define B200MP_MB(HH) return kind == 0 ? launch_msg_bwd<HH, 0>(a, n_part, st) : launch_msg_bwd<HH, 1>(a, n_part, st)
     if (kind != 0 && kind != 1) return B200MP_EINVAL;
     if (H == 64 && use_tensor_cores())
-        return launch_msg_bwd_umma(kind, E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, n_part, st);
+        return launch_msg_bwd_umma(kind, E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, n_part, g_acc, st);
+    if (g_acc) return B200MP_EINVAL;                             // tensor-core path only
     switch (H) { case 16: B200MP_MB(16); case 32: B200MP_MB(32); case 64: B200MP_MB(64); case 128: B200MP_MB(128); }
 #undef B200MP_MB
     return B200MP_EINVAL;
@@ -274,7 +276,7 @@ extern "C" int b200mp_edge_update_bwd(int H, int64_t E,
                                       const float* W1, const float* W2, float alpha, float beta,
                                       float* g_e, float* gP, float* gQ,
                                       float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part,
-                                      int n_part, void* stream) {
+                                      int n_part, const int32_t* g_eid, const int32_t* e_eid, void* stream) {
     using namespace b200mp;
     if (E < 0 || n_part <= 0 || !W1 || !W2 || !gW1_part || !gb1_part || !gW2_part || !gb2_part) return B200MP_EINVAL;
     if (E > 0 && (!g_e || !g_out || !h || !e || !dst || (gP && !src))) return B200MP_EINVAL;
@@ -282,7 +284,8 @@ extern "C" int b200mp_edge_update_bwd(int H, int64_t E,
     cudaStream_t st = (cudaStream_t)stream;
     if (H == 64 && use_tensor_cores())
         return launch_upd_bwd_umma(E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part,
-                                   gb2_part, n_part, st);
+                                   gb2_part, n_part, g_eid, e_eid, st);
+    if (g_eid || e_eid) return B200MP_EINVAL;                    // tensor-core path only
     switch (H) {
         case 16: return launch_upd_bwd<16>(a, n_part, st);
         case 32: return launch_upd_bwd<32>(a, n_part, st);

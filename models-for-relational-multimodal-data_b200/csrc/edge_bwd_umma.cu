@@ -22,6 +22,7 @@ struct UpdBwdUArgs {
     const float* W1; const float* W2; float alpha, beta;
     float* g_e; float* gP; float* gQ;
     float* gW1_part; float* gb1_part; float* gW2_part; float* gb2_part;
+    const int32_t* g_eid; const int32_t* e_eid;       // storage rows of g_out / e for segment position k (null = k)
 };
 
 constexpr int NTB = 512;                  // threads per CTA of the backward kernels (one CTA per SM)
@@ -119,7 +120,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
     const int32_t* idx_src = ch == 0 ? a.src : ch == 1 ? a.dst : nullptr;
     if ((int64_t)blockIdx.x < ntiles) {
         nrows_pf = (int)min64(TE, a.E - (int64_t)blockIdx.x * TE);
-        load_rows(Rg, a.g_out, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
+        load_rows(Rg, a.g_out, a.g_eid, (int64_t)blockIdx.x * TE, nrows_pf, tid);
         load_rows(Rh, a.h, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
         if (idx_src) idx_pf = __ldg(idx_src + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
     }
@@ -142,7 +143,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
             gemm3_wgrad(T_GW2, G_hi, G_lo, H_hi, H_lo, it > 0);
             mma_commit(&sync.bar[0]);
         }
-        load_rows(Re, a.e, nullptr, row0, nrows, tid);                // e tile in flight during the MMAs
+        load_rows(Re, a.e, a.e_eid, row0, nrows, tid);                // e tile in flight during the MMAs
         int srow[NP], drow[NP];
 #pragma unroll
         for (int i = 0; i < NP; ++i) { srow[i] = sidx[0][g * NP + i]; drow[i] = sidx[1][g * NP + i]; }
@@ -190,7 +191,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
         if (tile + gridDim.x < ntiles) {                 // next tile's h in flight (g follows once this tile's g is used)
             nrows_next = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
             load_rows(Rh, a.h, nullptr, (tile + gridDim.x) * TE, nrows_next, tid);
-            load_rows(Re, a.g_out, nullptr, (tile + gridDim.x) * TE, nrows_next, tid);
+            load_rows(Re, a.g_out, a.g_eid, (tile + gridDim.x) * TE, nrows_next, tid);
             if (idx_src) idx_pf = __ldg(idx_src + (tile + gridDim.x) * TE + min(t, nrows_next - 1));
         }
         mbar_wait(&sync.bar[1], par);
@@ -225,8 +226,9 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
 
 int launch_upd_bwd_umma(int64_t E, const float* g_out, const float* h, const float* e, const int32_t* src, const int32_t* dst,
                         const float* W1, const float* W2, float alpha, float beta, float* g_e, float* gP, float* gQ,
-                        float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part, cudaStream_t st) {
-    UpdBwdUArgs a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part};
+                        float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part,
+                        const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st) {
+    UpdBwdUArgs a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, g_eid, e_eid};
     const size_t smem = 4 * RT::BYTES + 4 * WT::BYTES + 1024;
     B200MP_CUDA(cudaFuncSetAttribute(edge_update_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     edge_update_bwd_umma_kernel<<<n_part, NTB, smem, st>>>(a);
@@ -244,6 +246,7 @@ struct MsgBwdUArgs {
     const float* node_in; const int32_t* seg; const int32_t* nbr;
     const float* W; float* g_e; int accumulate; float* gT1;
     float* gW_part; float* gb_part;
+    const float* g_acc;                               // optional [E,H] in segment order added to g_e
 };
 
 // PNA per-edge gradient from the saved message and the destination's coefficient rows
@@ -363,10 +366,17 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
             const int r = g * NP + i;
             orow[i] = (a.eid && r < nrows) ? (int64_t)__ldg(a.eid + row0 + r) : row0 + r;
         }
+#pragma unroll
+        for (int i = 0; i < NP; ++i) prev[i] = f4(0.f, 0.f, 0.f, 0.f);
         if (a.accumulate) {
 #pragma unroll
             for (int i = 0; i < NP; ++i)
-                prev[i] = (g * NP + i < nrows) ? *reinterpret_cast<const float4*>(a.g_e + orow[i] * HH + j * 4) : f4(0.f, 0.f, 0.f, 0.f);
+                if (g * NP + i < nrows) prev[i] = *reinterpret_cast<const float4*>(a.g_e + orow[i] * HH + j * 4);
+        }
+        if (a.g_acc) {
+#pragma unroll
+            for (int i = 0; i < NP; ++i)
+                if (g * NP + i < nrows) prev[i] = prev[i] + ldg4(a.g_acc + (row0 + g * NP + i) * HH + j * 4);
         }
         if (tile + gridDim.x < ntiles) prefetch(tile + gridDim.x);    // next tile's m, e and ids in flight
         mbar_wait(&sync.bar[0], it & 1);
@@ -379,7 +389,7 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
         for (int i = 0; i < NP; ++i) {
             const int r = g * NP + i;
             float4 v = lds4(stage + stage_off(r, j));
-            if (a.accumulate) v = v + prev[i];
+            v = v + prev[i];
             if (r < nrows) st4(a.g_e + orow[i] * HH + j * 4, v);
         }
         fence_before();
@@ -396,8 +406,8 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
 
 int launch_msg_bwd_umma(int kind, int64_t E, const float* m, const float* e, const int32_t* eid, const float* node_in,
                         const int32_t* seg, const int32_t* nbr, const float* W, float* g_e, int accumulate, float* gT1,
-                        float* gW_part, float* gb_part, int n_part, cudaStream_t st) {
-    MsgBwdUArgs a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part};
+                        float* gW_part, float* gb_part, int n_part, const float* g_acc, cudaStream_t st) {
+    MsgBwdUArgs a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, g_acc};
     const size_t smem = 4 * RT::BYTES + 2 * WT::BYTES + 1024;
     auto kern = kind == 0 ? message_bwd_umma_kernel<0> : message_bwd_umma_kernel<1>;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -19,7 +19,7 @@ struct EdgeFwdArgs {
     const float* T2; const int32_t* idx2;
     const float* W2; const float* b2;
     float alpha, beta;
-    float* out1; float* out2;
+    float* out1; float* out2; const int32_t* out_eid;
 };
 
 template <int H, int MODE>
@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(NT) edge_linear_fwd_kernel(EdgeFwdArgs a) {
                 const int r = ty * 4 + i;
                 if (r < nrows) {
                     const int64_t k = row0 + r;
-                    const int64_t row = a.eid ? (int64_t)__ldg(a.eid + k) : k;
+                    const int64_t row = a.out_eid ? (int64_t)__ldg(a.out_eid + k) : k;
                     float4 u = f4(acc2[i][0], acc2[i][1], acc2[i][2], acc2[i][3]) + bias2;
                     float4 x = lds4(Xs + r * T::LDX + c);
                     st4(a.out2 + row * H + c, a.alpha * x + a.beta * u);
@@ -117,7 +117,8 @@ static int dispatch_mode(int mode, const EdgeFwdArgs& a, cudaStream_t st) {
 
 int launch_edge_fwd_umma(int mode, int64_t E, const float* e, const int32_t* eid, const float* W1, const float* b1,
                          const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
-                         const float* W2, const float* b2, float alpha, float beta, float* out1, float* out2, cudaStream_t st);
+                         const float* W2, const float* b2, float alpha, float beta, float* out1, float* out2,
+                         const int32_t* out_eid, cudaStream_t st);
 
 }  // namespace b200mp
 
@@ -127,17 +128,17 @@ extern "C" int b200mp_edge_linear_fwd(int mode, int H, int64_t E,
                                       const float* T1, const int32_t* idx1,
                                       const float* T2, const int32_t* idx2,
                                       const float* W2, const float* b2, float alpha, float beta,
-                                      float* out1, float* out2, void* stream) {
+                                      float* out1, float* out2, const int32_t* out_eid, void* stream) {
     using namespace b200mp;
     if (E < 0 || mode < 0 || mode > 2) return B200MP_EINVAL;
     if (E == 0) return 0;
     if (!W1 || !b1 || !out1 || !e) return B200MP_EINVAL;
     if ((T1 && !idx1) || (T2 && !idx2)) return B200MP_EINVAL;
     if (mode == 2 && (!W2 || !b2 || !out2)) return B200MP_EINVAL;
-    EdgeFwdArgs a{E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2};
+    EdgeFwdArgs a{E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2, out_eid};
     cudaStream_t st = (cudaStream_t)stream;
     if (H == 64 && use_tensor_cores())
-        return launch_edge_fwd_umma(mode, E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2, st);
+        return launch_edge_fwd_umma(mode, E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2, out_eid, st);
     switch (H) {
         case 16: return dispatch_mode<16>(mode, a, st);
         case 32: return dispatch_mode<32>(mode, a, st);

@@ -19,7 +19,7 @@ struct EdgeFwdUArgs {
     const float* T2; const int32_t* idx2;
     const float* W2; const float* b2;
     float alpha, beta;
-    float* out1; float* out2;
+    float* out1; float* out2; const int32_t* out_eid;
 };
 
 // threads per CTA: the message modes fit two CTAs of 256 per SM; the update's tiles fill shared
@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
 #pragma unroll
             for (int i = 0; i < NP; ++i) {
                 const int r = g * NP + i;
-                orow[i] = (a.eid && r < nrows) ? (int64_t)__ldg(a.eid + row0 + r) : row0 + r;
+                orow[i] = (a.out_eid && r < nrows) ? (int64_t)__ldg(a.out_eid + row0 + r) : row0 + r;
             }
             mbar_wait(&sync.bar[1], par);
             fence_after();
@@ -174,8 +174,9 @@ static int launch_fwd_umma_mode(const EdgeFwdUArgs& a, cudaStream_t st) {
 
 int launch_edge_fwd_umma(int mode, int64_t E, const float* e, const int32_t* eid, const float* W1, const float* b1,
                          const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
-                         const float* W2, const float* b2, float alpha, float beta, float* out1, float* out2, cudaStream_t st) {
-    EdgeFwdUArgs a{E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2};
+                         const float* W2, const float* b2, float alpha, float beta, float* out1, float* out2,
+                         const int32_t* out_eid, cudaStream_t st) {
+    EdgeFwdUArgs a{E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2, out_eid};
     switch (mode) {
         case 0: return launch_fwd_umma_mode<0>(a, st);
         case 1: return launch_fwd_umma_mode<1>(a, st);

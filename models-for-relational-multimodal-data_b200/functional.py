@@ -97,6 +97,18 @@ def _permute(x, idx, scatter):
     return out
 
 
+def row_maps_available() -> bool:
+    """The eid / out_eid row maps of the edge update live in the tensor-core kernels (H = 64);
+    B200MP_SIMT=1 (A/B runs on the SIMT kernels) switches them off."""
+    import os
+    return os.environ.get("B200MP_SIMT", "0") != "1"
+
+
+def scatter_rows_i32(x, idx32):
+    """out[idx32[i]] = x[i] (no autograd; rare fallback of the row-map paths)."""
+    return _permute(x, idx32.long(), True)
+
+
 def gather_rows(x: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     """out[i] = x[idx[i]] for a permutation idx (backward = scatter, no atomics)."""
     return _PermuteRows.apply(x, idx, False)
@@ -240,14 +252,15 @@ def linear3x(x, W, b=None):
 
 
 # ----------------------------------------------------------------------------- raw launches
-def _edge_linear_fwd(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2=None, b2=None, alpha=0.0, beta=0.0):
+def _edge_linear_fwd(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2=None, b2=None, alpha=0.0, beta=0.0, out_eid=None):
     E, H = e.shape
     out1 = torch.empty((E, H), dtype=torch.float32, device=e.device)
     out2 = torch.empty((E, H), dtype=torch.float32, device=e.device) if mode == 2 else None
     with torch.cuda.device(e.device), _track(("pna_message_fwd", "gine_message_fwd", "edge_update_fwd")[mode]):
         L.check(L.lib().b200mp_edge_linear_fwd(mode, H, E, L.ptr(e), L.ptr(eid), L.ptr(W1), L.ptr(b1),
                                                L.ptr(T1), L.ptr(idx1), L.ptr(T2), L.ptr(idx2),
-                                               L.ptr(W2), L.ptr(b2), alpha, beta, L.ptr(out1), L.ptr(out2), L.stream()),
+                                               L.ptr(W2), L.ptr(b2), alpha, beta, L.ptr(out1), L.ptr(out2), L.ptr(out_eid),
+                                               L.stream()),
                 "b200mp_edge_linear_fwd")
     return out1, out2
 
@@ -283,10 +296,17 @@ class EdgeGradSink:
         return b
 
 
-def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N, g_e=None):
+def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N, g_e=None, eid=None):
+    """g_e: optional [E,H] gradient (segment order) the result is added to.  eid: storage row of e
+    (and of the returned gradient) for segment position k (default seg.eid32)."""
     E, H = m.shape
     dev = m.device
-    accumulate = 0 if g_e is None else 1
+    eid = seg.eid32 if eid is None else eid
+    accumulate, g_acc = 0, None
+    if g_e is not None and eid is not None:      # add in segment order, write in storage order
+        g_acc, g_e = g_e, None
+    elif g_e is not None:
+        accumulate = 1
     if g_e is None:
         g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
     gT1 = torch.zeros((N, H), dtype=torch.float32, device=dev) if need_T1 else None
@@ -294,14 +314,15 @@ def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N, g_e=None
     gW = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
     gb = torch.empty((npart, H), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev), _track("pna_message_bwd" if kind == 0 else "gine_message_bwd"):
-        L.check(L.lib().b200mp_message_bwd(kind, H, E, L.ptr(m), L.ptr(e), L.ptr(seg.eid32), L.ptr(node_in),
+        L.check(L.lib().b200mp_message_bwd(kind, H, E, L.ptr(m), L.ptr(e), L.ptr(eid), L.ptr(node_in),
                                            L.ptr(seg.seg32), L.ptr(seg.nbr32), L.ptr(W), L.ptr(g_e), accumulate, L.ptr(gT1),
-                                           L.ptr(gW), L.ptr(gb), npart, L.stream()),
+                                           L.ptr(gW), L.ptr(gb), npart, L.ptr(g_acc), L.stream()),
                 "b200mp_message_bwd")
     return g_e, gT1, gW.sum(0), gb.sum(0)
 
 
-def _edge_update_bwd(st: EdgeStructure, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q, nP=None, nQ=None):
+def _edge_update_bwd(st: EdgeStructure, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q, nP=None, nQ=None,
+                     g_eid=None, e_eid=None):
     E, H = e.shape
     dev = e.device
     g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
@@ -316,7 +337,7 @@ def _edge_update_bwd(st: EdgeStructure, g_out, h, e, W1, W2, alpha, beta, need_P
         L.check(L.lib().b200mp_edge_update_bwd(H, E, L.ptr(g_out), L.ptr(h), L.ptr(e), L.ptr(st.src32),
                                                L.ptr(st.dst32), L.ptr(W1), L.ptr(W2), alpha, beta,
                                                L.ptr(g_e), L.ptr(gP), L.ptr(gQ), L.ptr(gW1), L.ptr(gb1),
-                                               L.ptr(gW2), L.ptr(gb2), npart, L.stream()),
+                                               L.ptr(gW2), L.ptr(gb2), npart, L.ptr(g_eid), L.ptr(e_eid), L.stream()),
                 "b200mp_edge_update_bwd")
     return g_e, gP, gQ, gW1.sum(0), gb1.sum(0), gW2.sum(0), gb2.sum(0)
 
@@ -384,13 +405,13 @@ class _PNAAggregate(torch.autograd.Function):
     """agg4[N,4H] = [mean|min|max|std] over incoming m_k = A[seg_k] + B[nbr_k] + e_k W^T + b."""
 
     @staticmethod
-    def forward(ctx, A, B, e, W, b, seg: SegmentIndex, sink=None):
+    def forward(ctx, A, B, e, W, b, seg: SegmentIndex, sink=None, e_eid=None):
         A, B, e, W, b = map(_f32c, (A, B, e, W, b))
         L.require_cuda(A, B, e, W, b)
         H = _H(e)
-        m, _ = _edge_linear_fwd(0, e, seg.eid32, W, b, B, seg.nbr32, A, seg.seg32)
+        m, _ = _edge_linear_fwd(0, e, seg.eid32 if e_eid is None else e_eid, W, b, B, seg.nbr32, A, seg.seg32)
         agg, tie = _segment_reduce(0, seg, m, H)
-        ctx.seg, ctx.nB, ctx.sink = seg, B.shape[0], sink
+        ctx.seg, ctx.nB, ctx.sink, ctx.e_eid = seg, B.shape[0], sink, e_eid
         ctx.save_for_backward(m, e, W, agg, tie)
         ctx.mark_non_differentiable(tie)
         return agg, tie
@@ -403,13 +424,15 @@ class _PNAAggregate(torch.autograd.Function):
         coef, gA = _pna_coef(seg.ptr, g_agg, agg, tie, ctx.needs_input_grad[0])
         need_B = ctx.needs_input_grad[1]
         acc = ctx.sink.take() if (ctx.sink is not None and seg.eid32 is None) else None
-        g_e, gB, gW, gb = _message_bwd(0, seg, m, e, coef, W, need_B, ctx.nB, acc)
-        return gA, gB, g_e, gW, gb, None, None
+        g_e, gB, gW, gb = _message_bwd(0, seg, m, e, coef, W, need_B, ctx.nB, acc, ctx.e_eid)
+        return gA, gB, g_e, gW, gb, None, None, None
 
 
-def pna_aggregate(A, B, e, W, b, seg: SegmentIndex, sink=None):
-    """Returns (agg4 [N,4H] in the order mean,min,max,std, tie counts [N,2H])."""
-    return _PNAAggregate.apply(A, B, e, W, b, seg, sink)
+def pna_aggregate(A, B, e, W, b, seg: SegmentIndex, sink=None, e_eid=None):
+    """Returns (agg4 [N,4H] in the order mean,min,max,std, tie counts [N,2H]).  e_eid: int32 map
+    segment position -> row of e when e is NOT stored in segment order (first layer: the caller's
+    edge order); the gradient of e comes back in the same order."""
+    return _PNAAggregate.apply(A, B, e, W, b, seg, sink, e_eid)
 
 
 # ----------------------------------------------------------------------------- GINE aggregation
@@ -417,13 +440,13 @@ class _GINEAggregate(torch.autograd.Function):
     """agg[N,H] = sum over incoming relu(x[nbr_k] + e_k W^T + b)."""
 
     @staticmethod
-    def forward(ctx, x, e, W, b, seg: SegmentIndex, sink=None):
+    def forward(ctx, x, e, W, b, seg: SegmentIndex, sink=None, e_eid=None):
         x, e, W, b = map(_f32c, (x, e, W, b))
         L.require_cuda(x, e, W, b)
         H = _H(e)
-        m, _ = _edge_linear_fwd(1, e, seg.eid32, W, b, x, seg.nbr32, None, None)
+        m, _ = _edge_linear_fwd(1, e, seg.eid32 if e_eid is None else e_eid, W, b, x, seg.nbr32, None, None)
         agg, _ = _segment_reduce(1, seg, m, H)
-        ctx.seg, ctx.nx, ctx.sink = seg, x.shape[0], sink
+        ctx.seg, ctx.nx, ctx.sink, ctx.e_eid = seg, x.shape[0], sink, e_eid
         ctx.save_for_backward(m, e, W)
         return agg
 
@@ -432,12 +455,12 @@ class _GINEAggregate(torch.autograd.Function):
         m, e, W = ctx.saved_tensors
         seg: SegmentIndex = ctx.seg
         acc = ctx.sink.take() if (ctx.sink is not None and seg.eid32 is None) else None
-        g_e, gx, gW, gb = _message_bwd(1, seg, m, e, _f32c(g_agg), W, ctx.needs_input_grad[0], ctx.nx, acc)
-        return gx, g_e, gW, gb, None, None
+        g_e, gx, gW, gb = _message_bwd(1, seg, m, e, _f32c(g_agg), W, ctx.needs_input_grad[0], ctx.nx, acc, ctx.e_eid)
+        return gx, g_e, gW, gb, None, None, None
 
 
-def gine_aggregate(x, e, W, b, seg: SegmentIndex, sink=None):
-    return _GINEAggregate.apply(x, e, W, b, seg, sink)
+def gine_aggregate(x, e, W, b, seg: SegmentIndex, sink=None, e_eid=None):
+    return _GINEAggregate.apply(x, e, W, b, seg, sink, e_eid)
 
 
 # ----------------------------------------------------------------------------- edge update
@@ -445,12 +468,13 @@ class _EdgeUpdate(torch.autograd.Function):
     """e' = alpha e + beta (relu(P[src] + Q[dst] + e W1^T + b1) W2^T + b2), e-storage order."""
 
     @staticmethod
-    def forward(ctx, P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha, beta, sink=None):
+    def forward(ctx, P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha, beta, sink=None, e_eid=None, out_eid=None):
         P, Q, e, W1, b1, W2, b2 = map(_f32c, (P, Q, e, W1, b1, W2, b2))
         L.require_cuda(P, Q, e, W1, b1, W2, b2)
         _H(e)
-        h, out = _edge_linear_fwd(2, e, None, W1, b1, P, st.src32, Q, st.dst32, W2, b2, float(alpha), float(beta))
+        h, out = _edge_linear_fwd(2, e, e_eid, W1, b1, P, st.src32, Q, st.dst32, W2, b2, float(alpha), float(beta), out_eid)
         ctx.st, ctx.alpha, ctx.beta, ctx.nP, ctx.nQ, ctx.sink = st, float(alpha), float(beta), P.shape[0], Q.shape[0], sink
+        ctx.e_eid, ctx.out_eid = e_eid, out_eid
         ctx.save_for_backward(h, e, W1, W2)
         return out
 
@@ -458,12 +482,17 @@ class _EdgeUpdate(torch.autograd.Function):
     def backward(ctx, g_out):
         h, e, W1, W2 = ctx.saved_tensors
         g_e, gP, gQ, gW1, gb1, gW2, gb2 = _edge_update_bwd(ctx.st, _f32c(g_out), h, e, W1, W2, ctx.alpha, ctx.beta,
-                                                           ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.nP, ctx.nQ)
+                                                           ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.nP, ctx.nQ,
+                                                           ctx.out_eid, ctx.e_eid)
         if ctx.sink is not None and ctx.needs_input_grad[2]:
             ctx.sink.buf = g_e            # the same layer's message backward accumulates into it and returns it
             g_e = None
-        return gP, gQ, g_e, gW1, gb1, gW2, gb2, None, None, None, None
+        elif ctx.e_eid is not None and ctx.needs_input_grad[2]:
+            g_e = scatter_rows_i32(g_e, ctx.e_eid)     # g_e is in segment order, e was given in storage order
+        return gP, gQ, g_e, gW1, gb1, gW2, gb2, None, None, None, None, None, None
 
 
-def edge_update(P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha: float, beta: float, sink=None):
-    return _EdgeUpdate.apply(P, Q, e, W1, b1, W2, b2, st, alpha, beta, sink)
+def edge_update(P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha: float, beta: float, sink=None, e_eid=None, out_eid=None):
+    """e_eid / out_eid: int32 maps segment position -> row, for an input e / an output e' that
+    live in the caller's edge order instead of segment order (first / last layer)."""
+    return _EdgeUpdate.apply(P, Q, e, W1, b1, W2, b2, st, alpha, beta, sink, e_eid, out_eid)

@@ -33,6 +33,13 @@ class SegmentIndex:
     seg32: torch.Tensor      # int32 [E]   aggregation node of sorted edge k
     eid32: Optional[torch.Tensor] = None   # int32 [E] row of edge k in e-storage (None = k)
     _heavy: Optional[tuple] = field(default=None, repr=False)
+    _perm32: Optional[torch.Tensor] = field(default=None, repr=False)
+
+    def perm32(self):
+        """perm as int32 (row map for kernels that read / write the caller's edge order)."""
+        if getattr(self, "_perm32", None) is None:
+            self._perm32 = self.perm.to(torch.int32).contiguous()
+        return self._perm32
 
     def heavy(self):
         """(n_heavy, heavy_node32, heavy_chunk_ptr32, n_chunks, chunk_heavy32, chunk_begin64):

@@ -73,6 +73,24 @@ class _Backbone(nn.Module):
 
     def _layers(self, x, edge_index, e):
         st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
+        H = x.shape[1]
+        if self.reverse_mp or H != 64 or not BF.row_maps_available():
+            return self._layers_permuted(x, st, e)
+        # e stays in the caller's edge order at both ends: the first layer's kernels read it through
+        # the CSC permutation, the last edge update writes through it -- no permutation passes
+        perm32 = st.fwd.perm32()
+        L = self.num_gnn_layers
+        e_in = e
+        for i in range(L):
+            e_eid = perm32 if (i == 0 or not self.edge_updates) else None
+            out_eid = perm32 if i == L - 1 else None
+            sink = BF.EdgeGradSink() if (self.edge_updates and e.requires_grad and torch.is_grad_enabled()) else None
+            x = (x + F.relu(self.batch_norms[i](self.convs[i].forward_sorted(x, st.fwd, e, sink=sink, e_eid=e_eid)))) / 2
+            if self.edge_updates:
+                e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, sink=sink, e_eid=e_eid, out_eid=out_eid)
+        return x, (e if self.edge_updates else e_in)
+
+    def _layers_permuted(self, x, st, e):
         e = BF.gather_rows(e, st.fwd.perm)                      # caller order -> CSC storage order
         for i in range(self.num_gnn_layers):
             # conv and edge update of a layer read the same e: one gradient buffer for both

@@ -71,17 +71,18 @@ class GINEConv(nn.Module):
         self.eps.data.fill_(self.initial_eps)
         self.lin.reset_parameters()
 
-    def forward_sorted(self, x: Union[Tensor, tuple], seg: SegmentIndex, e: Tensor, gather=None, sink=None) -> Tensor:
+    def forward_sorted(self, x: Union[Tensor, tuple], seg: SegmentIndex, e: Tensor, gather=None, sink=None, e_eid=None) -> Tensor:
         """`gather` (multi-GPU, parallel.py): maps the owned rows of the source-side node table to
         the table of all ranks; the self term and the output stay on the owned rows.  `sink`:
-        functional.EdgeGradSink shared with the layer's edge update."""
+        functional.EdgeGradSink shared with the layer's edge update.  `e_eid`: int32 row map when e
+        is in the caller's edge order instead of segment order (functional.pna_aggregate)."""
         self_term = True
         if isinstance(x, (tuple, list)):
             x, x_dst = x
             self_term = x_dst is not None
         if self.lin.weight.shape[0] != self.lin.weight.shape[1] or x.shape[1] != self.lin.weight.shape[0]:
             raise ValueError("b200mp GINEConv kernels need edge_dim == in_channels")
-        out = BF.gine_aggregate(gather(x) if gather is not None else x, e, self.lin.weight, self.lin.bias, seg, sink)
+        out = BF.gine_aggregate(gather(x) if gather is not None else x, e, self.lin.weight, self.lin.bias, seg, sink, e_eid)
         if self_term:
             out = out + (1 + self.eps) * x
         return self.nn(out)
@@ -141,7 +142,7 @@ class PNAConv(nn.Module):
         self.post_nns[0][0].reset_parameters()
         self.lin.reset_parameters()
 
-    def forward_sorted(self, x: Tensor, seg: SegmentIndex, e: Tensor, gather=None, sink=None) -> Tensor:
+    def forward_sorted(self, x: Tensor, seg: SegmentIndex, e: Tensor, gather=None, sink=None, e_eid=None) -> Tensor:
         Fi = self.F_in
         pre = self.pre_nns[0][0]
         Wi, Wj, Wc = pre.weight[:, :Fi], pre.weight[:, Fi:2 * Fi], pre.weight[:, 2 * Fi:]
@@ -153,7 +154,7 @@ class PNAConv(nn.Module):
             B = gather(B)
         Wp = Wc @ self.edge_encoder.weight
         bp = Wc @ self.edge_encoder.bias + pre.bias
-        agg4, _ = BF.pna_aggregate(A, B, e, Wp, bp, seg, sink)
+        agg4, _ = BF.pna_aggregate(A, B, e, Wp, bp, seg, sink, e_eid)
 
         post = self.post_nns[0][0]
         na = len(self.aggregators)
@@ -174,7 +175,7 @@ class PNAConv(nn.Module):
 
 
 def edge_update_sorted(emlp: nn.Sequential, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float,
-                       gather=None, sink=None) -> Tensor:
+                       gather=None, sink=None, e_eid=None, out_eid=None) -> Tensor:
     """e' = alpha e + beta emlp([x[src], x[dst], e]) with emlp = Sequential(Linear(3H,H), ReLU,
     Linear(H,H)) (gine.py:71-75,88-89; pna.py:80-84,97-99; models/fused.py:215-219,254)."""
     l1, l2 = emlp[0], emlp[2]
@@ -184,4 +185,4 @@ def edge_update_sorted(emlp: nn.Sequential, x: Tensor, st: EdgeStructure, e: Ten
     if gather is not None:
         P = gather(P)
     Q = BF.linear3x(x, Wd)
-    return BF.edge_update(P, Q, e, We, l1.bias, l2.weight, l2.bias, st, alpha, beta, sink)
+    return BF.edge_update(P, Q, e, We, l1.bias, l2.weight, l2.bias, st, alpha, beta, sink, e_eid, out_eid)

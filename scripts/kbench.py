@@ -64,15 +64,15 @@ def main():
 
     def fwd(mode, eid, t1, i1, t2, i2):
         L.check(lib.b200mp_edge_linear_fwd(mode, H, E, p(ea), p(eid), p(W1), p(b1), p(t1), p(i1), p(t2), p(i2),
-                                           p(W2), p(b2), 1.0, 0.5, p(out1), p(out2 if mode == 2 else None), s()), "fwd")
+                                           p(W2), p(b2), 1.0, 0.5, p(out1), p(out2 if mode == 2 else None), None, s()), "fwd")
 
     def updb(src, dst, gp, gq):
         L.check(lib.b200mp_edge_update_bwd(H, E, p(gout), p(hh), p(ea), p(src), p(dst), p(W1), p(W2), 1.0, 0.5,
-                                           p(out1), p(gp), p(gq), p(gW1), p(gb1), p(gW2), p(gb2), npart, s()), "updb")
+                                           p(out1), p(gp), p(gq), p(gW1), p(gb1), p(gW2), p(gb2), npart, None, None, s()), "updb")
 
     def msgb(kind, node_in, gt1, eid=None):
         L.check(lib.b200mp_message_bwd(kind, H, E, p(m), p(ea), p(eid), p(node_in), p(seg.seg32), p(seg.nbr32), p(W1),
-                                       p(out1), 0, p(gt1), p(gW1), p(gb1), npart, s()), "msgb")
+                                       p(out1), 0, p(gt1), p(gW1), p(gb1), npart, None, s()), "msgb")
 
     def segr():
         BF._segment_reduce(0, seg, m, H)

@@ -36,7 +36,7 @@ def permute(x, idx, scatter):
     return out
 
 
-def edge_linear_fwd(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2=None, b2=None, alpha=0.0, beta=0.0):
+def edge_linear_fwd(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2=None, b2=None, alpha=0.0, beta=0.0, out_eid=None):
     rows = eid.long() if eid is not None else torch.arange(e.shape[0], device=e.device)
     x = e[rows]
     z = x @ W1.t() + b1
@@ -49,7 +49,8 @@ def edge_linear_fwd(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2=None, b2=None, 
     out2 = None
     if mode == 2:
         out2 = torch.empty_like(e)
-        out2[rows] = alpha * x + beta * (z @ W2.t() + b2)
+        orows = out_eid.long() if out_eid is not None else torch.arange(e.shape[0], device=e.device)
+        out2[orows] = alpha * x + beta * (z @ W2.t() + b2)
     return z, out2
 
 
@@ -76,11 +77,12 @@ def segment_reduce(kind, seg, m, H):
     return agg, torch.cat([cn, cx], 1) * has
 
 
-def message_bwd(kind, seg, m, e, node_in, W, need_T1, N, g_e=None):
+def message_bwd(kind, seg, m, e, node_in, W, need_T1, N, g_e=None, eid=None):
     H = m.shape[1]
     acc = g_e
     d = seg.seg32.long()
-    rows = seg.eid32.long() if seg.eid32 is not None else torch.arange(m.shape[0])
+    eid = seg.eid32 if eid is None else eid
+    rows = eid.long() if eid is not None else torch.arange(m.shape[0])
     if kind == 0:
         c = node_in[d]
         c0, c1, gmn, mn, gmx, mx, mu = [c[:, i * H:(i + 1) * H] for i in range(7)]
@@ -89,15 +91,22 @@ def message_bwd(kind, seg, m, e, node_in, W, need_T1, N, g_e=None):
         Gm = torch.where(m > 0, node_in[d], torch.zeros_like(m))
     gT1 = torch.zeros((N, H), dtype=m.dtype).index_add_(0, seg.nbr32.long(), Gm) if need_T1 else None
     g_e = torch.empty_like(e)
-    g_e[rows] = Gm @ W
-    if acc is not None:                      # kernel contract: accumulate into the given buffer and return it
-        acc += g_e
+    if acc is not None and eid is not None:  # kernel contract: add in segment order, write through the row map
+        g_e[rows] = Gm @ W + acc
+    elif acc is not None:                    # accumulate into the given buffer and return it
+        acc += Gm @ W
         g_e = acc
+    else:
+        g_e[rows] = Gm @ W
     return g_e, gT1, Gm.t() @ e[rows], Gm.sum(0)
 
 
-def edge_update_bwd(st, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q, nP=None, nQ=None):
+def edge_update_bwd(st, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q, nP=None, nQ=None, g_eid=None, e_eid=None):
     N, H = st.num_nodes, e.shape[1]
+    if g_eid is not None:
+        g_out = g_out[g_eid.long()]
+    if e_eid is not None:
+        e = e[e_eid.long()]
     Gout = beta * g_out
     Gh = (Gout @ W2) * (h > 0).to(e.dtype)
     gP = torch.zeros((nP or N, H), dtype=e.dtype).index_add_(0, st.src32.long(), Gh) if need_P else None

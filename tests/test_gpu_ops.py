@@ -126,6 +126,24 @@ def test_edge_kernels_vs_emulation(H):
     ref = EM.edge_update_bwd(stc, gout, h.cpu(), E_, W1, W2, 1.0, 0.5, True, True)
     for a, b, nm in zip(got, ref, ("g_e", "gP", "gQ", "gW1", "gb1", "gW2", "gb2")):
         assert rel_err(a, b) < 1e-5, (nm, rel_err(a, b))
+    # row maps (first / last layer read and write the caller's edge order)
+    p32 = st.fwd.perm32()
+    o1, o2 = BF._edge_linear_fwd(2, d(E_), p32, d(W1), d(b1), d(B), st.src32, d(A), st.dst32, d(W2), d(b2), 1.0, 0.5, p32)
+    r1, r2 = EM.edge_linear_fwd(2, E_, p32.cpu(), W1, b1, B, stc.src32, A, stc.dst32, W2, b2, 1.0, 0.5, p32.cpu())
+    assert rel_err(o1, r1) < 2e-6 and rel_err(o2, r2) < 2e-6
+    if H == 64:
+        got = BF._edge_update_bwd(st, d(gout), h, d(E_), d(W1), d(W2), 1.0, 0.5, True, True, None, None, p32, p32)
+        ref = EM.edge_update_bwd(stc, gout, h.cpu(), E_, W1, W2, 1.0, 0.5, True, True, None, None, p32.cpu(), p32.cpu())
+        for a, b, nm in zip(got, ref, ("g_e", "gP", "gQ", "gW1", "gb1", "gW2", "gb2")):
+            assert rel_err(a, b) < 1e-5, ("mapped", nm, rel_err(a, b))
+        acc = rnd(e, H)
+        m = BF._edge_linear_fwd(0, d(E_), p32, d(W1), d(b1), d(B), st.fwd.nbr32, d(A), st.fwd.seg32)[0]
+        for g_acc, eid in ((acc, p32), (acc, None), (None, p32)):
+            got = BF._message_bwd(1, st.fwd, m, d(E_), d(A), d(W1), True, n, None if g_acc is None else d(g_acc).clone(), eid)
+            ref = EM.message_bwd(1, stc.fwd, m.cpu(), E_, A, W1, True, n, None if g_acc is None else g_acc.clone(),
+                                 None if eid is None else eid.cpu())
+            for a, b, nm in zip(got, ref, ("g_e", "gT1", "gW", "gb")):
+                assert rel_err(a, b) < 1e-5, ("acc/map", nm, rel_err(a, b))
 
 
 def test_permute_roundtrip_and_empty():
