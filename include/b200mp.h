@@ -87,6 +87,10 @@ int b200mp_node_linear(const float* X, int64_t N, int K, int ldx, const float* W
  * (K % 128 == 0, NO in {64,128,192,256}); the caller sums the n_part partials (deterministic). */
 int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const float* Y, int ldy, int NO, int64_t N,
                              float* part, int n_part, void* stream);
+/* Weight gradients of two H = 64 node linears sharing their input Y (PNAConv pre_nn halves A | B, edge
+ * update halves P | Q, pna.py:71-84): part[p][0:64] = G0^T Y, part[p][64:128] = G1^T Y; all [N,64]. */
+int b200mp_node_pair_wgrad(const float* G0, const float* G1, const float* Y, int64_t N, float* part, int n_part,
+                           void* stream);
 
 /* ------------------------------------------------------------------ per-edge linear (forward)
  * One pass over E edges in segment order k = 0..E-1; H in {16,32,64,128}.

@@ -39,6 +39,7 @@ _SIGS = {
     "b200mp_split_tf32": [_p, _p, _p, _l, _p],
     "b200mp_node_linear": [_p, _l, _i, _i, _p, _i, _p, _p, _p],
     "b200mp_node_linear_wgrad": [_p, _i, _i, _p, _i, _i, _l, _p, _i, _p],
+    "b200mp_node_pair_wgrad": [_p, _p, _p, _l, _p, _i, _p],
     "b200mp_umma_selftest": [_i, _p, _p, _p, _p],
     "b200mp_umma_probe": [_p, _i, _p, _i, C.c_uint64, C.c_uint64, _i, _i, _i, C.c_uint32, _p, _p],
     "b200mp_edge_update_bwd": [_i, _l, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p],

@@ -162,6 +162,7 @@ struct NodeWgArgs {
     int64_t N; int ldx; int ldy;
     const float* X; const float* Y; float* part;   // part: [gridDim.x][K][NO]
     int K;
+    const float* X1;                               // pair mode (K = 128): columns 64..127 of X come from X1, both at ldx
 };
 }  // namespace ng
 
@@ -196,7 +197,9 @@ __global__ void __launch_bounds__(NT2, 2) node_wgrad_umma_kernel(NodeWgArgs a) {
         ok_pf = r < a.N;
         const int64_t rc = ok_pf ? r : a.N - 1;
 #pragma unroll
-        for (int p = 0; p < XPN; ++p) xr[p] = ldg4(a.X + rc * a.ldx + kb * 128 + p * 32 + piece * 4);
+        for (int p = 0; p < XPN; ++p)
+            xr[p] = ldg4((a.X1 && p >= 2) ? a.X1 + rc * a.ldx + (p - 2) * 32 + piece * 4
+                                          : a.X + rc * a.ldx + kb * 128 + p * 32 + piece * 4);
 #pragma unroll
         for (int p = 0; p < YPN; ++p) yr[p] = ldg4(a.Y + rc * a.ldy + p * 32 + piece * 4);
     };
@@ -284,7 +287,7 @@ extern "C" int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const fl
     using namespace b200mp;
     if (N <= 0 || K <= 0 || K % 128 || ldx < K || ldx % 4 || ldy < NO || ldy % 4 || n_part <= 0 || !X || !Y || !part)
         return B200MP_EINVAL;
-    NodeWgArgs a{N, ldx, ldy, X, Y, part, K};
+    NodeWgArgs a{N, ldx, ldy, X, Y, part, K, nullptr};
     cudaStream_t st = (cudaStream_t)stream;
     switch (NO) {
         case 64: return launch_node_wgrad<64>(a, n_part, st);
@@ -293,4 +296,14 @@ extern "C" int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const fl
         case 256: return launch_node_wgrad<256>(a, n_part, st);
     }
     return B200MP_EINVAL;
+}
+
+/* Weight gradients of two H = 64 node linears that share their input: part[p][0:64] = G0^T Y,
+ * part[p][64:128] = G1^T Y over the rows handled by CTA p (G0, G1, Y: [N, 64] contiguous). */
+extern "C" int b200mp_node_pair_wgrad(const float* G0, const float* G1, const float* Y, int64_t N, float* part, int n_part,
+                                      void* stream) {
+    using namespace b200mp;
+    if (N <= 0 || n_part <= 0 || !G0 || !G1 || !Y || !part) return B200MP_EINVAL;
+    NodeWgArgs a{N, 64, 64, G0, Y, part, 128, G1};
+    return launch_node_wgrad<64>(a, n_part, (cudaStream_t)stream);
 }

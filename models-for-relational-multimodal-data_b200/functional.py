@@ -245,6 +245,66 @@ class _Linear3x(torch.autograd.Function):
         return gx, gW, gb
 
 
+def _node_pair_wgrad(g0, g1, x):
+    """(g0^T x, g1^T x) for [N,64] tensors on the tcgen05 weight-gradient kernel (one launch)."""
+    N = x.shape[0]
+    npart = torch.cuda.get_device_properties(x.device).multi_processor_count
+    part = torch.empty((npart, 128, 64), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device), _track("node_pair_wgrad"):
+        L.check(L.lib().b200mp_node_pair_wgrad(L.ptr(g0), L.ptr(g1), L.ptr(x), N, L.ptr(part), npart, L.stream()),
+                "b200mp_node_pair_wgrad")
+    G = part.sum(0)
+    return G[:64], G[64:]
+
+
+class _LinearGroup(torch.autograd.Function):
+    """y_i = x W_i^T + b_i for several H x H node linears over the SAME input (PNAConv's hoisted
+    pre_nn halves and post_nn self term, the edge update's P | Q).  Forward: fp32 library GEMMs
+    (HBM bound).  Backward: the data gradients accumulate in the GEMM epilogue (no separate adds),
+    the weight gradients -- reductions over all N rows, which the library runs as slow split-K
+    GEMMs -- go two at a time through the tcgen05 weight-gradient kernel."""
+
+    @staticmethod
+    def forward(ctx, x, n, *params):
+        x = _f32c(x)
+        L.require_cuda(x)
+        Ws, bs = params[:n], params[n:]
+        ctx.n = n
+        ctx.save_for_backward(x, *Ws)
+        return tuple(torch.nn.functional.linear(x, W, b) for W, b in zip(Ws, bs))
+
+    @staticmethod
+    def backward(ctx, *gs):
+        x, *Ws = ctx.saved_tensors
+        n = ctx.n
+        gs = [None if g is None else _f32c(g) for g in gs]
+        gx = None
+        if ctx.needs_input_grad[0]:
+            for g, W in zip(gs, Ws):
+                if g is not None:
+                    gx = g @ W if gx is None else gx.addmm_(g, W)
+        gW = [None] * n
+        want = [i for i in range(n) if gs[i] is not None and ctx.needs_input_grad[2 + i]]
+        kernel_ok = x.shape[0] >= 4096 and x.shape[1] == 64 and all(Ws[i].shape == (64, 64) for i in want)
+        if kernel_ok:
+            for k in range(0, len(want), 2):
+                i0 = want[k]
+                i1 = want[k + 1] if k + 1 < len(want) else i0
+                gW[i0], g1 = _node_pair_wgrad(gs[i0], gs[i1], x)
+                if i1 != i0:
+                    gW[i1] = g1
+        else:
+            for i in want:
+                gW[i] = gs[i].t() @ x
+        gb = [gs[i].sum(0) if (gs[i] is not None and ctx.needs_input_grad[2 + n + i]) else None for i in range(n)]
+        return (gx, None, *gW, *gb)
+
+
+def linear_group(x, weights, biases):
+    """[x W^T + b for W, b in zip(weights, biases)] (b may be None) as one autograd node."""
+    return _LinearGroup.apply(x, len(weights), *weights, *biases)
+
+
 def linear3x(x, W, b=None):
     """torch.nn.functional.linear(x, W, b) for node-level [N, K] inputs, fp32-accurate on the
     tensor cores (three TF32 library GEMMs)."""

@@ -148,18 +148,16 @@ class PNAConv(nn.Module):
         Wi, Wj, Wc = pre.weight[:, :Fi], pre.weight[:, Fi:2 * Fi], pre.weight[:, 2 * Fi:]
         # pre_nn is one Linear without activation: hoist the node halves to N rows and fold the
         # edge encoder into a single H x H matrix (SURVEY.md section 7 "hoisting")
-        A = BF.linear3x(x, Wi)
-        B = BF.linear3x(x, Wj)
+        post = self.post_nns[0][0]
+        A, B, out = BF.linear_group(x, (Wi, Wj, post.weight[:, :Fi]), (None, None, post.bias))
         if gather is not None:            # multi-GPU: source rows of every rank (parallel.py)
             B = gather(B)
         Wp = Wc @ self.edge_encoder.weight
         bp = Wc @ self.edge_encoder.bias + pre.bias
         agg4, _ = BF.pna_aggregate(A, B, e, Wp, bp, seg, sink, e_eid)
 
-        post = self.post_nns[0][0]
         na = len(self.aggregators)
         cols = [_AGG_ORDER.index(a) for a in self.aggregators]
-        out = BF.linear3x(x, post.weight[:, :Fi], post.bias)
         lin_avg, log_avg = self.aggr_module.avg_deg_lin, self.aggr_module.avg_deg_log
         agg_used = agg4 if cols == [0, 1, 2, 3] else torch.cat([agg4[:, c * Fi:(c + 1) * Fi] for c in cols], dim=1)
         Ws = post.weight[:, Fi:]                          # [F_out, ns * na * Fi], scaler-major
@@ -167,7 +165,7 @@ class PNAConv(nn.Module):
         # one GEMM for all scalers: Z[:, s*F_out:(s+1)*F_out] = agg_used @ Ws_s^T
         Z = BF.linear3x(agg_used, Ws.reshape(self.F_out, ns, na * Fi).permute(1, 0, 2).reshape(ns * self.F_out, na * Fi))
         out = BF.pna_scale(out, Z, seg.ptr, self.scalers, lin_avg, log_avg)
-        return BF.linear3x(out, self.lin.weight, self.lin.bias)
+        return BF.linear_group(out, (self.lin.weight,), (self.lin.bias,))[0]
 
     def forward(self, x: Tensor, edge_index: Tensor, edge_attr: Tensor) -> Tensor:
         st = _resolve(x, edge_index)
@@ -181,8 +179,7 @@ def edge_update_sorted(emlp: nn.Sequential, x: Tensor, st: EdgeStructure, e: Ten
     l1, l2 = emlp[0], emlp[2]
     H = x.shape[1]
     Ws, Wd, We = l1.weight[:, :H], l1.weight[:, H:2 * H], l1.weight[:, 2 * H:]
-    P = BF.linear3x(x, Ws)
+    P, Q = BF.linear_group(x, (Ws, Wd), (None, None))
     if gather is not None:
         P = gather(P)
-    Q = BF.linear3x(x, Wd)
     return BF.edge_update(P, Q, e, We, l1.bias, l2.weight, l2.bias, st, alpha, beta, sink, e_eid, out_eid)

@@ -51,3 +51,22 @@ def test_linear3x_autograd_matches_fp64():
         err = rel_err(a, t)
         print(f"linear3x {name}: rel err {err:.2e}")
         assert err < 1e-5
+
+
+@pytest.mark.parametrize("N", [4096, 7001])
+def test_linear_group_matches_fp64(N):
+    g = torch.Generator(device="cuda").manual_seed(N)
+    x = torch.randn(N, 64, device="cuda", generator=g, requires_grad=True)
+    Wbig = (torch.randn(64, 192, device="cuda", generator=g) / 8).requires_grad_(True)     # sliced like pre_nn's weight
+    b2 = torch.randn(64, device="cuda", generator=g, requires_grad=True)
+    Ws = (Wbig[:, :64], Wbig[:, 64:128], Wbig[:, 128:])
+    gy = [torch.randn(N, 64, device="cuda", generator=g) for _ in range(3)]
+    ys = BF.linear_group(x, Ws, (None, None, b2))
+    torch.autograd.backward(ys, gy)
+    xd, Wd, bd = (t.detach().double().requires_grad_(True) for t in (x, Wbig, b2))
+    yd = [xd @ Wd[:, :64].t(), xd @ Wd[:, 64:128].t(), xd @ Wd[:, 128:].t() + bd]
+    torch.autograd.backward(yd, [t.double() for t in gy])
+    for name, a, t in (("y2", ys[2], yd[2]), ("gx", x.grad, xd.grad), ("gW", Wbig.grad, Wd.grad), ("gb", b2.grad, bd.grad)):
+        err = rel_err(a, t)
+        print(f"linear_group N={N} {name}: rel err {err:.2e}")
+        assert err < 1e-5
