@@ -77,80 +77,165 @@ __device__ __forceinline__ void cta_column_sums(float* red, float4 acc, float* _
     }
 }
 
-// Thread mappings as in edge_fwd_umma.cu: tensor memory is read row-per-thread into a staging tile;
-// loads, stores, REDs and all element-wise math run in the coalesced mapping (thread (g, j) =
-// 16-byte chunk j of 4 adjacent rows) with the g / h / e rows held in registers.
-__global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArgs a) {
-    constexpr int NTH = NTB, CW = CWB, NP = NPB;
+// ---- two independent 64-edge pipelines per CTA ---------------------------------------------------
+// ncu on the one-tile-per-CTA version: 38 % of the warp samples sat in the two mbarrier spins (the
+// tensor pipe's 3xTF32 time, fully exposed) and shared memory is too full for a second 128-edge tile.
+// So the CTA's 512 threads form TWO groups of 256, each running the whole tile pipeline on its own
+// 64-edge tile (M = 64 MMAs) with its own buffers, mbarriers, named barrier and tensor-memory columns,
+// sharing only the weight tiles: while one group waits for its MMAs the other runs its SIMT phases.
+namespace dual {
+constexpr int RG = 64;                    // edges per group tile
+constexpr int NTG = 256;                  // threads per group
+constexpr int NPG = RG * 16 / NTG;        // 4 adjacent rows per thread in the coalesced mapping
+using RG_T = RowFmt<RG, HH>;              // 16 KB operand tile
+
+struct Rows { float4 v[NPG]; };
+__device__ __forceinline__ void group_sync(int grp) { asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(NTG) : "memory"); }
+__device__ __forceinline__ void load_rows(Rows& R, const float* __restrict__ src, const int32_t* __restrict__ rowmap,
+                                          int64_t row0, int nrows, int lt) {
+    const int j = lt & 15, g = lt >> 4;
+    int64_t rows[NPG];
+#pragma unroll
+    for (int i = 0; i < NPG; ++i) {
+        const int rc = min(g * NPG + i, nrows - 1);
+        rows[i] = rowmap ? (int64_t)__ldg(rowmap + row0 + rc) : row0 + rc;
+    }
+#pragma unroll
+    for (int i = 0; i < NPG; ++i) R.v[i] = ldg4(src + rows[i] * HH + j * 4);
+}
+__device__ __forceinline__ void store_rows_split(const Rows& R, float* hi, float* lo, int nrows, int lt) {
+    const int j = lt & 15, g = lt >> 4;
+#pragma unroll
+    for (int i = 0; i < NPG; ++i) {
+        const int r = g * NPG + i;
+        float4 h, l;
+        split4(r < nrows ? R.v[i] : make_float4(0.f, 0.f, 0.f, 0.f), h, l);
+        const int o = RG_T::off(r, j);
+        st4(hi + o, h);
+        st4(lo + o, l);
+    }
+}
+// M = 64 accumulator [64 x 64] -> staging tile: row m sits in tensor-memory lane (m % 16) + 32 (m / 16),
+// so warp (quarter q = warp % 4, column half = group-local warp / 4) reads rows 16 q .. 16 q + 15 in its
+// lanes 0..15 (lanes 16..31 carry nothing).
+__device__ __forceinline__ void stage_from_tmem64(uint32_t tcols, float* S, int lwarp, int lane) {
+    const int q = lwarp & 3, half = lwarp >> 2;
+    const uint32_t taddr = tcols + ((uint32_t)(q * 32) << 16) + half * 32;
+    const int r = q * 16 + (lane & 15);
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        float v[16];
+        tmem_ld16(taddr + k * 16, v);
+        if (lane < 16) {
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj)
+                st4(S + stage_off(r, half * 8 + k * 4 + jj), f4(v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]));
+        }
+    }
+}
+__device__ __forceinline__ void gemm3_data64(uint32_t d, const float* x_hi, const float* x_lo, const float* w_hi, const float* w_lo,
+                                             uint32_t accumulate) {
+    issue_data_gemm_row32<RG, HH, HH>(d, smem_u32(x_lo), smem_u32(w_hi), accumulate);
+    issue_data_gemm_row32<RG, HH, HH>(d, smem_u32(x_hi), smem_u32(w_lo), 1);
+    issue_data_gemm_row32<RG, HH, HH>(d, smem_u32(x_hi), smem_u32(w_hi), 1);
+}
+__device__ __forceinline__ void gemm3_wgrad64(uint32_t d, const float* g_hi, const float* g_lo, const float* x_hi, const float* x_lo,
+                                              uint32_t accumulate) {
+    issue_wgrad_gemm_row32<RG, HH, HH>(d, smem_u32(g_lo), smem_u32(x_hi), accumulate);
+    issue_wgrad_gemm_row32<RG, HH, HH>(d, smem_u32(g_hi), smem_u32(x_lo), 1);
+    issue_wgrad_gemm_row32<RG, HH, HH>(d, smem_u32(g_hi), smem_u32(x_hi), 1);
+}
+// per-thread column partials -> this group's column sums (red: [NTG / 16][64] floats of the group's smem)
+__device__ __forceinline__ void group_column_sums(float* red, float4 acc, float* __restrict__ out, float scale, int lt, int grp) {
+    group_sync(grp);
+    st4(red + (lt >> 4) * HH + (lt & 15) * 4, acc);
+    group_sync(grp);
+    if (lt < HH) {
+        float sum = 0.f;
+#pragma unroll 8
+        for (int g = 0; g < NTG / 16; ++g) sum += red[g * HH + lt];
+        out[lt] = scale * sum;
+    }
+}
+}  // namespace dual
+
+__global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArgs a, int n_virtual) {
+    using namespace dual;
+    constexpr int NP = NPG;
     extern __shared__ __align__(128) float smem_raw[];
     float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;   // keeps the shared address space
-    float* G_hi = smem;                       // g tile; staging tile once its MMAs are done; then the e tile
-    float* G_lo = G_hi + RT::FLOATS;
-    float* H_hi = G_lo + RT::FLOATS;          // h tile, later the Gh tile
-    float* H_lo = H_hi + RT::FLOATS;
-    float* W2_hi = H_lo + RT::FLOATS;         // B[n=k][K=j] = W2[j][k]   (U = g W2)
+    float* W2_hi = smem;                      // B[n=k][K=j] = W2[j][k]   (U = g W2)
     float* W2_lo = W2_hi + WT::FLOATS;
     float* W1_hi = W2_lo + WT::FLOATS;        // B[n=k][K=j] = W1[j][k]   (g_e = Gh W1)
     float* W1_lo = W1_hi + WT::FLOATS;
-    __shared__ TileSync sync;
-    __shared__ int sidx[2][TE];               // src / dst ids of the tile's rows (clamped rows)
+    __shared__ uint64_t bars[2][2];
+    __shared__ uint32_t tmem_base_s;
+    __shared__ int sidx_s[2][2][RG];          // [group][src / dst][row]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int t = tid & (TE - 1), ch = tid >> 7;           // tensor-memory side
-    const int j = tid & 15, g = tid >> 4;                  // global-memory side
-    if (warp == 0) tmem_alloc(&sync.tmem_base, 256);
-    if (tid == 0) { mbar_init(&sync.bar[0], 1); mbar_init(&sync.bar[1], 1); mbar_fence_init(); }
-    load_weight_tiles<true, NTH>(W2_hi, W2_lo, a.W2, tid);
-    load_weight_tiles<true, NTH>(W1_hi, W1_lo, a.W1, tid);
+    const int grp = tid >> 8, lt = tid & (NTG - 1), lwarp = lt >> 5;
+    const int j = lt & 15, g = lt >> 4;                    // global-memory side
+    float* G_hi = W1_lo + WT::FLOATS + grp * 4 * RG_T::FLOATS;   // g tile; staging tile once its MMAs are done; then the e tile
+    float* G_lo = G_hi + RG_T::FLOATS;
+    float* H_hi = G_lo + RG_T::FLOATS;        // h tile, later the Gh tile
+    float* H_lo = H_hi + RG_T::FLOATS;
+    uint64_t* bar = bars[grp];
+    int (*sidx)[RG] = sidx_s[grp];
+    if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+    if (lt == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
+    load_weight_tiles<true, NTB>(W2_hi, W2_lo, a.W2, tid);
+    load_weight_tiles<true, NTB>(W1_hi, W1_lo, a.W1, tid);
     fence_async_smem();
     fence_before();
     __syncthreads();
     fence_after();
-    const uint32_t tm = sync.tmem_base;
-    const uint32_t T_GW2 = tm + 128, T_GW1 = tm + 192;
-    const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
-    const uint32_t T_U = tm + lane_off + ch * CW, T_ACC2 = tm + 64 + lane_off + ch * CW;
+    const uint32_t tm = tmem_base_s + grp * 256;
+    const uint32_t T_U = tm, T_ACC2 = tm + 64, T_GW2 = tm + 128, T_GW1 = tm + 192;
     float* stage = G_hi;
 
     float4 accb1 = f4(0.f, 0.f, 0.f, 0.f), accb2 = f4(0.f, 0.f, 0.f, 0.f);   // columns 4 j .. 4 j + 3 over this thread's rows
-    const int64_t ntiles = (a.E + TE - 1) / TE;
+    const int64_t ntiles = (a.E + RG - 1) / RG;
+    const int64_t v0 = (int64_t)blockIdx.x * 2 + grp;      // this group's virtual CTA
+    const int64_t stride = n_virtual;
+    const bool active = v0 < n_virtual;
     uint32_t it = 0;
-    RowRegs<NTH> Rg, Rh, Re;
+    Rows Rg, Rh, Re;
     int nrows_pf = 0, idx_pf = 0;
-    const int32_t* idx_src = ch == 0 ? a.src : ch == 1 ? a.dst : nullptr;
-    if ((int64_t)blockIdx.x < ntiles) {
-        nrows_pf = (int)min64(TE, a.E - (int64_t)blockIdx.x * TE);
-        load_rows(Rg, a.g_out, a.g_eid, (int64_t)blockIdx.x * TE, nrows_pf, tid);
-        load_rows(Rh, a.h, nullptr, (int64_t)blockIdx.x * TE, nrows_pf, tid);
-        if (idx_src) idx_pf = __ldg(idx_src + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
+    const int t = lt & (RG - 1), which = lt >> 6;          // index staging: thread lt < 128 -> (src | dst) of row t
+    const int32_t* idx_src = which == 0 ? a.src : which == 1 ? a.dst : nullptr;
+    if (active && v0 < ntiles) {
+        nrows_pf = (int)min64(RG, a.E - v0 * RG);
+        load_rows(Rg, a.g_out, a.g_eid, v0 * RG, nrows_pf, lt);
+        load_rows(Rh, a.h, nullptr, v0 * RG, nrows_pf, lt);
+        if (idx_src) idx_pf = __ldg(idx_src + v0 * RG + min(t, nrows_pf - 1));
     }
 
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const int64_t row0 = tile * TE;
+    for (int64_t tile = v0; active && tile < ntiles; tile += stride, ++it) {
+        const int64_t row0 = tile * RG;
         const int nrows = nrows_pf;
         const uint32_t par = it & 1;
 
         // ---- phase A: g and h tiles (prefetched, kept in registers too) -> shared memory; U = g W2; GW2 += g^T h
-        store_rows_split(Rg, G_hi, G_lo, nrows, tid);
-        store_rows_split(Rh, H_hi, H_lo, nrows, tid);
-        if (ch < 2) sidx[ch][t] = idx_pf;
+        store_rows_split(Rg, G_hi, G_lo, nrows, lt);
+        store_rows_split(Rh, H_hi, H_lo, nrows, lt);
+        if (which < 2) sidx[which][t] = idx_pf;
         fence_async_smem();
         fence_before();
-        __syncthreads();
+        group_sync(grp);
         fence_after();
-        if (tid == 0) {
-            gemm3_data(tm, G_hi, G_lo, W2_hi, W2_lo, 0);
-            gemm3_wgrad(T_GW2, G_hi, G_lo, H_hi, H_lo, it > 0);
-            mma_commit(&sync.bar[0]);
+        if (lt == 0) {
+            gemm3_data64(T_U, G_hi, G_lo, W2_hi, W2_lo, 0);
+            gemm3_wgrad64(T_GW2, G_hi, G_lo, H_hi, H_lo, it > 0);
+            mma_commit(&bar[0]);
         }
-        load_rows(Re, a.e, a.e_eid, row0, nrows, tid);                // e tile in flight during the MMAs
+        load_rows(Re, a.e, a.e_eid, row0, nrows, lt);                 // e tile in flight during the MMAs
         int srow[NP], drow[NP];
 #pragma unroll
         for (int i = 0; i < NP; ++i) { srow[i] = sidx[0][g * NP + i]; drow[i] = sidx[1][g * NP + i]; }
-        mbar_wait(&sync.bar[0], par);
+        mbar_wait(&bar[0], par);
         fence_after();
-        stage_from_tmem<NTH>(T_U, stage, t, ch);                      // the g tile is dead: U rows take its place
-        __syncthreads();
+        stage_from_tmem64(T_U, stage, lwarp, lane);                   // the g tile is dead: U rows take its place
+        group_sync(grp);
 
         // ---- Gh = beta U [h > 0] in the coalesced mapping; gP[src], gQ[dst], bias partials; Gh -> MMA operand
         {
@@ -168,36 +253,36 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
                 if (valid && a.gP) red_add4(a.gP + (int64_t)srow[i] * HH + j * 4, Gh[i]);
                 float4 gh, gl;
                 split4(Gh[i], gh, gl);
-                const int o = RT::off(r, j);
+                const int o = RG_T::off(r, j);
                 st4(H_hi + o, gh);
                 st4(H_lo + o, gl);
             }
             if (a.gQ) red_runs(a.gQ, drow, Gh, j, lane);
         }
-        __syncthreads();                                 // every thread is done reading the staged U rows
-        store_rows_split(Re, G_hi, G_lo, nrows, tid);    // e tile replaces them
+        group_sync(grp);                                 // every thread is done reading the staged U rows
+        store_rows_split(Re, G_hi, G_lo, nrows, lt);     // e tile replaces them
         fence_async_smem();
         fence_before();
-        __syncthreads();
+        group_sync(grp);
         fence_after();
 
         // ---- phase B: ACC2 = Gh W1; GW1 += Gh^T e
-        if (tid == 0) {
-            gemm3_data(tm + 64, H_hi, H_lo, W1_hi, W1_lo, 0);
-            gemm3_wgrad(T_GW1, H_hi, H_lo, G_hi, G_lo, it > 0);
-            mma_commit(&sync.bar[1]);
+        if (lt == 0) {
+            gemm3_data64(T_ACC2, H_hi, H_lo, W1_hi, W1_lo, 0);
+            gemm3_wgrad64(T_GW1, H_hi, H_lo, G_hi, G_lo, it > 0);
+            mma_commit(&bar[1]);
         }
         int nrows_next = 0;
-        if (tile + gridDim.x < ntiles) {                 // next tile's h in flight (g follows once this tile's g is used)
-            nrows_next = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
-            load_rows(Rh, a.h, nullptr, (tile + gridDim.x) * TE, nrows_next, tid);
-            load_rows(Re, a.g_out, a.g_eid, (tile + gridDim.x) * TE, nrows_next, tid);
-            if (idx_src) idx_pf = __ldg(idx_src + (tile + gridDim.x) * TE + min(t, nrows_next - 1));
+        if (tile + stride < ntiles) {                    // next tile's h and g in flight
+            nrows_next = (int)min64(RG, a.E - (tile + stride) * RG);
+            load_rows(Rh, a.h, nullptr, (tile + stride) * RG, nrows_next, lt);
+            load_rows(Re, a.g_out, a.g_eid, (tile + stride) * RG, nrows_next, lt);
+            if (idx_src) idx_pf = __ldg(idx_src + (tile + stride) * RG + min(t, nrows_next - 1));
         }
-        mbar_wait(&sync.bar[1], par);
+        mbar_wait(&bar[1], par);
         fence_after();
-        stage_from_tmem<NTH>(T_ACC2, stage, t, ch);      // the e tile is dead too
-        __syncthreads();
+        stage_from_tmem64(T_ACC2, stage, lwarp, lane);   // the e tile is dead too
+        group_sync(grp);
 
         // ---- g_e = alpha g + Gh W1, coalesced rows
 #pragma unroll
@@ -210,18 +295,20 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
         for (int i = 0; i < NP; ++i) Rg.v[i] = Re.v[i];
         nrows_pf = nrows_next;
         fence_before();
-        __syncthreads();
+        group_sync(grp);
         fence_after();
     }
 
-    const bool any = it > 0;
-    store_wgrad_partial(T_GW1, a.gW1_part + (int64_t)blockIdx.x * HH * HH, 1.f, any, tid);
-    store_wgrad_partial(T_GW2, a.gW2_part + (int64_t)blockIdx.x * HH * HH, a.beta, any, tid);
-    cta_column_sums(G_hi, accb1, a.gb1_part + (int64_t)blockIdx.x * HH, 1.f, tid);
-    cta_column_sums(G_hi, accb2, a.gb2_part + (int64_t)blockIdx.x * HH, a.beta, tid);
+    if (active) {
+        const bool any = it > 0;
+        store_wgrad_partial(T_GW1, a.gW1_part + v0 * HH * HH, 1.f, any, lt);
+        store_wgrad_partial(T_GW2, a.gW2_part + v0 * HH * HH, a.beta, any, lt);
+        group_column_sums(G_hi, accb1, a.gb1_part + v0 * HH, 1.f, lt, grp);
+        group_column_sums(G_hi, accb2, a.gb2_part + v0 * HH, a.beta, lt, grp);
+    }
     fence_before();
     __syncthreads();
-    if (warp == 0) tmem_dealloc(tm, 256);
+    if (warp == 0) tmem_dealloc(tmem_base_s, 512);
 }
 
 int launch_upd_bwd_umma(int64_t E, const float* g_out, const float* h, const float* e, const int32_t* src, const int32_t* dst,
@@ -229,9 +316,9 @@ int launch_upd_bwd_umma(int64_t E, const float* g_out, const float* h, const flo
                         float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part,
                         const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st) {
     UpdBwdUArgs a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, g_eid, e_eid};
-    const size_t smem = 4 * RT::BYTES + 4 * WT::BYTES + 1024;
+    const size_t smem = 8 * dual::RG_T::BYTES + 4 * WT::BYTES + 1024;
     B200MP_CUDA(cudaFuncSetAttribute(edge_update_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    edge_update_bwd_umma_kernel<<<n_part, NTB, smem, st>>>(a);
+    edge_update_bwd_umma_kernel<<<(n_part + 1) / 2, NTB, smem, st>>>(a, n_part);   // two 64-edge pipelines (partial rows) per CTA
     B200MP_LAUNCH_CHECK();
     return 0;
 }

@@ -176,7 +176,8 @@ extern "C" int b200mp_partial_rows(int* rows) {
 
 extern "C" int b200mp_partial_rows_for(int H, int* rows) {
     if (!rows) return B200MP_EINVAL;
-    *rows = (H == 64 && use_tensor_cores()) ? device_info().sms : device_info().sms * 2;   // tensor-core kernels: one CTA per SM
+    (void)H;
+    *rows = device_info().sms * 2;             // tensor-core kernels: two 64-edge pipelines per CTA, one CTA per SM
     return 0;
 }
 
