@@ -132,6 +132,20 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel, workload, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the committed ncu
+    --set full capture of this workload (profiles/traffic.json, written by scripts/ncu_traffic.py);
+    None when there is no capture for this kernel / workload / partitioning."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        if t.get("workload") != workload or world != 1:
+            return None
+        return t["kernels"][kernel]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def cpu_reference_steps(kind, steps, warmup, threads=None):
     """The CPU restatement of the reference path (oracle/models.py: reference model files'
     layer loop over restated PyG ops), fwd+bwd, on a bounded sample of the workload shape:
@@ -280,7 +294,7 @@ def run_b200(args, rank, world, local_rank):
     top = max(((k, v) for k, v in summ.items() if k in KERNEL_BYTES), key=lambda kv: kv[1][1])[0]
     achieved = kern[top]["achieved_gbs"]
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "frac": round(achieved / peak, 4), "traffic": ncu_traffic(top, args.workload, world), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": KERNEL_BYTES[top] * e_loc}
     step_bytes = LAYERS * (e_loc * algorithmic_bytes_per_edge(args.model) + n_loc * 12 * 4 * H)
     step_roofline = {"algorithmic_bytes_per_step": step_bytes, "achieved_gbs": round(step_bytes / (ms_step * 1e-3) / 1e9, 1),

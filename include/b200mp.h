@@ -175,6 +175,36 @@ int b200mp_edge_update_bwd(int H, int64_t E,
                            float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part,
                            int n_part, const int32_t* g_eid, const int32_t* e_eid, void* stream);
 
+/* ------------------------------------------------------------------ batch construction
+ * Negative sampler (replaces src/primitives/negative_sampling/negative_sampling.cpp:10-76, the
+ * reference's only native component, called at src/utils/batch_processing.py:145).  edge_index [2,E]
+ * and pos [2,B] are int64 device arrays of batch-local node ids (< 2^31).  Per positive (src, dst):
+ * num_neg/2 edges (src, n) then num_neg/2 edges (n, dst); n uniform on [0, num_nodes) excluding src, dst
+ * and the undirected neighbours of src and dst in edge_index.  num_nodes <= 0: the number of distinct
+ * ids in edge_index (what the reference's nodeset.size() is).  neg: [2, B * 2 * (num_neg/2)].  The draw
+ * is a hash of (seed, output slot, attempt): reproducible (the reference's std::random_device is not).
+ * num_neg <= 0 -> B200MP_EINVAL (reference: std::invalid_argument). */
+int b200mp_negative_sample_workspace_bytes(int64_t E, size_t* bytes);
+int b200mp_negative_sample(const int64_t* edge_index, int64_t E, int64_t num_nodes, const int64_t* pos, int64_t B,
+                           int num_neg, uint64_t seed, int64_t* neg, void* workspace, size_t workspace_bytes,
+                           void* stream);
+
+/* CSC neighbour sampler, one hop (PyG NeighborSampler.sample_from_edges / pyg-lib neighbor_sample as
+ * reached from src/datasets/ibm_transactions_for_aml.py:88-102; fan-out [100,100], non-disjoint, no
+ * replacement).  For frontier nodes f[0..F) in order: take[i] = min(in-degree, fanout) (fanout < 0: all);
+ * after the caller's exclusive scan `offs`, out_pos[offs[i] + j] = CSC positions of the taken in-edges:
+ * the whole slice in slice order when deg <= fanout (bit-exact), else `fanout` distinct positions drawn
+ * with Floyd's algorithm from a hash of (seed, node).
+ * b200mp_first_occurrence: flags[k] = 1 iff cand[k] is an unvisited node and k is the first position
+ * holding it (discovery order of the next frontier); marks those nodes visited.  visited: [N] bytes,
+ * first: [N] scratch preset to 0xFF..FF (left in that state). */
+int b200mp_sample_hop_count(const int64_t* colptr, const int64_t* frontier, int64_t F, int64_t fanout, int64_t* take,
+                            void* stream);
+int b200mp_sample_hop_fill(const int64_t* colptr, const int64_t* frontier, int64_t F, int64_t fanout,
+                           const int64_t* offs, uint64_t seed, int64_t* out_pos, void* stream);
+int b200mp_first_occurrence(const int64_t* cand, int64_t K, uint8_t* visited, uint64_t* first, uint8_t* flags,
+                            void* stream);
+
 /* ------------------------------------------------------------------ tensor-core self test
  * One-CTA check of the tcgen05 building blocks (csrc/umma.cuh) used by the per-edge kernels:
  *   mode 0: Y[128,64] = X[128,64] W[64,64]^T     mode 1: Y = X W      (3xTF32)

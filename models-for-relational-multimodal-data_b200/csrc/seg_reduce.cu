@@ -128,8 +128,12 @@ __global__ void __launch_bounds__(NT) seg_light_kernel(int64_t N, const int64_t*
     const int lane = threadIdx.x & 31;
     const int g = lane / LPR, c = (lane % LPR) * 4;
     const int64_t warps = (int64_t)gridDim.x * (NT / 32);
-    for (int64_t node = (int64_t)blockIdx.x * (NT / 32) + (threadIdx.x >> 5); node < N; node += warps) {
-        const int64_t begin = __ldg(ptr + node), end = __ldg(ptr + node + 1);
+    int64_t node = (int64_t)blockIdx.x * (NT / 32) + (threadIdx.x >> 5);
+    int64_t nb = 0, ne = 0;
+    if (node < N) { nb = __ldg(ptr + node); ne = __ldg(ptr + node + 1); }
+    for (; node < N; node += warps) {
+        const int64_t begin = nb, end = ne;
+        if (node + warps < N) { nb = __ldg(ptr + node + warps); ne = __ldg(ptr + node + warps + 1); }   // next segment's bounds in flight
         if (end - begin > light_max) continue;          // handled by the heavy path
         Acc<STATS> a;
         a.init();

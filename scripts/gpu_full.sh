@@ -11,6 +11,15 @@ CMD="python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 echo "ncu list rc=$?"
 CMD2="python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline --workload hi_small"
-$CMD2 > gpurun_out/plain2.log 2>&1 && timeout 900 ncu --set full --clock-control none --import-source on -k regex:'umma|seg_light' -s ${SKIP:-60} -c ${COUNT:-20} -f -o gpurun_out/prof_small $CMD2 > gpurun_out/ncu_full.log 2>&1
+$CMD2 > gpurun_out/plain2.log 2>&1 && timeout 900 ncu --set full --clock-control none --import-source on -k regex:'umma|seg_light' -s ${SKIP:-48} -c ${COUNT:-9} -f -o gpurun_out/prof_small $CMD2 > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"; tail -2 gpurun_out/ncu_full.log
-ls -la gpurun_out
+# reports are too big to travel back (64 MiB cap): export the pages here, drop the .ncu-rep
+ncu -i gpurun_out/prof_small.ncu-rep --page raw --csv > gpurun_out/prof_small_raw.csv 2>/dev/null
+ncu -i gpurun_out/prof_small.ncu-rep --page source --csv --print-source sass > gpurun_out/prof_small_src.csv 2>/dev/null
+rm -f gpurun_out/prof_small.ncu-rep
+# DRAM traffic of the per-edge kernels at the bench workload itself (one timed step: launches after the 3 warm-ups)
+timeout 900 ncu --set full --clock-control none -k regex:'umma_kernel|seg_light' -s ${TSKIP:-48} -c 14 -f -o gpurun_out/prof_medium $CMD > gpurun_out/ncu_medium.log 2>&1
+echo "ncu medium rc=$?"; tail -2 gpurun_out/ncu_medium.log
+ncu -i gpurun_out/prof_medium.ncu-rep --page raw --csv > gpurun_out/prof_medium_raw.csv 2>/dev/null
+rm -f gpurun_out/prof_medium.ncu-rep
+du -sh gpurun_out; ls -la gpurun_out
