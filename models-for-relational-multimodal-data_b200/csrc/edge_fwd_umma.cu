@@ -71,11 +71,15 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
     uint32_t it = 0;
     RowRegs<NTH> R, G;
     int nrows_pf = 0, idx_pf = 0;             // thread tid < 256: index (tid / 128) of row tid % 128, one tile ahead
+    RowIds<NTH> eids;                         // a.eid: storage rows of the tile AFTER the next one (two tiles ahead)
     const int32_t* idx_src = ch == 0 ? a.idx1 : ch == 1 ? a.idx2 : nullptr;
     if ((int64_t)blockIdx.x < ntiles) {
         nrows_pf = (int)min64(TE, a.E - (int64_t)blockIdx.x * TE);
         load_rows(R, a.e, a.eid, (int64_t)blockIdx.x * TE, nrows_pf, tid);
         if (idx_src) idx_pf = __ldg(idx_src + (int64_t)blockIdx.x * TE + min(t, nrows_pf - 1));
+        if (a.eid && (int64_t)blockIdx.x + gridDim.x < ntiles)
+            load_row_ids(eids, a.eid, ((int64_t)blockIdx.x + gridDim.x) * TE,
+                         (int)min64(TE, a.E - ((int64_t)blockIdx.x + gridDim.x) * TE), tid);
     }
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
@@ -93,13 +97,25 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
             gemm3_data(tm, E_hi, E_lo, W1_hi, W1_lo, 0);
             mma_commit(&sync.bar[0]);
         }
-        gather_rows(G, a.T1, sidx[0], a.T2, sidx[1], tid);   // coalesced, in flight while the MMAs run
+        RowRegs<NTH> G2;                     // mode 2 (registers to spare): the add waits until the prefetch is issued
+        if (MODE == 2) gather_rows_issue(G, G2, a.T1, sidx[0], a.T2, sidx[1], tid);
+        else gather_rows(G, a.T1, sidx[0], a.T2, sidx[1], tid);   // coalesced, in flight while the MMAs run
         RowRegs<NTH> Rn;                     // mode 2 keeps this tile's e rows for the residual
         int nrows_next = 0;
         if (tile + gridDim.x < ntiles) {     // next tile's e rows in flight
-            nrows_next = (int)min64(TE, a.E - (tile + gridDim.x) * TE);
-            load_rows(MODE == 2 ? Rn : R, a.e, a.eid, (tile + gridDim.x) * TE, nrows_next, tid);
-            if (idx_src) idx_pf = __ldg(idx_src + (tile + gridDim.x) * TE + min(t, nrows_next - 1));
+            const int64_t nt = tile + gridDim.x;
+            nrows_next = (int)min64(TE, a.E - nt * TE);
+            if (a.eid) {
+                load_rows_by_id(MODE == 2 ? Rn : R, a.e, eids, tid);       // ids were fetched a tile ago
+                if (nt + gridDim.x < ntiles) load_row_ids(eids, a.eid, (nt + gridDim.x) * TE, (int)min64(TE, a.E - (nt + gridDim.x) * TE), tid);
+            } else {
+                load_rows(MODE == 2 ? Rn : R, a.e, nullptr, nt * TE, nrows_next, tid);
+            }
+            if (idx_src) idx_pf = __ldg(idx_src + nt * TE + min(t, nrows_next - 1));
+        }
+        if (MODE == 2) {
+#pragma unroll
+            for (int i = 0; i < NP; ++i) G.v[i] = G.v[i] + G2.v[i];
         }
         mbar_wait(&sync.bar[0], par);
         fence_after();

@@ -99,6 +99,37 @@ __device__ __forceinline__ void gather_rows(RowRegs<NTH>& R, const float* __rest
 #pragma unroll
     for (int i = 0; i < NP; ++i) R.v[i] = R.v[i] + t[i];
 }
+// The same gather with the two tables kept apart (no add yet): lets the caller issue further loads
+// before the first use of these registers forces a wait on the gathered rows.
+template <int NTH>
+__device__ __forceinline__ void gather_rows_issue(RowRegs<NTH>& R1, RowRegs<NTH>& R2, const float* __restrict__ T1, const int* i1,
+                                                  const float* __restrict__ T2, const int* i2, int tid) {
+    constexpr int NP = RowRegs<NTH>::NP;
+    const int j = tid & 15, r0 = tid >> 4;
+#pragma unroll
+    for (int i = 0; i < NP; ++i) {
+        R1.v[i] = T1 ? ldg4(T1 + (int64_t)i1[r0 * NP + i] * HH + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        R2.v[i] = T2 ? ldg4(T2 + (int64_t)i2[r0 * NP + i] * HH + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+// Row ids of a tile through an optional map, and rows from precomputed ids: with the ids fetched one
+// tile earlier the row loads do not wait for an index load (one DRAM latency instead of two).
+template <int NTH>
+struct RowIds { int v[RowRegs<NTH>::NP]; };
+template <int NTH>
+__device__ __forceinline__ void load_row_ids(RowIds<NTH>& I, const int32_t* __restrict__ rowmap, int64_t row0, int nrows, int tid) {
+    constexpr int NP = RowRegs<NTH>::NP;
+    const int r0 = tid >> 4;
+#pragma unroll
+    for (int i = 0; i < NP; ++i) I.v[i] = __ldg(rowmap + row0 + min(r0 * NP + i, nrows - 1));
+}
+template <int NTH>
+__device__ __forceinline__ void load_rows_by_id(RowRegs<NTH>& R, const float* __restrict__ src, const RowIds<NTH>& I, int tid) {
+    constexpr int NP = RowRegs<NTH>::NP;
+    const int j = tid & 15;
+#pragma unroll
+    for (int i = 0; i < NP; ++i) R.v[i] = ldg4(src + (int64_t)I.v[i] * HH + j * 4);
+}
 template <int NTH>
 __device__ __forceinline__ void store_rows_split(const RowRegs<NTH>& R, float* hi, float* lo, int nrows, int tid) {
     constexpr int NP = RowRegs<NTH>::NP;

@@ -83,6 +83,8 @@ def main():
         "msg_fwd(B[src] only)": lambda: fwd(0, None, T1, seg.nbr32, None, None),
         "upd_fwd(P[src]+Q[dst])": lambda: fwd(2, None, T1, st.src32, T2, st.dst32),
         "upd_fwd(no gathers)": lambda: fwd(2, None, None, None, None, None),
+        "msg_fwd(eid map)": lambda: fwd(0, seg.perm32(), T1, seg.nbr32, T2, seg.seg32),
+        "upd_fwd(eid map)": lambda: fwd(2, seg.perm32(), T1, st.src32, T2, st.dst32),
         "upd_bwd(gP+gQ)": lambda: updb(st.src32, st.dst32, gP, gQ),
         "upd_bwd(gQ only)": lambda: updb(st.src32, st.dst32, None, gQ),
         "upd_bwd(gP only)": lambda: updb(st.src32, st.dst32, gP, None),
