@@ -26,10 +26,13 @@ struct Acc {
     }
     static __device__ __forceinline__ void add1(float v, float& s, float& q, float& mn, float& cn, float& mx, float& cx) {
         s += v;
-        if (STATS) {
+        if (STATS) {                       // branch free: the lanes of a warp hold different columns and would diverge
             q = fmaf(v, v, q);
-            if (v < mn) { mn = v; cn = 1.f; } else if (v == mn) cn += 1.f;
-            if (v > mx) { mx = v; cx = 1.f; } else if (v == mx) cx += 1.f;
+            const float nmn = fminf(mn, v), nmx = fmaxf(mx, v);
+            cn = (v == nmn) ? ((nmn == mn) ? cn + 1.f : 1.f) : cn;
+            cx = (v == nmx) ? ((nmx == mx) ? cx + 1.f : 1.f) : cx;
+            mn = nmn;
+            mx = nmx;
         }
     }
     __device__ __forceinline__ void add(float4 v) {
@@ -43,8 +46,11 @@ struct Acc {
         s += os;
         if (STATS) {
             q += oq;
-            if (omn < mn) { mn = omn; cn = ocn; } else if (omn == mn) cn += ocn;
-            if (omx > mx) { mx = omx; cx = ocx; } else if (omx == mx) cx += ocx;
+            const float nmn = fminf(mn, omn), nmx = fmaxf(mx, omx);
+            cn = (omn == nmn ? ocn : 0.f) + (mn == nmn ? cn : 0.f);
+            cx = (omx == nmx ? ocx : 0.f) + (mx == nmx ? cx : 0.f);
+            mn = nmn;
+            mx = nmx;
         }
     }
     __device__ __forceinline__ void merge(const Acc& o) {
