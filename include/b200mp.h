@@ -87,6 +87,11 @@ int b200mp_node_linear(const float* X, int64_t N, int K, int ldx, const float* W
  * (K % 128 == 0, NO in {64,128,192,256}); the caller sums the n_part partials (deterministic). */
 int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const float* Y, int ldy, int NO, int64_t N,
                              float* part, int n_part, void* stream);
+/* Several H = 64 node linears in one pass: X = [X0 | X1 | X2] (nx blocks of [N,64], e.g. the gradients of
+ * A | B | out0), Y = X W^T + bias, NO in {64,128,192,256}; ysplit != 0 writes Y as NO/64 separate [N,64]
+ * blocks (A, B, out0 of PNAConv's hoisted pre_nn / post_nn self term; P, Q of the edge update). */
+int b200mp_node_linear64(const float* X0, const float* X1, const float* X2, int nx, int64_t N, const float* Wimg,
+                         int NO, const float* bias, float* Y, int ysplit, void* stream);
 /* Weight gradients of two H = 64 node linears sharing their input Y (PNAConv pre_nn halves A | B, edge
  * update halves P | Q, pna.py:71-84): part[p][0:64] = G0^T Y, part[p][64:128] = G1^T Y; all [N,64]. */
 int b200mp_node_pair_wgrad(const float* G0, const float* G1, const float* Y, int64_t N, float* part, int n_part,

@@ -36,6 +36,8 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 struct NodeLinArgs {
     int64_t N; int K; int ldx;
     const float* X; const float* Wimg; const float* bias; float* Y;
+    const float* X1; const float* X2;         // segmented input: columns 64 s .. 64 s + 63 of X come from X<s>, each [N, 64]
+    int ysplit;                               // output as NO / 64 separate [N, 64] blocks (Y + g N 64) instead of [N, NO]
 };
 }  // namespace ng
 using namespace ng;
@@ -48,7 +50,7 @@ __global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a)
     float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;
     float* X_hi = smem;
     float* X_lo = X_hi + XP::FLOATS;
-    float* W_hi = X_lo + XP::FLOATS;          // weight chunk; staging tile in the epilogue (needs 32 KB: NO >= 128)
+    float* W_hi = X_lo + XP::FLOATS;          // weight chunk; staging tile in the epilogue (the buffer is >= 32 KB)
     float* W_lo = W_hi + W_PART;
     __shared__ uint64_t bar_w, bar_m;
     __shared__ uint32_t tmem_base;
@@ -57,7 +59,7 @@ __global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a)
     const int t = tid & (TE - 1), ch = tid >> 7;           // tensor-memory side: row t, 32 columns
     const int j8 = tid & 7, g8 = tid >> 3;                 // chunk loads: 16-byte piece j8 of rows 4 g8 .. 4 g8 + 3
     const int j = tid & 15, g = tid >> 4;                  // output rows: 16-byte chunk j of rows 8 g .. 8 g + 7
-    constexpr uint32_t NCOLS = NO <= 128 ? 128 : 256;
+    constexpr uint32_t NCOLS = NO <= 64 ? 64 : NO <= 128 ? 128 : 256;
     if (warp == 0) tmem_alloc(&tmem_base, NCOLS);
     if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_m, 1); mbar_fence_init(); }
     fence_before();
@@ -76,7 +78,9 @@ __global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a)
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int rc = min(g8 * 4 + i, nr - 1);
-            xr[i] = ldg4(a.X + (r0 + rc) * a.ldx + c_ * KCH + j8 * 4);
+            const float* xb = a.X1 ? (c_ < 2 ? a.X : c_ < 4 ? a.X1 : a.X2) + (r0 + rc) * 64 + (c_ & 1) * KCH
+                                   : a.X + (r0 + rc) * a.ldx + c_ * KCH;
+            xr[i] = ldg4(xb + j8 * 4);
         }
     };
     if ((int64_t)blockIdx.x < ntiles) load_chunk(blockIdx.x, 0);
@@ -124,7 +128,8 @@ __global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a)
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int r = g * 8 + i;
-                if (r < nrows) st4(a.Y + (row0 + r) * NO + grp * 64 + j * 4, lds4(stage + stage_off(r, j)) + b4);
+                float* yo = a.ysplit ? a.Y + ((int64_t)grp * a.N + row0 + r) * 64 : a.Y + (row0 + r) * NO + grp * 64;
+                if (r < nrows) st4(yo + j * 4, lds4(stage + stage_off(r, j)) + b4);
             }
             __syncthreads();
         }
@@ -140,7 +145,8 @@ __global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a)
 
 template <int NO>
 static int launch_node_linear(const NodeLinArgs& a, cudaStream_t st) {
-    const size_t smem = 2 * XP::BYTES + 2 * NO * KCH * 4 + 1024;
+    const size_t wbuf = 2 * NO * KCH * 4;
+    const size_t smem = 2 * XP::BYTES + (wbuf > 32768 ? wbuf : 32768) + 1024;
     auto kern = node_linear_umma_kernel<NO>;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ntiles = (a.N + TE - 1) / TE;
@@ -272,7 +278,7 @@ extern "C" int b200mp_node_linear(const float* X, int64_t N, int K, int ldx, con
     using namespace b200mp;
     if (N < 0 || K <= 0 || K % 32 || ldx < K || ldx % 4 || !X || !Wimg || !Y) return B200MP_EINVAL;
     if (N == 0) return 0;
-    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y};
+    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0};
     cudaStream_t st = (cudaStream_t)stream;
     switch (NO) {
         case 128: return launch_node_linear<128>(a, st);
@@ -306,4 +312,22 @@ extern "C" int b200mp_node_pair_wgrad(const float* G0, const float* G1, const fl
     if (N <= 0 || n_part <= 0 || !G0 || !G1 || !Y || !part) return B200MP_EINVAL;
     NodeWgArgs a{N, 64, 64, G0, Y, part, 128, G1};
     return launch_node_wgrad<64>(a, n_part, (cudaStream_t)stream);
+}
+
+/* H = 64 node linears sharing their rows: X = [X0 | X1 | X2] (nx blocks of [N,64]), Y = X W^T + bias with
+ * NO in {64,128,192,256}; ysplit: Y as NO/64 separate [N,64] blocks. */
+extern "C" int b200mp_node_linear64(const float* X0, const float* X1, const float* X2, int nx, int64_t N, const float* Wimg,
+                                    int NO, const float* bias, float* Y, int ysplit, void* stream) {
+    using namespace b200mp;
+    if (N < 0 || nx < 1 || nx > 3 || !X0 || (nx > 1 && !X1) || (nx > 2 && !X2) || !Wimg || !Y) return B200MP_EINVAL;
+    if (N == 0) return 0;
+    NodeLinArgs a{N, 64 * nx, 64, X0, Wimg, bias, Y, nx > 1 ? X1 : X0, nx > 2 ? X2 : X0, ysplit};
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (NO) {
+        case 64: return launch_node_linear<64>(a, st);
+        case 128: return launch_node_linear<128>(a, st);
+        case 192: return launch_node_linear<192>(a, st);
+        case 256: return launch_node_linear<256>(a, st);
+    }
+    return B200MP_EINVAL;
 }

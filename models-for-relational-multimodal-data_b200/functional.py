@@ -257,6 +257,20 @@ def _node_pair_wgrad(g0, g1, x):
     return G[:64], G[64:]
 
 
+def _node_linear64(xs, Wcat, bias, ysplit):
+    """[x_0 | x_1 | ..] Wcat^T + bias for [N,64] blocks on the tcgen05 node kernel; ysplit: the result as
+    Wcat.shape[0] / 64 separate contiguous [N,64] tensors."""
+    N, NO = xs[0].shape[0], Wcat.shape[0]
+    dev = xs[0].device
+    y = torch.empty((NO // 64, N, 64) if ysplit else (N, NO), dtype=torch.float32, device=dev)
+    img = _w_image(Wcat)
+    px = [L.ptr(t) for t in xs] + [None] * (3 - len(xs))
+    with torch.cuda.device(dev), _track("node_linear64"):
+        L.check(L.lib().b200mp_node_linear64(px[0], px[1], px[2], len(xs), N, L.ptr(img), NO, L.ptr(bias), L.ptr(y),
+                                             1 if ysplit else 0, L.stream()), "b200mp_node_linear64")
+    return list(y.unbind(0)) if ysplit else y
+
+
 class _LinearGroup(torch.autograd.Function):
     """y_i = x W_i^T + b_i for several H x H node linears over the SAME input (PNAConv's hoisted
     pre_nn halves and post_nn self term, the edge update's P | Q).  Forward: fp32 library GEMMs
@@ -271,6 +285,12 @@ class _LinearGroup(torch.autograd.Function):
         Ws, bs = params[:n], params[n:]
         ctx.n = n
         ctx.save_for_backward(x, *Ws)
+        ctx.kernel_ok = x.shape[0] >= 4096 and x.shape[1] == 64 and n <= 3 and all(W.shape == (64, 64) for W in Ws)
+        if ctx.kernel_ok:                    # one pass over x for all outputs (tcgen05, 3xTF32)
+            bias = None
+            if any(b is not None for b in bs):
+                bias = torch.cat([b if b is not None else x.new_zeros(64) for b in bs])
+            return tuple(_node_linear64([x], torch.cat(list(Ws), 0), bias, True))
         return tuple(torch.nn.functional.linear(x, W, b) for W, b in zip(Ws, bs))
 
     @staticmethod
@@ -280,9 +300,13 @@ class _LinearGroup(torch.autograd.Function):
         gs = [None if g is None else _f32c(g) for g in gs]
         gx = None
         if ctx.needs_input_grad[0]:
-            for g, W in zip(gs, Ws):
-                if g is not None:
-                    gx = g @ W if gx is None else gx.addmm_(g, W)
+            if ctx.kernel_ok and all(g is not None for g in gs):
+                # gx = [g_0 | g_1 | ..] [W_0; W_1; ..]: one pass over the gradients, no separate adds
+                gx = _node_linear64(gs, torch.cat(list(Ws), 0).t(), None, False)
+            else:
+                for g, W in zip(gs, Ws):
+                    if g is not None:
+                        gx = g @ W if gx is None else gx.addmm_(g, W)
         gW = [None] * n
         want = [i for i in range(n) if gs[i] is not None and ctx.needs_input_grad[2 + i]]
         kernel_ok = x.shape[0] >= 4096 and x.shape[1] == 64 and all(Ws[i].shape == (64, 64) for i in want)
