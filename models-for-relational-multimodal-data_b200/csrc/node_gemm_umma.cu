@@ -43,16 +43,20 @@ struct NodeLinArgs {
 using namespace ng;
 
 // Wimg: [K / 32][2 (hi, lo)][8 (16-byte k chunk)][NO][4] floats
+//
+// Pipeline (one CTA per SM, everything double buffered): chunk c's weights are bulk-copied while chunk
+// c - 1's MMAs run, and chunk c's X panel is split and stored while they run too -- the serial version
+// (two CTAs per SM, single buffers) spent ~3.4 us per chunk for 0.6 us of tensor work, mostly waiting for
+// the 48-64 KB weight copy from L2.
 template <int NO>
-__global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a) {
+__global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a) {
     constexpr int W_PART = NO * KCH;                       // floats per hi (or lo) weight chunk
+    constexpr int W_BUF = 2 * W_PART;                      // hi + lo
     extern __shared__ __align__(128) float smem_raw[];
     float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;
-    float* X_hi = smem;
-    float* X_lo = X_hi + XP::FLOATS;
-    float* W_hi = X_lo + XP::FLOATS;          // weight chunk; staging tile in the epilogue (the buffer is >= 32 KB)
-    float* W_lo = W_hi + W_PART;
-    __shared__ uint64_t bar_w, bar_m;
+    float* Xb = smem;                         // [2][hi | lo] X panels, 64 KB; the first 32 KB double as the epilogue's staging tile
+    float* Wb = Xb + 4 * XP::FLOATS;          // [2][hi | lo] weight chunks
+    __shared__ uint64_t bar_w[2], bar_m[2];
     __shared__ uint32_t tmem_base;
 
     const int tid = threadIdx.x, warp = tid >> 5;
@@ -61,7 +65,10 @@ __global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a)
     const int j = tid & 15, g = tid >> 4;                  // output rows: 16-byte chunk j of rows 8 g .. 8 g + 7
     constexpr uint32_t NCOLS = NO <= 64 ? 64 : NO <= 128 ? 128 : 256;
     if (warp == 0) tmem_alloc(&tmem_base, NCOLS);
-    if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_m, 1); mbar_fence_init(); }
+    if (tid == 0) {
+        mbar_init(&bar_w[0], 1); mbar_init(&bar_w[1], 1); mbar_init(&bar_m[0], 1); mbar_init(&bar_m[1], 1);
+        mbar_fence_init();
+    }
     fence_before();
     __syncthreads();
     fence_after();
@@ -69,57 +76,93 @@ __global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a)
     const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
     const int nchunks = a.K / KCH;
     const int64_t ntiles = (a.N + TE - 1) / TE;
-    uint32_t phase = 0;                        // both barriers complete once per chunk
+    const int64_t my_tiles = (int64_t)blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int64_t total = my_tiles * nchunks;              // chunks this CTA walks, numbered gc = 0 .. total - 1
 
-    float4 xr[4];
-    auto load_chunk = [&](int64_t tile_, int c_) {
-        const int64_t r0 = tile_ * TE;
+    // X chunks are prefetched PF chunks ahead in registers (PF = 3 measured no faster than 1: the loop is
+    // bound by the issue -> commit -> wait chain of one chunk's MMAs, not by the loads)
+    constexpr int PF = 1;
+    float4 xr[PF][4];
+    int64_t pf_tile = blockIdx.x;             // prefetch cursor: next chunk to load
+    int pf_c = 0;
+    auto load_next = [&](float4 (&dst)[4]) {
+        if (pf_tile >= ntiles) return;
+        const int64_t r0 = pf_tile * TE;
         const int nr = (int)min64(TE, a.N - r0);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int rc = min(g8 * 4 + i, nr - 1);
-            const float* xb = a.X1 ? (c_ < 2 ? a.X : c_ < 4 ? a.X1 : a.X2) + (r0 + rc) * 64 + (c_ & 1) * KCH
-                                   : a.X + (r0 + rc) * a.ldx + c_ * KCH;
-            xr[i] = ldg4(xb + j8 * 4);
+            const float* xb = a.X1 ? (pf_c < 2 ? a.X : pf_c < 4 ? a.X1 : a.X2) + (r0 + rc) * 64 + (pf_c & 1) * KCH
+                                   : a.X + (r0 + rc) * a.ldx + pf_c * KCH;
+            dst[i] = ldg4(xb + j8 * 4);
         }
+        if (++pf_c == nchunks) { pf_c = 0; pf_tile += gridDim.x; }
     };
-    if ((int64_t)blockIdx.x < ntiles) load_chunk(blockIdx.x, 0);
+    auto issue_w = [&](int64_t gc_) {         // one thread: weights of global chunk gc_ -> buffer gc_ & 1
+        const int b = (int)(gc_ & 1);
+        mbar_expect_tx(&bar_w[b], W_BUF * 4);
+        bulk_g2s(Wb + b * W_BUF, a.Wimg + (size_t)(gc_ % nchunks) * W_BUF, W_BUF * 4, &bar_w[b]);
+    };
+    if (total > 0) {
+#pragma unroll
+        for (int k = 0; k < PF; ++k) load_next(xr[k]);
+        if (tid == 0) issue_w(0);
+    }
 
+    int64_t gc = 0;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int64_t row0 = tile * TE;
         const int nrows = (int)min64(TE, a.N - row0);
-        for (int c = 0; c < nchunks; ++c, phase ^= 1) {
-            if (tid == 0) {                    // the previous chunk's MMAs (readers of W_hi / W_lo) are done
-                mbar_expect_tx(&bar_w, 2 * W_PART * 4);
-                bulk_g2s(W_hi, a.Wimg + (size_t)c * 2 * W_PART, 2 * W_PART * 4, &bar_w);
+        for (int c = 0; c < nchunks; ++c, ++gc) {
+            const int b = (int)(gc & 1);
+            const uint32_t ph = (uint32_t)((gc >> 1) & 1);            // phase of buffer b's barriers at their use number gc / 2
+            float* X_hi = Xb + b * 2 * XP::FLOATS;
+            float* X_lo = X_hi + XP::FLOATS;
+            if (gc >= 2) {                     // the MMAs of chunk gc - 2 read X buffer b
+                mbar_wait(&bar_m[b], ph ^ 1);
+                fence_after();
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 const int r = g8 * 4 + i;
                 float4 h, l;
-                split4(r < nrows ? xr[i] : f4(0.f, 0.f, 0.f, 0.f), h, l);
+                split4(r < nrows ? xr[0][i] : f4(0.f, 0.f, 0.f, 0.f), h, l);
                 const int o = XP::off(r, j8);
                 st4(X_hi + o, h);
                 st4(X_lo + o, l);
             }
-            if (c + 1 < nchunks) load_chunk(tile, c + 1);
-            else if (tile + gridDim.x < ntiles) load_chunk(tile + gridDim.x, 0);
+#pragma unroll
+            for (int k = 0; k + 1 < PF; ++k) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) xr[k][i] = xr[k + 1][i];
+            }
+            load_next(xr[PF - 1]);
+            if (tid == 0 && gc + 1 < total) {  // next chunk's weights -> the other buffer, free once chunk gc - 1's MMAs are done
+                if (gc >= 1) mbar_wait(&bar_m[b ^ 1], (uint32_t)(((gc - 1) >> 1) & 1));
+                issue_w(gc + 1);
+            }
             fence_async_smem();
             fence_before();
             __syncthreads();
             fence_after();
             if (tid == 0) {
-                mbar_wait(&bar_w, phase);
+                mbar_wait(&bar_w[b], ph);
+                const float* W_hi = Wb + b * W_BUF;
+                const float* W_lo = W_hi + W_PART;
                 issue_data_gemm_row32<TE, NO, KCH>(tm, smem_u32(X_lo), smem_u32(W_hi), c > 0);
                 issue_data_gemm_row32<TE, NO, KCH>(tm, smem_u32(X_hi), smem_u32(W_lo), 1);
                 issue_data_gemm_row32<TE, NO, KCH>(tm, smem_u32(X_hi), smem_u32(W_hi), 1);
-                mma_commit(&bar_m);
+                mma_commit(&bar_m[b]);
             }
-            mbar_wait(&bar_m, phase);
+        }
+        // ---- epilogue: all MMAs of the tile done (the last two commits cover both X buffers)
+        {
+            const int64_t last = gc - 1;
+            mbar_wait(&bar_m[last & 1], (uint32_t)((last >> 1) & 1));
+            if (last >= 1) mbar_wait(&bar_m[(last - 1) & 1], (uint32_t)(((last - 1) >> 1) & 1));
             fence_after();
         }
-        // ---- epilogue: 64 output columns at a time through the staging tile, coalesced rows out
-        float* stage = W_hi;
+        float* stage = Xb;
 #pragma unroll 1
         for (int grp = 0; grp < NO / 64; ++grp) {
             stage_from_tmem<NT2>(tm + lane_off + grp * 64 + ch * 32, stage, t, ch);
@@ -133,7 +176,6 @@ __global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a)
             }
             __syncthreads();
         }
-        fence_async_smem();                    // generic-proxy use of the weight buffer ends before the next bulk copy
         fence_before();
         __syncthreads();
         fence_after();
@@ -145,8 +187,7 @@ __global__ void __launch_bounds__(NT2, 2) node_linear_umma_kernel(NodeLinArgs a)
 
 template <int NO>
 static int launch_node_linear(const NodeLinArgs& a, cudaStream_t st) {
-    const size_t wbuf = 2 * NO * KCH * 4;
-    const size_t smem = 2 * XP::BYTES + (wbuf > 32768 ? wbuf : 32768) + 1024;
+    const size_t smem = 4 * XP::BYTES + 2 * (2 * NO * KCH * 4) + 1024;    // X panels and weight chunks, double buffered
     auto kern = node_linear_umma_kernel<NO>;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ntiles = (a.N + TE - 1) / TE;
