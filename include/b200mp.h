@@ -180,6 +180,18 @@ int b200mp_edge_update_bwd(int H, int64_t E,
                            float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part,
                            int n_part, const int32_t* g_eid, const int32_t* e_eid, void* stream);
 
+/* ------------------------------------------------------------------ column attention core
+ * softmax(Q K^T / sqrt(d)) V of nn.MultiheadAttention inside the reference's TransformerEncoderLayer
+ * (src/nn/models/tabgnn.py:199-209, fused.py:83-93,187-197, inteleaved.py:155) over column tokens:
+ * q, k, v, out, gradients: [R, S, C] fp32 contiguous, S <= 8, head_dim = C / nhead in {4, 8, 16}.
+ * p_drop: dropout on the attention probabilities (training), mask = hash(seed, row, head, i, j), the
+ * backward recomputes it from the same seed. */
+int b200mp_col_attention_fwd(const float* q, const float* k, const float* v, int64_t R, int S, int C, int nhead,
+                             float p_drop, uint64_t seed, float* out, void* stream);
+int b200mp_col_attention_bwd(const float* q, const float* k, const float* v, const float* g_out, int64_t R, int S,
+                             int C, int nhead, float p_drop, uint64_t seed, float* gq, float* gk, float* gv,
+                             void* stream);
+
 /* ------------------------------------------------------------------ batch construction
  * Negative sampler (replaces src/primitives/negative_sampling/negative_sampling.cpp:10-76, the
  * reference's only native component, called at src/utils/batch_processing.py:145).  edge_index [2,E]

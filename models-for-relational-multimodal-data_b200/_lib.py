@@ -46,6 +46,8 @@ _SIGS = {
     "b200mp_sample_hop_count": [_p, _p, _l, _l, _p, _p],
     "b200mp_sample_hop_fill": [_p, _p, _l, _l, _p, C.c_uint64, _p, _p],
     "b200mp_first_occurrence": [_p, _l, _p, _p, _p, _p],
+    "b200mp_col_attention_fwd": [_p, _p, _p, _l, _i, _i, _i, _f, C.c_uint64, _p, _p],
+    "b200mp_col_attention_bwd": [_p, _p, _p, _p, _l, _i, _i, _i, _f, C.c_uint64, _p, _p, _p, _p],
     "b200mp_umma_selftest": [_i, _p, _p, _p, _p],
     "b200mp_umma_probe": [_p, _i, _p, _i, C.c_uint64, C.c_uint64, _i, _i, _i, C.c_uint32, _p, _p],
     "b200mp_edge_update_bwd": [_i, _l, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p],

@@ -1,0 +1,221 @@
+// Column attention core of the FT-Transformer layers: the
+// softmax(Q K^T / sqrt(d)) V of torch.nn.MultiheadAttention inside nn.TransformerEncoderLayer as the
+// reference builds it (src/nn/models/tabgnn.py:199-209, fused.py:83-93,187-197, inteleaved.py:155:
+// d_model = C, nhead = 8, batch_first) over [rows, S, C] column tokens, S = K + 1 <= 8, head_dim = C / 8 (1, 2, 4, 8 or 16).
+// The projections around it (in_proj, out_proj, feed-forward) are [rows * S, 64] x 64 linears and run on
+// the tcgen05 node kernels (functional.linear_group); this file is the part between them.
+//
+// The sequences are tiny (S <= 8, d = 8 or 16), so nothing is tiled: one thread per (row, head, token),
+// operands read through L1 (the S threads of a (row, head) share them), everything else in registers.
+// Attention-probability dropout (the layer's dropout applies to them in training) uses a counter hash
+// of (seed, row, head, i, j), recomputed in backward -- no mask tensor.
+#include "common.cuh"
+
+namespace b200mp {
+
+__device__ __forceinline__ uint32_t hash32(uint64_t z) {
+    z += 0x9e3779b97f4a7c15ull;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return (uint32_t)((z ^ (z >> 31)) >> 32);
+}
+// keep-mask scale of probability (i, j): 0 or 1 / (1 - p)
+__device__ __forceinline__ float drop_scale(uint64_t seed, int64_t row, int head, int i, int j, float p, float inv_keep) {
+    if (p <= 0.f) return 1.f;
+    const uint32_t h = hash32(seed ^ ((uint64_t)row * 0x100000001b3ull + (uint64_t)((head * 8 + i) * 8 + j)));
+    return ((float)h * (1.0f / 4294967296.0f)) < p ? 0.f : inv_keep;
+}
+
+// HD contiguous floats to / from registers: 16-byte accesses when HD is a multiple of 4, else 8- or 4-byte
+template <int HD>
+__device__ __forceinline__ void ld_vec(float (&d)[HD], const float* __restrict__ p) {
+    if constexpr (HD % 4 == 0) {
+#pragma unroll
+        for (int c = 0; c < HD; c += 4) { const float4 x = ldg4(p + c); d[c] = x.x; d[c + 1] = x.y; d[c + 2] = x.z; d[c + 3] = x.w; }
+    } else if constexpr (HD % 2 == 0) {
+#pragma unroll
+        for (int c = 0; c < HD; c += 2) { const float2 x = __ldg(reinterpret_cast<const float2*>(p + c)); d[c] = x.x; d[c + 1] = x.y; }
+    } else {
+#pragma unroll
+        for (int c = 0; c < HD; ++c) d[c] = __ldg(p + c);
+    }
+}
+template <int HD>
+__device__ __forceinline__ void st_vec(float* __restrict__ p, const float (&d)[HD]) {
+    if constexpr (HD % 4 == 0) {
+#pragma unroll
+        for (int c = 0; c < HD; c += 4) st4(p + c, f4(d[c], d[c + 1], d[c + 2], d[c + 3]));
+    } else if constexpr (HD % 2 == 0) {
+#pragma unroll
+        for (int c = 0; c < HD; c += 2) *reinterpret_cast<float2*>(p + c) = make_float2(d[c], d[c + 1]);
+    } else {
+#pragma unroll
+        for (int c = 0; c < HD; ++c) p[c] = d[c];
+    }
+}
+template <int HD>
+__device__ __forceinline__ float dot(const float* __restrict__ a, const float* __restrict__ b) {
+    float x[HD], y[HD], s = 0.f;
+    ld_vec<HD>(x, a); ld_vec<HD>(y, b);
+#pragma unroll
+    for (int c = 0; c < HD; ++c) s = fmaf(x[c], y[c], s);
+    return s;
+}
+// d += w * p[0..HD)
+template <int HD>
+__device__ __forceinline__ void axpy(float (&d)[HD], float w, const float* __restrict__ p) {
+    float x[HD];
+    ld_vec<HD>(x, p);
+#pragma unroll
+    for (int c = 0; c < HD; ++c) d[c] = fmaf(w, x[c], d[c]);
+}
+
+struct AttnArgs {
+    int64_t R; int S; int C; int nhead;
+    const float* q; const float* k; const float* v;       // [R, S, C] each
+    float p; uint64_t seed;
+};
+
+// out[r, i, h*HD : (h+1)*HD] = sum_j drop(softmax_j(q_i . k_j / sqrt(HD))) v_j
+template <int HD>
+__global__ void __launch_bounds__(256) col_attention_fwd_kernel(AttnArgs a, float* __restrict__ out) {
+    const int64_t tix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t total = a.R * a.S * a.nhead;
+    if (tix >= total) return;
+    const int h = (int)(tix % a.nhead);
+    const int i = (int)((tix / a.nhead) % a.S);
+    const int64_t r = tix / ((int64_t)a.nhead * a.S);
+    const float scale = rsqrtf((float)HD), inv_keep = a.p > 0.f ? 1.f / (1.f - a.p) : 1.f;
+    const int64_t base = r * a.S * a.C + h * HD;
+    const float* qi = a.q + base + (int64_t)i * a.C;
+    float s[8], m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        s[j] = j < a.S ? dot<HD>(qi, a.k + base + (int64_t)j * a.C) * scale : -INFINITY;
+        m = fmaxf(m, s[j]);
+    }
+    float l = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j] = j < a.S ? __expf(s[j] - m) : 0.f; l += s[j]; }
+    const float inv_l = 1.f / l;
+    float acc[HD];
+#pragma unroll
+    for (int c = 0; c < HD; ++c) acc[c] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        if (j < a.S) {
+            const float pj = s[j] * inv_l * drop_scale(a.seed, r, h, i, j, a.p, inv_keep);
+            const float* vj = a.v + base + (int64_t)j * a.C;
+            axpy<HD>(acc, pj, vj);
+        }
+    }
+    st_vec<HD>(out + base + (int64_t)i * a.C, acc);
+}
+
+// Thread (r, h, t): dQ_t, dK_t, dV_t.  With P = softmax rows, Pd = drop(P), dPd_ij = dO_i . v_j,
+// dP_ij = dPd_ij * dropscale_ij, D_i = sum_j P_ij dP_ij, dS_ij = P_ij (dP_ij - D_i):
+//   dQ_t = scale sum_j dS_tj k_j ,  dK_t = scale sum_i dS_it q_i ,  dV_t = sum_i Pd_it dO_i
+template <int HD>
+__global__ void __launch_bounds__(256) col_attention_bwd_kernel(AttnArgs a, const float* __restrict__ g_out,
+                                                                float* __restrict__ gq, float* __restrict__ gk,
+                                                                float* __restrict__ gv) {
+    const int64_t tix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t total = a.R * a.S * a.nhead;
+    if (tix >= total) return;
+    const int h = (int)(tix % a.nhead);
+    const int t = (int)((tix / a.nhead) % a.S);
+    const int64_t r = tix / ((int64_t)a.nhead * a.S);
+    const float scale = rsqrtf((float)HD), inv_keep = a.p > 0.f ? 1.f / (1.f - a.p) : 1.f;
+    const int64_t base = r * a.S * a.C + h * HD;
+    float dq[HD], dk[HD], dv[HD];
+#pragma unroll
+    for (int c = 0; c < HD; ++c) dq[c] = dk[c] = dv[c] = 0.f;
+    for (int i = 0; i < a.S; ++i) {                        // row i of the attention matrix
+        const float* qi = a.q + base + (int64_t)i * a.C;
+        const float* gi = g_out + base + (int64_t)i * a.C;
+        float s[8], dp[8], m = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            s[j] = j < a.S ? dot<HD>(qi, a.k + base + (int64_t)j * a.C) * scale : -INFINITY;
+            m = fmaxf(m, s[j]);
+        }
+        float l = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s[j] = j < a.S ? __expf(s[j] - m) : 0.f; l += s[j]; }
+        const float inv_l = 1.f / l;
+        float D = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            s[j] *= inv_l;                                  // P_ij
+            dp[j] = j < a.S ? dot<HD>(gi, a.v + base + (int64_t)j * a.C) * drop_scale(a.seed, r, h, i, j, a.p, inv_keep) : 0.f;
+            D = fmaf(s[j], dp[j], D);
+        }
+        float p_it = 0.f, dp_it = 0.f;                      // column t of row i (register arrays need static indices)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { if (j == t) { p_it = s[j]; dp_it = dp[j]; } }
+        const float ds_it = p_it * (dp_it - D) * scale;
+        const float pd_it = p_it * drop_scale(a.seed, r, h, i, t, a.p, inv_keep);
+        axpy<HD>(dk, ds_it, qi);
+        axpy<HD>(dv, pd_it, gi);
+        if (i == t) {                                       // row t: dQ_t
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (j < a.S) {
+                    const float ds = s[j] * (dp[j] - D) * scale;
+                    axpy<HD>(dq, ds, a.k + base + (int64_t)j * a.C);
+                }
+            }
+        }
+    }
+    const int64_t o = base + (int64_t)t * a.C;
+    st_vec<HD>(gq + o, dq);
+    st_vec<HD>(gk + o, dk);
+    st_vec<HD>(gv + o, dv);
+}
+
+}  // namespace b200mp
+
+extern "C" int b200mp_col_attention_fwd(const float* q, const float* k, const float* v, int64_t R, int S, int C, int nhead,
+                                        float p_drop, uint64_t seed, float* out, void* stream) {
+    using namespace b200mp;
+    if (R < 0 || S < 1 || S > 8 || nhead < 1 || nhead > 16 || C % nhead || p_drop < 0.f || p_drop >= 1.f) return B200MP_EINVAL;
+    if (R == 0) return 0;
+    if (!q || !k || !v || !out) return B200MP_EINVAL;
+    AttnArgs a{R, S, C, nhead, q, k, v, p_drop, seed};
+    const int64_t total = R * S * nhead;
+    const unsigned grid = (unsigned)((total + 255) / 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (C / nhead) {
+        case 1: col_attention_fwd_kernel<1><<<grid, 256, 0, st>>>(a, out); break;
+        case 2: col_attention_fwd_kernel<2><<<grid, 256, 0, st>>>(a, out); break;
+        case 4: col_attention_fwd_kernel<4><<<grid, 256, 0, st>>>(a, out); break;
+        case 8: col_attention_fwd_kernel<8><<<grid, 256, 0, st>>>(a, out); break;
+        case 16: col_attention_fwd_kernel<16><<<grid, 256, 0, st>>>(a, out); break;
+        default: return B200MP_EINVAL;
+    }
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int b200mp_col_attention_bwd(const float* q, const float* k, const float* v, const float* g_out, int64_t R, int S,
+                                        int C, int nhead, float p_drop, uint64_t seed, float* gq, float* gk, float* gv,
+                                        void* stream) {
+    using namespace b200mp;
+    if (R < 0 || S < 1 || S > 8 || nhead < 1 || nhead > 16 || C % nhead || p_drop < 0.f || p_drop >= 1.f) return B200MP_EINVAL;
+    if (R == 0) return 0;
+    if (!q || !k || !v || !g_out || !gq || !gk || !gv) return B200MP_EINVAL;
+    AttnArgs a{R, S, C, nhead, q, k, v, p_drop, seed};
+    const int64_t total = R * S * nhead;
+    const unsigned grid = (unsigned)((total + 255) / 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (C / nhead) {
+        case 1: col_attention_bwd_kernel<1><<<grid, 256, 0, st>>>(a, g_out, gq, gk, gv); break;
+        case 2: col_attention_bwd_kernel<2><<<grid, 256, 0, st>>>(a, g_out, gq, gk, gv); break;
+        case 4: col_attention_bwd_kernel<4><<<grid, 256, 0, st>>>(a, g_out, gq, gk, gv); break;
+        case 8: col_attention_bwd_kernel<8><<<grid, 256, 0, st>>>(a, g_out, gq, gk, gv); break;
+        case 16: col_attention_bwd_kernel<16><<<grid, 256, 0, st>>>(a, g_out, gq, gk, gv); break;
+        default: return B200MP_EINVAL;
+    }
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}

@@ -580,3 +580,79 @@ def edge_update(P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha: float, beta: 
     """e_eid / out_eid: int32 maps segment position -> row, for an input e / an output e' that
     live in the caller's edge order instead of segment order (first / last layer)."""
     return _EdgeUpdate.apply(P, Q, e, W1, b1, W2, b2, st, alpha, beta, sink, e_eid, out_eid)
+
+
+# ----------------------------------------------------------------------------- column attention
+def _col_attention_fwd(q, k, v, nhead, p, seed):
+    R, S, Cc = q.shape
+    out = torch.empty_like(q)
+    with torch.cuda.device(q.device), _track("col_attention_fwd"):
+        L.check(L.lib().b200mp_col_attention_fwd(L.ptr(q), L.ptr(k), L.ptr(v), R, S, Cc, nhead, float(p), C_u64(seed), L.ptr(out),
+                                                 L.stream()), "b200mp_col_attention_fwd")
+    return out
+
+
+def _col_attention_bwd(q, k, v, g, nhead, p, seed):
+    R, S, Cc = q.shape
+    gq, gk, gv = torch.empty_like(q), torch.empty_like(q), torch.empty_like(q)
+    with torch.cuda.device(q.device), _track("col_attention_bwd"):
+        L.check(L.lib().b200mp_col_attention_bwd(L.ptr(q), L.ptr(k), L.ptr(v), L.ptr(g), R, S, Cc, nhead, float(p), C_u64(seed),
+                                                 L.ptr(gq), L.ptr(gk), L.ptr(gv), L.stream()), "b200mp_col_attention_bwd")
+    return gq, gk, gv
+
+
+def C_u64(x):
+    return L.C.c_uint64(int(x) & (2 ** 64 - 1))
+
+
+_attn_calls = [0]
+
+
+class _ColAttention(torch.autograd.Function):
+    """softmax(q k^T / sqrt(d)) v per (row, head) over [R, S, C] column tokens, with the attention
+    probability dropout of nn.MultiheadAttention (mask regenerated from the seed in backward)."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, nhead, p):
+        q, k, v = map(_f32c, (q, k, v))
+        L.require_cuda(q, k, v)
+        seed = 0
+        if p > 0.0:
+            _attn_calls[0] += 1
+            seed = torch.initial_seed() * 0x9E3779B97F4A7C15 + _attn_calls[0]
+        ctx.nhead, ctx.p, ctx.seed = int(nhead), float(p), seed
+        ctx.save_for_backward(q, k, v)
+        return _col_attention_fwd(q, k, v, ctx.nhead, ctx.p, seed)
+
+    @staticmethod
+    def backward(ctx, g):
+        q, k, v = ctx.saved_tensors
+        gq, gk, gv = _col_attention_bwd(q, k, v, _f32c(g), ctx.nhead, ctx.p, ctx.seed)
+        return gq, gk, gv, None, None
+
+
+def col_attention(q, k, v, nhead: int, p: float = 0.0):
+    return _ColAttention.apply(q, k, v, nhead, p)
+
+
+def transformer_encoder_layer(layer: torch.nn.TransformerEncoderLayer, x: torch.Tensor) -> torch.Tensor:
+    """forward of a post-norm, batch_first nn.TransformerEncoderLayer (the module stays the parameter
+    container: same state_dict keys) over column tokens x [R, S, C]: the four projections run as node
+    linears (tcgen05 kernels for C = 64, R S >= 4096), the attention core on col_attention.cu; residuals,
+    LayerNorms and the sub-layer dropouts are torch element-wise ops."""
+    if layer.norm_first:
+        raise ValueError("b200mp column attention implements the post-norm layer the reference builds")
+    R, S, Cc = x.shape
+    mha = layer.self_attn
+    x2 = x.reshape(R * S, Cc)
+    Wq, Wk, Wv = mha.in_proj_weight.chunk(3)
+    bq, bk, bv = mha.in_proj_bias.chunk(3)
+    q, k, v = linear_group(x2, (Wq, Wk, Wv), (bq, bk, bv))
+    att = col_attention(q.view(R, S, Cc), k.view(R, S, Cc), v.view(R, S, Cc), mha.num_heads,
+                        float(mha.dropout) if layer.training else 0.0)
+    sa = linear_group(att.reshape(R * S, Cc), (mha.out_proj.weight,), (mha.out_proj.bias,))[0]
+    x2 = layer.norm1(x2 + layer.dropout1(sa))
+    hmid = layer.activation(linear_group(x2, (layer.linear1.weight,), (layer.linear1.bias,))[0])
+    ff = linear_group(layer.dropout(hmid), (layer.linear2.weight,), (layer.linear2.bias,))[0]
+    x2 = layer.norm2(x2 + layer.dropout2(ff))
+    return x2.view(R, S, Cc)

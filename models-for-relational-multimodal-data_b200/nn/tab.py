@@ -42,7 +42,9 @@ class _ColumnAttention(nn.Module):
         self.tab_norm = nn.LayerNorm(channels)
 
     def attend(self, t: Tensor) -> Tensor:
-        return self.tab_norm(self.tab_conv(t))
+        # tab_conv holds the parameters (state_dict keys of nn.TransformerEncoderLayer); the math runs on
+        # the b200mp kernels (functional.transformer_encoder_layer)
+        return self.tab_norm(BF.transformer_encoder_layer(self.tab_conv, t))
 
     def _reset_attention(self):
         _xavier(self.tab_conv)

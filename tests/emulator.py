@@ -159,7 +159,26 @@ def pna_coef(ptr, g_agg, agg, tie, need_gA):
     return coef.contiguous(), gA
 
 
+def col_attention_fwd(q, k, v, nhead, p, seed):
+    assert p == 0.0, "the emulator has no dropout stream"
+    R, S, C = q.shape
+    hd = C // nhead
+    sp = lambda t: t.view(R, S, nhead, hd).transpose(1, 2)
+    a = torch.softmax(sp(q) @ sp(k).transpose(-1, -2) / hd ** 0.5, -1) @ sp(v)
+    return a.transpose(1, 2).reshape(R, S, C)
+
+
+def col_attention_bwd(q, k, v, g, nhead, p, seed):
+    q, k, v = (t.detach().clone().requires_grad_(True) for t in (q, k, v))
+    with torch.enable_grad():
+        out = col_attention_fwd(q, k, v, nhead, p, seed)
+    out.backward(g)
+    return q.grad, k.grad, v.grad
+
+
 _PATCHES = [
+    (BF, "_col_attention_fwd", col_attention_fwd),
+    (BF, "_col_attention_bwd", col_attention_bwd),
     (BF, "_pna_scale_fwd", pna_scale_fwd),
     (BF, "_pna_scale_bwd", pna_scale_bwd),
     (BF, "_pna_coef", pna_coef),
