@@ -192,6 +192,31 @@ int b200mp_col_attention_bwd(const float* q, const float* k, const float* v, con
                              int C, int nhead, float p_drop, uint64_t seed, float* gq, float* gk, float* gv,
                              void* stream);
 
+/* ------------------------------------------------------------------ column (stype-wise) encoders
+ * What the reference's StypeWiseFeatureEncoder call computes (src/utils.py:139-140,357-359, fused.py:71-72;
+ * encoders chosen at src/datasets/ibm_transactions_for_aml.py:283-294): every column of every stype -> one
+ * [C] token, all tokens of a row written once as out [rows, S, C], S = ncol (+ 1 when cls != NULL: the CLS
+ * token of src/nn/models/tabgnn.py:214 / fused.py:149 goes to slot 0).  Columns appear in output order. */
+enum { B200MP_COL_NUMERICAL = 0, B200MP_COL_CATEGORICAL = 1, B200MP_COL_TIMESTAMP = 2 };
+typedef struct b200mp_column {
+    int32_t kind;        /* B200MP_COL_* */
+    int32_t offset;      /* element offset of this column inside a row of feat */
+    int64_t stride;      /* elements per row of feat */
+    const void* feat;    /* numerical: float32 [rows, stride]; categorical: int64 ids, -1 = missing;
+                            timestamp: int64, 7 consecutive fields (year, month, day, weekday, hour, minute, second) */
+    const float* weight; /* numerical [C]; categorical [ncat + 1, C], row 0 = missing; timestamp [7 * 8, C] */
+    const float* bias;   /* numerical, timestamp: [C]; categorical: NULL */
+    float mean, std;     /* numerical: x = (v - mean) / std * weight + bias */
+    float min_year;      /* timestamp: the positional encoding takes year - min_year */
+    int32_t ncat;        /* categorical: number of categories */
+} b200mp_column;
+int b200mp_col_encode_fwd(const b200mp_column* cols, int ncol, const float* cls, int64_t rows, int C, float* out,
+                          void* stream);
+/* parameter gradients (the inputs are data): g_weight[i] / g_bias[i] have the shape of cols[i].weight / bias and
+ * are ACCUMULATED into (zero them first); g_bias[i] is NULL for categorical columns; g_cls [C] when has_cls. */
+int b200mp_col_encode_bwd(const b200mp_column* cols, int ncol, int has_cls, int64_t rows, int C, const float* g_out,
+                          float* const* g_weight, float* const* g_bias, float* g_cls, void* stream);
+
 /* ------------------------------------------------------------------ batch construction
  * Negative sampler (replaces src/primitives/negative_sampling/negative_sampling.cpp:10-76, the
  * reference's only native component, called at src/utils/batch_processing.py:145).  edge_index [2,E]

@@ -48,10 +48,22 @@ _SIGS = {
     "b200mp_first_occurrence": [_p, _l, _p, _p, _p, _p],
     "b200mp_col_attention_fwd": [_p, _p, _p, _l, _i, _i, _i, _f, C.c_uint64, _p, _p],
     "b200mp_col_attention_bwd": [_p, _p, _p, _p, _l, _i, _i, _i, _f, C.c_uint64, _p, _p, _p, _p],
+    "b200mp_col_encode_fwd": [_p, _i, _p, _l, _i, _p, _p],
+    "b200mp_col_encode_bwd": [_p, _i, _i, _l, _i, _p, _p, _p, _p, _p],
     "b200mp_umma_selftest": [_i, _p, _p, _p, _p],
     "b200mp_umma_probe": [_p, _i, _p, _i, C.c_uint64, C.c_uint64, _i, _i, _i, C.c_uint32, _p, _p],
     "b200mp_edge_update_bwd": [_i, _l, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p],
 }
+
+
+class Column(C.Structure):
+    """struct b200mp_column of include/b200mp.h"""
+    _fields_ = [("kind", C.c_int32), ("offset", C.c_int32), ("stride", C.c_int64), ("feat", C.c_void_p),
+                ("weight", C.c_void_p), ("bias", C.c_void_p), ("mean", C.c_float), ("std", C.c_float),
+                ("min_year", C.c_float), ("ncat", C.c_int32)]
+
+
+COL_NUMERICAL, COL_CATEGORICAL, COL_TIMESTAMP = 0, 1, 2
 
 
 def declared_symbols():

@@ -7,6 +7,8 @@ Saved tensors are never modified, so ``retain_graph=True`` + repeated backward (
 """
 from __future__ import annotations
 
+from typing import NamedTuple, Optional, Sequence
+
 import torch
 
 from . import _lib as L
@@ -656,3 +658,88 @@ def transformer_encoder_layer(layer: torch.nn.TransformerEncoderLayer, x: torch.
     ff = linear_group(layer.dropout(hmid), (layer.linear2.weight,), (layer.linear2.bias,))[0]
     x2 = layer.norm2(x2 + layer.dropout2(ff))
     return x2.view(R, S, Cc)
+
+
+# ----------------------------------------------------------------------------- column (stype-wise) encoders
+class EncColumn(NamedTuple):
+    """One output token of the stype-wise encoder (struct b200mp_column): ``feat`` is the stype's whole feature
+    tensor, this column's value(s) of row r start at element r * stride + offset."""
+    kind: int
+    feat: torch.Tensor
+    offset: int
+    stride: int
+    weight: torch.Tensor                  # numerical [C] | categorical [ncat + 1, C] | timestamp [7, 8, C]
+    bias: Optional[torch.Tensor]          # [C] | None (categorical)
+    mean: float = 0.0
+    std: float = 1.0
+    min_year: float = 0.0
+    ncat: int = 0
+
+
+def _enc_struct(cols: Sequence[EncColumn]):
+    arr = (L.Column * max(len(cols), 1))()
+    for i, c in enumerate(cols):
+        want = torch.float32 if c.kind == L.COL_NUMERICAL else torch.int64
+        if c.feat.dtype != want or not c.feat.is_contiguous():
+            raise ValueError(f"column {i}: features must be contiguous {want}, got {c.feat.dtype}")
+        L.require_cuda(c.feat, c.weight, c.bias)
+        arr[i] = L.Column(c.kind, c.offset, c.stride, c.feat.data_ptr(), c.weight.data_ptr(),
+                          0 if c.bias is None else c.bias.data_ptr(), c.mean, c.std, c.min_year, c.ncat)
+    return arr
+
+
+def _col_encode_fwd(cols: Sequence[EncColumn], cls: Optional[torch.Tensor], rows: int, Cc: int) -> torch.Tensor:
+    S = len(cols) + (cls is not None)
+    dev = cols[0].weight.device if cols else cls.device
+    out = torch.empty(rows, S, Cc, device=dev, dtype=torch.float32)
+    with torch.cuda.device(dev), _track("col_encode_fwd"):
+        L.check(L.lib().b200mp_col_encode_fwd(_enc_struct(cols), len(cols), L.ptr(cls), rows, Cc, L.ptr(out), L.stream()),
+                "b200mp_col_encode_fwd")
+    return out
+
+
+def _col_encode_bwd(cols: Sequence[EncColumn], has_cls: bool, rows: int, Cc: int, g_out: torch.Tensor,
+                    g_weight: Sequence[torch.Tensor], g_bias: Sequence[Optional[torch.Tensor]], g_cls: Optional[torch.Tensor]):
+    """accumulates into g_weight[i] / g_bias[i] (views with the layout of cols[i].weight / bias) and g_cls"""
+    n = len(cols)
+    pw = (L.C.c_void_p * max(n, 1))(*[t.data_ptr() for t in g_weight])
+    pb = (L.C.c_void_p * max(n, 1))(*[None if t is None else t.data_ptr() for t in g_bias])
+    with torch.cuda.device(g_out.device), _track("col_encode_bwd"):
+        L.check(L.lib().b200mp_col_encode_bwd(_enc_struct(cols), n, int(has_cls), rows, Cc, L.ptr(g_out), pw, pb, L.ptr(g_cls),
+                                              L.stream()), "b200mp_col_encode_bwd")
+
+
+class _ColEncode(torch.autograd.Function):
+    """plan: per column (kind, feat, offset, stride, (param index, row | None) of the weight, same of the bias | None,
+    mean, std, min_year, ncat); params: the parameter tensors the plan indexes (fp32 contiguous)."""
+
+    @staticmethod
+    def _columns(plan, tensors):
+        pick = lambda ref, ts: None if ref is None else (ts[ref[0]] if ref[1] is None else ts[ref[0]][ref[1]])
+        return [EncColumn(k, feat, off, stride, pick(wref, tensors), pick(bref, tensors), mean, std, my, ncat)
+                for (k, feat, off, stride, wref, bref, mean, std, my, ncat) in plan]
+
+    @staticmethod
+    def forward(ctx, plan, rows, Cc, cls, *params):
+        params = tuple(_f32c(p.detach()) for p in params)
+        cls_ = None if cls is None else _f32c(cls.detach()).view(-1)
+        ctx.plan, ctx.rows, ctx.Cc, ctx.has_cls = plan, int(rows), int(Cc), cls is not None
+        ctx.cls_shape = None if cls is None else cls.shape
+        ctx.save_for_backward(*params)
+        return _col_encode_fwd(_ColEncode._columns(plan, params), cls_, ctx.rows, ctx.Cc)
+
+    @staticmethod
+    def backward(ctx, g):
+        params = ctx.saved_tensors
+        g = _f32c(g)
+        grads = tuple(torch.zeros_like(p) for p in params)
+        g_cls = torch.zeros(ctx.Cc, device=g.device, dtype=torch.float32) if ctx.has_cls else None
+        cols = _ColEncode._columns(ctx.plan, params)
+        gcols = _ColEncode._columns(ctx.plan, grads)
+        _col_encode_bwd(cols, ctx.has_cls, ctx.rows, ctx.Cc, g, [c.weight for c in gcols], [c.bias for c in gcols], g_cls)
+        return (None, None, None, None if g_cls is None else g_cls.view(ctx.cls_shape)) + grads
+
+
+def col_encode(plan, rows: int, Cc: int, cls: Optional[torch.Tensor], params: Sequence[torch.Tensor]) -> torch.Tensor:
+    """[rows, S, C] tokens of all columns in ``plan`` (+ CLS in slot 0) in one launch; see ``_ColEncode``"""
+    return _ColEncode.apply(tuple(plan), rows, Cc, cls, *params)

@@ -176,7 +176,55 @@ def col_attention_bwd(q, k, v, g, nhead, p, seed):
     return q.grad, k.grad, v.grad
 
 
+def _enc_blocks(cols):
+    """EncColumn list -> the oracle's per-column blocks (one column per block keeps the output order)"""
+    from oracle import stype_encoders as O  # noqa: F401
+    blocks = []
+    for c in cols:
+        if c.kind == 0:
+            v = c.feat.reshape(c.feat.shape[0], -1)[:, c.offset:c.offset + 1]
+            blocks.append(('numerical', v, torch.tensor([c.mean]), torch.tensor([c.std]), c.weight.view(1, -1), c.bias.view(1, -1)))
+        elif c.kind == 1:
+            v = c.feat.reshape(c.feat.shape[0], -1)[:, c.offset:c.offset + 1]
+            blocks.append(('categorical', v, [c.weight]))
+        else:
+            v = c.feat.reshape(c.feat.shape[0], -1)[:, c.offset:c.offset + 7].unsqueeze(1)
+            blocks.append(('timestamp', v, torch.tensor([c.min_year]), c.weight.reshape(1, 7, 8, -1), c.bias.view(1, -1)))
+    return blocks
+
+
+def col_encode_fwd(cols, cls, rows, Cc):
+    from oracle import stype_encoders as O
+    return O.stype_wise_encode(_enc_blocks(cols), cls).contiguous()
+
+
+def col_encode_bwd(cols, has_cls, rows, Cc, g_out, g_weight, g_bias, g_cls):
+    from oracle import stype_encoders as O
+    with torch.enable_grad():
+        leaves = []
+        cols2 = []
+        for c in cols:
+            w = c.weight.detach().clone().requires_grad_(True)
+            b = None if c.bias is None else c.bias.detach().clone().requires_grad_(True)
+            leaves.append((w, b))
+            cols2.append(c._replace(weight=w, bias=b))
+        cls = torch.zeros(Cc, requires_grad=True) if has_cls else None
+        out = O.stype_wise_encode(_enc_blocks(cols2), cls)
+        out.backward(g_out)
+    for (w, b), gw, gb, c in zip(leaves, g_weight, g_bias, cols):
+        g = w.grad.clone()
+        if c.kind == 1:
+            g[0] = 0                       # padding row of nn.Embedding(padding_idx=0)
+        gw += g.view_as(gw)
+        if b is not None:
+            gb += b.grad.view_as(gb)
+    if has_cls:
+        g_cls += cls.grad
+
+
 _PATCHES = [
+    (BF, "_col_encode_fwd", col_encode_fwd),
+    (BF, "_col_encode_bwd", col_encode_bwd),
     (BF, "_col_attention_fwd", col_attention_fwd),
     (BF, "_col_attention_bwd", col_attention_bwd),
     (BF, "_pna_scale_fwd", pna_scale_fwd),
