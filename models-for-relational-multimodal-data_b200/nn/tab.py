@@ -6,8 +6,10 @@ attention residual: tabgnn.py:219 vs fused.py:249 / inteleaved.py:219).
 
 Graph side (PNAConv -> BatchNorm -> ReLU -> residual, edge update) runs on the b200mp CUDA kernels
 with the edge tensors held in CSC storage order for all layers.  The column attention over the
-S = K + 1 tokens of a row is torch's post-norm TransformerEncoderLayer (library kernels) behind the
-same attribute names (``tab_conv`` / ``tab_norm``); it is row-wise, hence order-independent.
+S = K + 1 tokens of a row keeps ``nn.TransformerEncoderLayer`` as the parameter container (same attribute
+names ``tab_conv`` / ``tab_norm``, same state_dict keys) and runs it through
+``functional.transformer_encoder_layer``: projections on the tcgen05 node kernels, attention core on
+csrc/col_attention.cu; it is row-wise, hence order-independent.
 """
 from __future__ import annotations
 
