@@ -7,6 +7,7 @@ Host code is Python/PyTorch (device memory, streams, autograd plumbing) over han
 kernels behind the C ABI in ``include/b200mp.h``; there is no CPU / PyTorch fallback.
 """
 from . import _lib, functional, graph, parallel, sampling   # noqa: F401
+from .feeder import DeviceFeeder   # noqa: F401
 from .sampling import NeighborSampler, generate_negative_samples   # noqa: F401
 from .graph import (EdgeStructure, SegmentIndex, degree, degree_histogram, edge_structure,   # noqa: F401
                     relabel, to_csc)

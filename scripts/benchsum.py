@@ -1,5 +1,6 @@
 import sys, json
-for l in sys.stdin:
+src = open(sys.argv[1]) if len(sys.argv) > 1 else sys.stdin      # never block on a terminal-less stdin by accident
+for l in src:
     if l.startswith('{'):
         d = json.loads(l)
         print("ms/step", round(d['ms_per_step'], 2), "top", d['roofline']['kernel'], d['roofline']['frac'], "step frac", d['step_roofline']['frac'],
