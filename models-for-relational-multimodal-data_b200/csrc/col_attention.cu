@@ -112,31 +112,56 @@ __global__ void __launch_bounds__(256) col_attention_fwd_kernel(AttnArgs a, floa
     st_vec<HD>(out + base + (int64_t)i * a.C, acc);
 }
 
-// Thread (r, h, t): dQ_t, dK_t, dV_t.  With P = softmax rows, Pd = drop(P), dPd_ij = dO_i . v_j,
-// dP_ij = dPd_ij * dropscale_ij, D_i = sum_j P_ij dP_ij, dS_ij = P_ij (dP_ij - D_i):
-//   dQ_t = scale sum_j dS_tj k_j ,  dK_t = scale sum_i dS_it q_i ,  dV_t = sum_i Pd_it dO_i
+// Backward: eight lanes per (row, head), lane i = token i (lanes >= S idle).  Each lane stages its token's q, k, v, dO
+// slices in shared memory once, computes ROW i of the probabilities (P = softmax rows, Pd = drop(P),
+// dPd_ij = dO_i . v_j, dP_ij = dPd_ij * dropscale_ij, D_i = sum_j P_ij dP_ij, dS_ij = P_ij (dP_ij - D_i)) and
+// dQ_i = scale sum_j dS_ij k_j, leaves dS_i. and Pd_i. in shared memory, and after a warp barrier reads COLUMN i:
+//   dK_i = scale sum_t dS_ti q_t ,  dV_i = sum_t Pd_ti dO_t
+// (the first version recomputed every row in every lane: S times the loads and dot products; 88 -> see DESIGN.md)
+constexpr int ATT_BT = 128;               // threads per CTA = 16 (row, head) groups
 template <int HD>
-__global__ void __launch_bounds__(256) col_attention_bwd_kernel(AttnArgs a, const float* __restrict__ g_out,
-                                                                float* __restrict__ gq, float* __restrict__ gk,
-                                                                float* __restrict__ gv) {
-    const int64_t tix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t total = a.R * a.S * a.nhead;
-    if (tix >= total) return;
-    const int h = (int)(tix % a.nhead);
-    const int t = (int)((tix / a.nhead) % a.S);
-    const int64_t r = tix / ((int64_t)a.nhead * a.S);
+__global__ void __launch_bounds__(ATT_BT) col_attention_bwd_kernel(AttnArgs a, const float* __restrict__ g_out,
+                                                                   float* __restrict__ gq, float* __restrict__ gk,
+                                                                   float* __restrict__ gv) {
+    constexpr int NG = ATT_BT / 8;
+    constexpr int LD = HD % 4 == 0 ? HD : 4;              // 16-byte rows at least
+    __shared__ __align__(16) float sq[NG][8][LD], sk[NG][8][LD], sv[NG][8][LD], sg[NG][8][LD];
+    __shared__ float sds[NG][8][9], spd[NG][8][9];
+    const int grp = threadIdx.x >> 3, i = threadIdx.x & 7;
+    const int64_t gid = (int64_t)blockIdx.x * NG + grp;
+    const bool live = gid < a.R * a.nhead && i < a.S;
+    const int h = (int)(gid % a.nhead);
+    const int64_t r = gid / a.nhead;
     const float scale = rsqrtf((float)HD), inv_keep = a.p > 0.f ? 1.f / (1.f - a.p) : 1.f;
-    const int64_t base = r * a.S * a.C + h * HD;
+    const int64_t o = live ? (r * a.S + i) * a.C + h * HD : 0;
+    float qi[HD], gi[HD], tmp[HD];
+    if (live) {
+        ld_vec<HD>(qi, a.q + o);
+        ld_vec<HD>(gi, g_out + o);
+#pragma unroll
+        for (int c = 0; c < HD; ++c) { sq[grp][i][c] = qi[c]; sg[grp][i][c] = gi[c]; }
+        ld_vec<HD>(tmp, a.k + o);
+#pragma unroll
+        for (int c = 0; c < HD; ++c) sk[grp][i][c] = tmp[c];
+        ld_vec<HD>(tmp, a.v + o);
+#pragma unroll
+        for (int c = 0; c < HD; ++c) sv[grp][i][c] = tmp[c];
+    }
+    __syncwarp();
     float dq[HD], dk[HD], dv[HD];
 #pragma unroll
     for (int c = 0; c < HD; ++c) dq[c] = dk[c] = dv[c] = 0.f;
-    for (int i = 0; i < a.S; ++i) {                        // row i of the attention matrix
-        const float* qi = a.q + base + (int64_t)i * a.C;
-        const float* gi = g_out + base + (int64_t)i * a.C;
+    if (live) {
         float s[8], dp[8], m = -INFINITY;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            s[j] = j < a.S ? dot<HD>(qi, a.k + base + (int64_t)j * a.C) * scale : -INFINITY;
+            float d = 0.f, e = 0.f;
+            if (j < a.S) {
+#pragma unroll
+                for (int c = 0; c < HD; ++c) { d = fmaf(qi[c], sk[grp][j][c], d); e = fmaf(gi[c], sv[grp][j][c], e); }
+            }
+            s[j] = j < a.S ? d * scale : -INFINITY;
+            dp[j] = j < a.S ? e * drop_scale(a.seed, r, h, i, j, a.p, inv_keep) : 0.f;
             m = fmaxf(m, s[j]);
         }
         float l = 0.f;
@@ -145,32 +170,29 @@ __global__ void __launch_bounds__(256) col_attention_bwd_kernel(AttnArgs a, cons
         const float inv_l = 1.f / l;
         float D = 0.f;
 #pragma unroll
+        for (int j = 0; j < 8; ++j) { s[j] *= inv_l; D = fmaf(s[j], dp[j], D); }
+#pragma unroll
         for (int j = 0; j < 8; ++j) {
-            s[j] *= inv_l;                                  // P_ij
-            dp[j] = j < a.S ? dot<HD>(gi, a.v + base + (int64_t)j * a.C) * drop_scale(a.seed, r, h, i, j, a.p, inv_keep) : 0.f;
-            D = fmaf(s[j], dp[j], D);
-        }
-        float p_it = 0.f, dp_it = 0.f;                      // column t of row i (register arrays need static indices)
+            if (j < a.S) {
+                const float ds = s[j] * (dp[j] - D) * scale;
+                sds[grp][i][j] = ds;
+                spd[grp][i][j] = s[j] * drop_scale(a.seed, r, h, i, j, a.p, inv_keep);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { if (j == t) { p_it = s[j]; dp_it = dp[j]; } }
-        const float ds_it = p_it * (dp_it - D) * scale;
-        const float pd_it = p_it * drop_scale(a.seed, r, h, i, t, a.p, inv_keep);
-        axpy<HD>(dk, ds_it, qi);
-        axpy<HD>(dv, pd_it, gi);
-        if (i == t) {                                       // row t: dQ_t
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                if (j < a.S) {
-                    const float ds = s[j] * (dp[j] - D) * scale;
-                    axpy<HD>(dq, ds, a.k + base + (int64_t)j * a.C);
-                }
+                for (int c = 0; c < HD; ++c) dq[c] = fmaf(ds, sk[grp][j][c], dq[c]);
             }
         }
     }
-    const int64_t o = base + (int64_t)t * a.C;
-    st_vec<HD>(gq + o, dq);
-    st_vec<HD>(gk + o, dk);
-    st_vec<HD>(gv + o, dv);
+    __syncwarp();
+    if (live) {
+        for (int t = 0; t < a.S; ++t) {
+            const float ds = sds[grp][t][i], pd = spd[grp][t][i];
+#pragma unroll
+            for (int c = 0; c < HD; ++c) { dk[c] = fmaf(ds, sq[grp][t][c], dk[c]); dv[c] = fmaf(pd, sg[grp][t][c], dv[c]); }
+        }
+        st_vec<HD>(gq + o, dq);
+        st_vec<HD>(gk + o, dk);
+        st_vec<HD>(gv + o, dv);
+    }
 }
 
 }  // namespace b200mp
@@ -205,15 +227,15 @@ extern "C" int b200mp_col_attention_bwd(const float* q, const float* k, const fl
     if (R == 0) return 0;
     if (!q || !k || !v || !g_out || !gq || !gk || !gv) return B200MP_EINVAL;
     AttnArgs a{R, S, C, nhead, q, k, v, p_drop, seed};
-    const int64_t total = R * S * nhead;
-    const unsigned grid = (unsigned)((total + 255) / 256);
+    const int64_t groups = R * nhead;
+    const unsigned grid = (unsigned)((groups + ATT_BT / 8 - 1) / (ATT_BT / 8));
     cudaStream_t st = (cudaStream_t)stream;
     switch (C / nhead) {
-        case 1: col_attention_bwd_kernel<1><<<grid, 256, 0, st>>>(a, g_out, gq, gk, gv); break;
-        case 2: col_attention_bwd_kernel<2><<<grid, 256, 0, st>>>(a, g_out, gq, gk, gv); break;
-        case 4: col_attention_bwd_kernel<4><<<grid, 256, 0, st>>>(a, g_out, gq, gk, gv); break;
-        case 8: col_attention_bwd_kernel<8><<<grid, 256, 0, st>>>(a, g_out, gq, gk, gv); break;
-        case 16: col_attention_bwd_kernel<16><<<grid, 256, 0, st>>>(a, g_out, gq, gk, gv); break;
+        case 1: col_attention_bwd_kernel<1><<<grid, ATT_BT, 0, st>>>(a, g_out, gq, gk, gv); break;
+        case 2: col_attention_bwd_kernel<2><<<grid, ATT_BT, 0, st>>>(a, g_out, gq, gk, gv); break;
+        case 4: col_attention_bwd_kernel<4><<<grid, ATT_BT, 0, st>>>(a, g_out, gq, gk, gv); break;
+        case 8: col_attention_bwd_kernel<8><<<grid, ATT_BT, 0, st>>>(a, g_out, gq, gk, gv); break;
+        case 16: col_attention_bwd_kernel<16><<<grid, ATT_BT, 0, st>>>(a, g_out, gq, gk, gv); break;
         default: return B200MP_EINVAL;
     }
     B200MP_LAUNCH_CHECK();

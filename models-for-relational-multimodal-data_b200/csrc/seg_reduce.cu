@@ -13,6 +13,9 @@
 
 namespace b200mp {
 
+#ifndef SEG_MINB
+#define SEG_MINB 4
+#endif
 constexpr float STD_EPS = 1e-5f;
 constexpr float STD_THR = 0.0031622776601683794f;   // (float)math.sqrt(1e-5)
 
@@ -128,7 +131,7 @@ __device__ __forceinline__ void finalize_store(const Acc<STATS>& a, int64_t deg,
 
 // ---- light segments: one warp per node
 template <bool STATS, int H>
-__global__ void __launch_bounds__(NT) seg_light_kernel(int64_t N, const int64_t* __restrict__ ptr, const float* __restrict__ m,
+__global__ void __launch_bounds__(NT, SEG_MINB) seg_light_kernel(int64_t N, const int64_t* __restrict__ ptr, const float* __restrict__ m,
                                                        float* __restrict__ agg, float* __restrict__ tie, int64_t light_max) {
     constexpr int LPR = H / 4, RPW = 32 / LPR;
     const int lane = threadIdx.x & 31;

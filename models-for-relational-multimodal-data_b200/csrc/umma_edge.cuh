@@ -220,6 +220,88 @@ __device__ __forceinline__ void store_wgrad_partial(uint32_t tmem_cols, float* _
     }
 }
 
+// ---- two independent 64-edge pipelines per CTA ---------------------------------------------------
+// ncu on the one-tile-per-CTA version: 38 % of the warp samples sat in the two mbarrier spins (the
+// tensor pipe's 3xTF32 time, fully exposed) and shared memory is too full for a second 128-edge tile.
+// So the CTA's 512 threads form TWO groups of 256, each running the whole tile pipeline on its own
+// 64-edge tile (M = 64 MMAs) with its own buffers, mbarriers, named barrier and tensor-memory columns,
+// sharing only the weight tiles: while one group waits for its MMAs the other runs its SIMT phases.
+namespace dual {
+constexpr int RG = 64;                    // edges per group tile
+constexpr int NTG = 256;                  // threads per group
+constexpr int NPG = RG * 16 / NTG;        // 4 adjacent rows per thread in the coalesced mapping
+using RG_T = RowFmt<RG, HH>;              // 16 KB operand tile
+
+struct Rows { float4 v[NPG]; };
+__device__ __forceinline__ void group_sync(int grp) { asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(NTG) : "memory"); }
+__device__ __forceinline__ void load_rows(Rows& R, const float* __restrict__ src, const int32_t* __restrict__ rowmap,
+                                          int64_t row0, int nrows, int lt) {
+    const int j = lt & 15, g = lt >> 4;
+    int64_t rows[NPG];
+#pragma unroll
+    for (int i = 0; i < NPG; ++i) {
+        const int rc = min(g * NPG + i, nrows - 1);
+        rows[i] = rowmap ? (int64_t)__ldg(rowmap + row0 + rc) : row0 + rc;
+    }
+#pragma unroll
+    for (int i = 0; i < NPG; ++i) R.v[i] = ldg4(src + rows[i] * HH + j * 4);
+}
+__device__ __forceinline__ void store_rows_split(const Rows& R, float* hi, float* lo, int nrows, int lt) {
+    const int j = lt & 15, g = lt >> 4;
+#pragma unroll
+    for (int i = 0; i < NPG; ++i) {
+        const int r = g * NPG + i;
+        float4 h, l;
+        split4(r < nrows ? R.v[i] : make_float4(0.f, 0.f, 0.f, 0.f), h, l);
+        const int o = RG_T::off(r, j);
+        st4(hi + o, h);
+        st4(lo + o, l);
+    }
+}
+// M = 64 accumulator [64 x 64] -> staging tile: row m sits in tensor-memory lane (m % 16) + 32 (m / 16),
+// so warp (quarter q = warp % 4, column half = group-local warp / 4) reads rows 16 q .. 16 q + 15 in its
+// lanes 0..15 (lanes 16..31 carry nothing).
+__device__ __forceinline__ void stage_from_tmem64(uint32_t tcols, float* S, int lwarp, int lane) {
+    const int q = lwarp & 3, half = lwarp >> 2;
+    const uint32_t taddr = tcols + ((uint32_t)(q * 32) << 16) + half * 32;
+    const int r = q * 16 + (lane & 15);
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        float v[16];
+        tmem_ld16(taddr + k * 16, v);
+        if (lane < 16) {
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj)
+                st4(S + stage_off(r, half * 8 + k * 4 + jj), f4(v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]));
+        }
+    }
+}
+__device__ __forceinline__ void gemm3_data64(uint32_t d, const float* x_hi, const float* x_lo, const float* w_hi, const float* w_lo,
+                                             uint32_t accumulate) {
+    issue_data_gemm_row32<RG, HH, HH>(d, smem_u32(x_lo), smem_u32(w_hi), accumulate);
+    issue_data_gemm_row32<RG, HH, HH>(d, smem_u32(x_hi), smem_u32(w_lo), 1);
+    issue_data_gemm_row32<RG, HH, HH>(d, smem_u32(x_hi), smem_u32(w_hi), 1);
+}
+__device__ __forceinline__ void gemm3_wgrad64(uint32_t d, const float* g_hi, const float* g_lo, const float* x_hi, const float* x_lo,
+                                              uint32_t accumulate) {
+    issue_wgrad_gemm_row32<RG, HH, HH>(d, smem_u32(g_lo), smem_u32(x_hi), accumulate);
+    issue_wgrad_gemm_row32<RG, HH, HH>(d, smem_u32(g_hi), smem_u32(x_lo), 1);
+    issue_wgrad_gemm_row32<RG, HH, HH>(d, smem_u32(g_hi), smem_u32(x_hi), 1);
+}
+// per-thread column partials -> this group's column sums (red: [NTG / 16][64] floats of the group's smem)
+__device__ __forceinline__ void group_column_sums(float* red, float4 acc, float* __restrict__ out, float scale, int lt, int grp) {
+    group_sync(grp);
+    st4(red + (lt >> 4) * HH + (lt & 15) * 4, acc);
+    group_sync(grp);
+    if (lt < HH) {
+        float sum = 0.f;
+#pragma unroll 8
+        for (int g = 0; g < NTG / 16; ++g) sum += red[g * HH + lt];
+        out[lt] = scale * sum;
+    }
+}
+}  // namespace dual
+
 struct TileSync {
     uint64_t bar[2];
     uint32_t tmem_base;

@@ -17,8 +17,9 @@ import torch
 
 from . import _lib as L
 
-LIGHT_MAX = 512     # segments longer than this are reduced by the chunked (multi-CTA) path
-CHUNK = 1024        # rows per chunk of a heavy segment
+import os as _os
+LIGHT_MAX = int(_os.environ.get("B200MP_LIGHT_MAX", 512))     # segments longer than this are reduced by the chunked (multi-CTA) path
+CHUNK = int(_os.environ.get("B200MP_CHUNK", 1024))            # rows per chunk of a heavy segment
 
 
 @dataclass
