@@ -5,8 +5,8 @@
 // The projections around it (in_proj, out_proj, feed-forward) are [rows * S, 64] x 64 linears and run on
 // the tcgen05 node kernels (functional.linear_group); this file is the part between them.
 //
-// The sequences are tiny (S <= 8, d = 8 or 16), so nothing is tiled: one thread per (row, head, token),
-// operands read through L1 (the S threads of a (row, head) share them), everything else in registers.
+// The sequences are tiny (S <= 8, d <= 16), so nothing is tiled: eight lanes per (row, head), lane = token; the lanes
+// stage their tokens' slices in shared memory (each operand leaves global memory once), the rest is registers.
 // Attention-probability dropout (the layer's dropout applies to them in training) uses a counter hash
 // of (seed, row, head, i, j), recomputed in backward -- no mask tensor.
 #include "common.cuh"
@@ -77,21 +77,42 @@ struct AttnArgs {
 };
 
 // out[r, i, h*HD : (h+1)*HD] = sum_j drop(softmax_j(q_i . k_j / sqrt(HD))) v_j
+// Eight lanes per (row, head), lane i = token i (lanes >= S idle): every lane stages its token's k and v slices in shared
+// memory once, so a (row, head) reads each operand from global memory exactly once.
+constexpr int ATT_BT = 128;               // threads per CTA = 16 (row, head) groups
 template <int HD>
-__global__ void __launch_bounds__(256) col_attention_fwd_kernel(AttnArgs a, float* __restrict__ out) {
-    const int64_t tix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t total = a.R * a.S * a.nhead;
-    if (tix >= total) return;
-    const int h = (int)(tix % a.nhead);
-    const int i = (int)((tix / a.nhead) % a.S);
-    const int64_t r = tix / ((int64_t)a.nhead * a.S);
+__global__ void __launch_bounds__(ATT_BT) col_attention_fwd_kernel(AttnArgs a, float* __restrict__ out) {
+    constexpr int NG = ATT_BT / 8;
+    constexpr int LD = HD % 4 == 0 ? HD : 4;
+    __shared__ __align__(16) float sk[NG][8][LD], sv[NG][8][LD];
+    const int grp = threadIdx.x >> 3, i = threadIdx.x & 7;
+    const int64_t gid = (int64_t)blockIdx.x * NG + grp;
+    const bool live = gid < a.R * a.nhead && i < a.S;
+    const int h = (int)(gid % a.nhead);
+    const int64_t r = gid / a.nhead;
     const float scale = rsqrtf((float)HD), inv_keep = a.p > 0.f ? 1.f / (1.f - a.p) : 1.f;
-    const int64_t base = r * a.S * a.C + h * HD;
-    const float* qi = a.q + base + (int64_t)i * a.C;
+    const int64_t o = live ? (r * a.S + i) * a.C + h * HD : 0;
+    float qi[HD], tmp[HD];
+    if (live) {
+        ld_vec<HD>(qi, a.q + o);
+        ld_vec<HD>(tmp, a.k + o);
+#pragma unroll
+        for (int c = 0; c < HD; ++c) sk[grp][i][c] = tmp[c];
+        ld_vec<HD>(tmp, a.v + o);
+#pragma unroll
+        for (int c = 0; c < HD; ++c) sv[grp][i][c] = tmp[c];
+    }
+    __syncwarp();
+    if (!live) return;
     float s[8], m = -INFINITY;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        s[j] = j < a.S ? dot<HD>(qi, a.k + base + (int64_t)j * a.C) * scale : -INFINITY;
+        float d = 0.f;
+        if (j < a.S) {
+#pragma unroll
+            for (int c = 0; c < HD; ++c) d = fmaf(qi[c], sk[grp][j][c], d);
+        }
+        s[j] = j < a.S ? d * scale : -INFINITY;
         m = fmaxf(m, s[j]);
     }
     float l = 0.f;
@@ -105,11 +126,11 @@ __global__ void __launch_bounds__(256) col_attention_fwd_kernel(AttnArgs a, floa
     for (int j = 0; j < 8; ++j) {
         if (j < a.S) {
             const float pj = s[j] * inv_l * drop_scale(a.seed, r, h, i, j, a.p, inv_keep);
-            const float* vj = a.v + base + (int64_t)j * a.C;
-            axpy<HD>(acc, pj, vj);
+#pragma unroll
+            for (int c = 0; c < HD; ++c) acc[c] = fmaf(pj, sv[grp][j][c], acc[c]);
         }
     }
-    st_vec<HD>(out + base + (int64_t)i * a.C, acc);
+    st_vec<HD>(out + o, acc);
 }
 
 // Backward: eight lanes per (row, head), lane i = token i (lanes >= S idle).  Each lane stages its token's q, k, v, dO
@@ -118,7 +139,6 @@ __global__ void __launch_bounds__(256) col_attention_fwd_kernel(AttnArgs a, floa
 // dQ_i = scale sum_j dS_ij k_j, leaves dS_i. and Pd_i. in shared memory, and after a warp barrier reads COLUMN i:
 //   dK_i = scale sum_t dS_ti q_t ,  dV_i = sum_t Pd_ti dO_t
 // (the first version recomputed every row in every lane: S times the loads and dot products; 88 -> see DESIGN.md)
-constexpr int ATT_BT = 128;               // threads per CTA = 16 (row, head) groups
 template <int HD>
 __global__ void __launch_bounds__(ATT_BT) col_attention_bwd_kernel(AttnArgs a, const float* __restrict__ g_out,
                                                                    float* __restrict__ gq, float* __restrict__ gk,
@@ -204,15 +224,15 @@ extern "C" int b200mp_col_attention_fwd(const float* q, const float* k, const fl
     if (R == 0) return 0;
     if (!q || !k || !v || !out) return B200MP_EINVAL;
     AttnArgs a{R, S, C, nhead, q, k, v, p_drop, seed};
-    const int64_t total = R * S * nhead;
-    const unsigned grid = (unsigned)((total + 255) / 256);
+    const int64_t groups = R * nhead;
+    const unsigned grid = (unsigned)((groups + ATT_BT / 8 - 1) / (ATT_BT / 8));
     cudaStream_t st = (cudaStream_t)stream;
     switch (C / nhead) {
-        case 1: col_attention_fwd_kernel<1><<<grid, 256, 0, st>>>(a, out); break;
-        case 2: col_attention_fwd_kernel<2><<<grid, 256, 0, st>>>(a, out); break;
-        case 4: col_attention_fwd_kernel<4><<<grid, 256, 0, st>>>(a, out); break;
-        case 8: col_attention_fwd_kernel<8><<<grid, 256, 0, st>>>(a, out); break;
-        case 16: col_attention_fwd_kernel<16><<<grid, 256, 0, st>>>(a, out); break;
+        case 1: col_attention_fwd_kernel<1><<<grid, ATT_BT, 0, st>>>(a, out); break;
+        case 2: col_attention_fwd_kernel<2><<<grid, ATT_BT, 0, st>>>(a, out); break;
+        case 4: col_attention_fwd_kernel<4><<<grid, ATT_BT, 0, st>>>(a, out); break;
+        case 8: col_attention_fwd_kernel<8><<<grid, ATT_BT, 0, st>>>(a, out); break;
+        case 16: col_attention_fwd_kernel<16><<<grid, ATT_BT, 0, st>>>(a, out); break;
         default: return B200MP_EINVAL;
     }
     B200MP_LAUNCH_CHECK();
