@@ -192,6 +192,17 @@ int b200mp_col_attention_bwd(const float* q, const float* k, const float* v, con
                              int C, int nhead, float p_drop, uint64_t seed, float* gq, float* gk, float* gv,
                              void* stream);
 
+/* ------------------------------------------------------------------ residual + dropout + LayerNorm
+ * y = LayerNorm(x + dropout(sub)) over rows of C in {16, 32, 64, 128} floats (sub == NULL: y = LayerNorm(x)): norm1 /
+ * norm2 with dropout1 / dropout2 of the post-norm nn.TransformerEncoderLayer and the LayerNorm after it
+ * (src/nn/models/tabgnn.py:199-209,219, fused.py:83-93,249).  stats [rows, 2] = (mean, rstd) for backward.
+ * Backward writes g_x, g_sub (NULL allowed when p_drop == 0: it equals g_x) and ACCUMULATES into ggamma / gbeta [C]. */
+int b200mp_add_dropout_layernorm_fwd(const float* x, const float* sub, int64_t rows, int C, float p_drop, uint64_t seed,
+                                     const float* gamma, const float* beta, float eps, float* y, float* stats, void* stream);
+int b200mp_add_dropout_layernorm_bwd(const float* g, const float* x, const float* sub, const float* stats, int64_t rows,
+                                     int C, float p_drop, uint64_t seed, const float* gamma, float* gx, float* gsub,
+                                     float* ggamma, float* gbeta, void* stream);
+
 /* ------------------------------------------------------------------ column (stype-wise) encoders
  * What the reference's StypeWiseFeatureEncoder call computes (src/utils.py:139-140,357-359, fused.py:71-72;
  * encoders chosen at src/datasets/ibm_transactions_for_aml.py:283-294): every column of every stype -> one

@@ -641,7 +641,8 @@ def transformer_encoder_layer(layer: torch.nn.TransformerEncoderLayer, x: torch.
     """forward of a post-norm, batch_first nn.TransformerEncoderLayer (the module stays the parameter
     container: same state_dict keys) over column tokens x [R, S, C]: the four projections run as node
     linears (tcgen05 kernels for C = 64, R S >= 4096), the attention core on col_attention.cu; residuals,
-    LayerNorms and the sub-layer dropouts are torch element-wise ops."""
+    LayerNorms with their dropouts on row_norm.cu (add_dropout_layernorm); the feed-forward's inner
+    activation + dropout are torch element-wise ops."""
     if layer.norm_first:
         raise ValueError("b200mp column attention implements the post-norm layer the reference builds")
     R, S, Cc = x.shape
@@ -653,10 +654,11 @@ def transformer_encoder_layer(layer: torch.nn.TransformerEncoderLayer, x: torch.
     att = col_attention(q.view(R, S, Cc), k.view(R, S, Cc), v.view(R, S, Cc), mha.num_heads,
                         float(mha.dropout) if layer.training else 0.0)
     sa = linear_group(att.reshape(R * S, Cc), (mha.out_proj.weight,), (mha.out_proj.bias,))[0]
-    x2 = layer.norm1(x2 + layer.dropout1(sa))
+    train = layer.training
+    x2 = add_dropout_layernorm(x2, sa, float(layer.dropout1.p) if train else 0.0, layer.norm1)
     hmid = layer.activation(linear_group(x2, (layer.linear1.weight,), (layer.linear1.bias,))[0])
     ff = linear_group(layer.dropout(hmid), (layer.linear2.weight,), (layer.linear2.bias,))[0]
-    x2 = layer.norm2(x2 + layer.dropout2(ff))
+    x2 = add_dropout_layernorm(x2, ff, float(layer.dropout2.p) if train else 0.0, layer.norm2)
     return x2.view(R, S, Cc)
 
 
@@ -743,3 +745,68 @@ class _ColEncode(torch.autograd.Function):
 def col_encode(plan, rows: int, Cc: int, cls: Optional[torch.Tensor], params: Sequence[torch.Tensor]) -> torch.Tensor:
     """[rows, S, C] tokens of all columns in ``plan`` (+ CLS in slot 0) in one launch; see ``_ColEncode``"""
     return _ColEncode.apply(tuple(plan), rows, Cc, cls, *params)
+
+
+# ----------------------------------------------------------------------------- residual + dropout + LayerNorm
+_ROW_NORM_C = (16, 32, 64, 128)
+
+
+def _row_norm_fwd(x, sub, p, seed, gamma, beta, eps):
+    rows, Cc = x.shape
+    y = torch.empty_like(x)
+    stats = torch.empty(rows, 2, device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device), _track("add_dropout_layernorm_fwd"):
+        L.check(L.lib().b200mp_add_dropout_layernorm_fwd(L.ptr(x), L.ptr(sub), rows, Cc, float(p), C_u64(seed), L.ptr(gamma), L.ptr(beta),
+                                                         float(eps), L.ptr(y), L.ptr(stats), L.stream()), "b200mp_add_dropout_layernorm_fwd")
+    return y, stats
+
+
+def _row_norm_bwd(g, x, sub, stats, p, seed, gamma):
+    rows, Cc = x.shape
+    gx = torch.empty_like(x)
+    gsub = torch.empty_like(x) if (sub is not None and p > 0.0) else None
+    gg = torch.zeros(2, Cc, device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device), _track("add_dropout_layernorm_bwd"):
+        L.check(L.lib().b200mp_add_dropout_layernorm_bwd(L.ptr(g), L.ptr(x), L.ptr(sub), L.ptr(stats), rows, Cc, float(p), C_u64(seed),
+                                                         L.ptr(gamma), L.ptr(gx), L.ptr(gsub), L.ptr(gg[0]), L.ptr(gg[1]), L.stream()),
+                "b200mp_add_dropout_layernorm_bwd")
+    return gx, gsub, gg[0], gg[1]
+
+
+class _AddDropoutLayerNorm(torch.autograd.Function):
+    """y = LayerNorm(x + dropout(sub)) (sub None: LayerNorm(x)) over [rows, C]; mask regenerated from the seed in backward"""
+
+    @staticmethod
+    def forward(ctx, x, sub, p, gamma, beta, eps):
+        x, gamma, beta = _f32c(x), _f32c(gamma), _f32c(beta)
+        sub = None if sub is None else _f32c(sub)
+        L.require_cuda(x, sub, gamma, beta)
+        p = float(p) if sub is not None else 0.0
+        seed = 0
+        if p > 0.0:
+            _attn_calls[0] += 1
+            seed = torch.initial_seed() * 0x9E3779B97F4A7C15 + _attn_calls[0] * 0x632BE59BD9B4E019
+        y, stats = _row_norm_fwd(x, sub, p, seed, gamma, beta, eps)
+        ctx.p, ctx.seed, ctx.has_sub = p, seed, sub is not None
+        ctx.save_for_backward(x, sub, stats, gamma)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        x, sub, stats, gamma = ctx.saved_tensors
+        gx, gsub, gg, gb = _row_norm_bwd(_f32c(g), x, sub, stats, ctx.p, ctx.seed, gamma)
+        if ctx.has_sub and gsub is None:
+            gsub = gx
+        return gx, (gsub if ctx.has_sub else None), None, gg, gb, None
+
+
+def add_dropout_layernorm(x: torch.Tensor, sub: Optional[torch.Tensor], p: float, norm: torch.nn.LayerNorm) -> torch.Tensor:
+    """``norm(x + dropout(sub, p))`` (``sub`` None: ``norm(x)``) over the last dimension, one kernel pass each way for
+    C in {16, 32, 64, 128}; other widths (not used by the reference's models) go through torch's own ops."""
+    Cc = x.shape[-1]
+    if Cc not in _ROW_NORM_C or norm.weight is None or norm.bias is None or tuple(norm.normalized_shape) != (Cc,):
+        z = x if sub is None else x + torch.nn.functional.dropout(sub, p, p > 0.0)
+        return norm(z)
+    y = _AddDropoutLayerNorm.apply(x.reshape(-1, Cc), None if sub is None else sub.reshape(-1, Cc), p, norm.weight, norm.bias,
+                                   norm.eps)
+    return y.view(x.shape)

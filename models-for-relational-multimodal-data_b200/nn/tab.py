@@ -46,7 +46,7 @@ class _ColumnAttention(nn.Module):
     def attend(self, t: Tensor) -> Tensor:
         # tab_conv holds the parameters (state_dict keys of nn.TransformerEncoderLayer); the math runs on
         # the b200mp kernels (functional.transformer_encoder_layer)
-        return self.tab_norm(BF.transformer_encoder_layer(self.tab_conv, t))
+        return BF.add_dropout_layernorm(BF.transformer_encoder_layer(self.tab_conv, t), None, 0.0, self.tab_norm)
 
     def _reset_attention(self):
         _xavier(self.tab_conv)

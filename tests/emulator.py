@@ -222,7 +222,35 @@ def col_encode_bwd(cols, has_cls, rows, Cc, g_out, g_weight, g_bias, g_cls):
         g_cls += cls.grad
 
 
+def row_norm_fwd(x, sub, p, seed, gamma, beta, eps):
+    z = x if sub is None else x + sub * _drop_mask(sub, p, seed)
+    mean = z.mean(-1, keepdim=True)
+    var = z.var(-1, unbiased=False, keepdim=True)
+    rstd = torch.rsqrt(var + eps)
+    return ((z - mean) * rstd * gamma + beta).contiguous(), torch.cat([mean, rstd], -1).contiguous()
+
+
+def _drop_mask(t, p, seed):
+    if p <= 0.0:
+        return torch.ones_like(t)
+    g = torch.Generator().manual_seed(int(seed) & (2 ** 62 - 1))
+    return (torch.rand(t.shape, generator=g) >= p).to(t.dtype) / (1.0 - p)
+
+
+def row_norm_bwd(g, x, sub, stats, p, seed, gamma):
+    mask = None if sub is None else _drop_mask(sub, p, seed)
+    z = x if sub is None else x + sub * mask
+    mean, rstd = stats[:, :1], stats[:, 1:]
+    zh = (z - mean) * rstd
+    gh = g * gamma
+    gz = rstd * (gh - gh.mean(-1, keepdim=True) - zh * (gh * zh).mean(-1, keepdim=True))
+    gsub = (gz * mask).contiguous() if (sub is not None and p > 0.0) else None
+    return gz.contiguous(), gsub, (g * zh).sum(0), g.sum(0)
+
+
 _PATCHES = [
+    (BF, "_row_norm_fwd", row_norm_fwd),
+    (BF, "_row_norm_bwd", row_norm_bwd),
     (BF, "_col_encode_fwd", col_encode_fwd),
     (BF, "_col_encode_bwd", col_encode_bwd),
     (BF, "_col_attention_fwd", col_attention_fwd),
