@@ -192,6 +192,22 @@ int b200mp_col_attention_bwd(const float* q, const float* k, const float* v, con
                              int C, int nhead, float p_drop, uint64_t seed, float* gq, float* gk, float* gv,
                              void* stream);
 
+/* ------------------------------------------------------------------ BatchNorm + ReLU + residual average
+ * x' = (x + relu(BatchNorm(c))) / 2 over node rows [N, H], H in {16, 32, 64, 128}, training-mode statistics: the tail of
+ * every backbone layer (src/nn/gnn/gine.py:87, pna.py:96; models/tabgnn.py:185-188).  sums: fp64 [2, H], zeroed by the
+ * caller, accumulated into.  mean_rstd: fp32 [2, H] = (mean, 1 / sqrt(biased var + eps)) computed by the caller from sums.
+ *   b200mp_bn_stats                 sums = (sum c, sum c^2) per column
+ *   b200mp_bn_relu_res_fwd          out = (x + relu((c - mean) rstd gamma + beta)) / 2
+ *   b200mp_bn_relu_res_bwd_reduce   sums = (sum gr, sum gr chat), gr = g / 2 where BatchNorm(c) > 0  (= g_beta, g_gamma)
+ *   b200mp_bn_relu_res_bwd_apply    gc = gamma rstd (gr - gmeans[0] - chat gmeans[1]),  gx = g / 2;  gmeans = sums / N */
+int b200mp_bn_stats(const float* c, int64_t N, int H, double* sums, void* stream);
+int b200mp_bn_relu_res_fwd(const float* c, const float* x, int64_t N, int H, const float* gamma, const float* beta,
+                           const float* mean_rstd, float* out, void* stream);
+int b200mp_bn_relu_res_bwd_reduce(const float* g, const float* c, int64_t N, int H, const float* gamma, const float* beta,
+                                  const float* mean_rstd, double* sums, void* stream);
+int b200mp_bn_relu_res_bwd_apply(const float* g, const float* c, int64_t N, int H, const float* gamma, const float* beta,
+                                 const float* mean_rstd, const float* gmeans, float* gc, float* gx, void* stream);
+
 /* ------------------------------------------------------------------ residual + dropout + LayerNorm
  * y = LayerNorm(x + dropout(sub)) over rows of C in {16, 32, 64, 128} floats (sub == NULL: y = LayerNorm(x)): norm1 /
  * norm2 with dropout1 / dropout2 of the post-norm nn.TransformerEncoderLayer and the LayerNorm after it

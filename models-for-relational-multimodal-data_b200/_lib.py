@@ -48,6 +48,10 @@ _SIGS = {
     "b200mp_first_occurrence": [_p, _l, _p, _p, _p, _p],
     "b200mp_col_attention_fwd": [_p, _p, _p, _l, _i, _i, _i, _f, C.c_uint64, _p, _p],
     "b200mp_col_attention_bwd": [_p, _p, _p, _p, _l, _i, _i, _i, _f, C.c_uint64, _p, _p, _p, _p],
+    "b200mp_bn_stats": [_p, _l, _i, _p, _p],
+    "b200mp_bn_relu_res_fwd": [_p, _p, _l, _i, _p, _p, _p, _p, _p],
+    "b200mp_bn_relu_res_bwd_reduce": [_p, _p, _l, _i, _p, _p, _p, _p, _p],
+    "b200mp_bn_relu_res_bwd_apply": [_p, _p, _l, _i, _p, _p, _p, _p, _p, _p, _p],
     "b200mp_add_dropout_layernorm_fwd": [_p, _p, _l, _i, _f, C.c_uint64, _p, _p, _f, _p, _p, _p],
     "b200mp_add_dropout_layernorm_bwd": [_p, _p, _p, _p, _l, _i, _f, C.c_uint64, _p, _p, _p, _p, _p, _p],
     "b200mp_col_encode_fwd": [_p, _i, _p, _l, _i, _p, _p],

@@ -810,3 +810,72 @@ def add_dropout_layernorm(x: torch.Tensor, sub: Optional[torch.Tensor], p: float
     y = _AddDropoutLayerNorm.apply(x.reshape(-1, Cc), None if sub is None else sub.reshape(-1, Cc), p, norm.weight, norm.bias,
                                    norm.eps)
     return y.view(x.shape)
+
+
+# ----------------------------------------------------------------------------- BatchNorm + ReLU + residual average
+def _bn_stats(c):
+    N, H = c.shape
+    sums = torch.zeros(2, H, device=c.device, dtype=torch.float64)
+    with torch.cuda.device(c.device), _track("bn_stats"):
+        L.check(L.lib().b200mp_bn_stats(L.ptr(c), N, H, L.ptr(sums), L.stream()), "b200mp_bn_stats")
+    return sums
+
+
+def _bn_relu_res_fwd(c, x, gamma, beta, mean_rstd):
+    N, H = c.shape
+    out = torch.empty_like(c)
+    with torch.cuda.device(c.device), _track("bn_relu_res_fwd"):
+        L.check(L.lib().b200mp_bn_relu_res_fwd(L.ptr(c), L.ptr(x), N, H, L.ptr(gamma), L.ptr(beta), L.ptr(mean_rstd), L.ptr(out),
+                                               L.stream()), "b200mp_bn_relu_res_fwd")
+    return out
+
+
+def _bn_relu_res_bwd(g, c, gamma, beta, mean_rstd):
+    """-> g_c, g_x, g_gamma, g_beta"""
+    N, H = c.shape
+    sums = torch.zeros(2, H, device=c.device, dtype=torch.float64)
+    gc, gx = torch.empty_like(c), torch.empty_like(c)
+    with torch.cuda.device(c.device), _track("bn_relu_res_bwd"):
+        L.check(L.lib().b200mp_bn_relu_res_bwd_reduce(L.ptr(g), L.ptr(c), N, H, L.ptr(gamma), L.ptr(beta), L.ptr(mean_rstd), L.ptr(sums),
+                                                      L.stream()), "b200mp_bn_relu_res_bwd_reduce")
+        gmeans = (sums / N).float()
+        L.check(L.lib().b200mp_bn_relu_res_bwd_apply(L.ptr(g), L.ptr(c), N, H, L.ptr(gamma), L.ptr(beta), L.ptr(mean_rstd), L.ptr(gmeans),
+                                                     L.ptr(gc), L.ptr(gx), L.stream()), "b200mp_bn_relu_res_bwd_apply")
+    return gc, gx, sums[1].float(), sums[0].float()
+
+
+class _BnReluRes(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, c, x, gamma, beta, eps, bn):
+        c, x, gamma, beta = map(_f32c, (c, x, gamma, beta))
+        L.require_cuda(c, x, gamma, beta)
+        N = c.shape[0]
+        sums = _bn_stats(c)
+        mean = sums[0] / N
+        var = (sums[1] / N - mean * mean).clamp_min_(0.0)           # biased, fp64
+        mean_rstd = torch.stack([mean, torch.rsqrt(var + eps)]).float()
+        if bn is not None and bn.track_running_stats and bn.running_mean is not None:
+            with torch.no_grad():
+                bn.num_batches_tracked += 1
+                m = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+                bn.running_mean.mul_(1 - m).add_(mean.to(bn.running_mean.dtype), alpha=m)
+                bn.running_var.mul_(1 - m).add_((var * (N / max(N - 1, 1))).to(bn.running_var.dtype), alpha=m)
+        ctx.save_for_backward(c, gamma, beta, mean_rstd)
+        return _bn_relu_res_fwd(c, x, gamma, beta, mean_rstd)
+
+    @staticmethod
+    def backward(ctx, g):
+        c, gamma, beta, mean_rstd = ctx.saved_tensors
+        gc, gx, gg, gb = _bn_relu_res_bwd(_f32c(g), c, gamma, beta, mean_rstd)
+        return gc, gx, gg, gb, None, None
+
+
+def bn_relu_residual(bn: torch.nn.BatchNorm1d, c: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    """``(x + relu(bn(c))) / 2`` (gine.py:87, pna.py:96).  Training mode with affine parameters and H in {16, 32, 64, 128}:
+    two kernel passes forward, two backward (csrc/node_norm.cu), running statistics updated as BatchNorm1d does;
+    eval mode / other shapes: torch's own ops."""
+    H = c.shape[-1]
+    if (bn.training or not bn.track_running_stats) and bn.affine and c.dim() == 2 and c.shape == x.shape \
+            and H in _ROW_NORM_C and c.shape[0] > 1:
+        return _BnReluRes.apply(c, x, bn.weight, bn.bias, bn.eps, bn)
+    return (x + torch.relu(bn(c))) / 2

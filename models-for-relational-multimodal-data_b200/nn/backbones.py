@@ -85,7 +85,7 @@ class _Backbone(nn.Module):
             e_eid = perm32 if (i == 0 or not self.edge_updates) else None
             out_eid = perm32 if i == L - 1 else None
             sink = BF.EdgeGradSink() if (self.edge_updates and e.requires_grad and torch.is_grad_enabled()) else None
-            x = (x + F.relu(self.batch_norms[i](self.convs[i].forward_sorted(x, st.fwd, e, sink=sink, e_eid=e_eid)))) / 2
+            x = BF.bn_relu_residual(self.batch_norms[i].module, self.convs[i].forward_sorted(x, st.fwd, e, sink=sink, e_eid=e_eid), x)
             if self.edge_updates:
                 e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, sink=sink, e_eid=e_eid, out_eid=out_eid)
         return x, (e if self.edge_updates else e_in)
@@ -95,7 +95,7 @@ class _Backbone(nn.Module):
         for i in range(self.num_gnn_layers):
             # conv and edge update of a layer read the same e: one gradient buffer for both
             sink = BF.EdgeGradSink() if (self.edge_updates and e.requires_grad and torch.is_grad_enabled()) else None
-            x = (x + F.relu(self.batch_norms[i](_conv_sorted(self.convs[i], x, st, e, sink)))) / 2
+            x = BF.bn_relu_residual(self.batch_norms[i].module, _conv_sorted(self.convs[i], x, st, e, sink), x)
             if self.edge_updates:
                 e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, sink=sink)
         return x, BF.scatter_rows(e, st.fwd.perm)               # back to caller order

@@ -71,7 +71,7 @@ class _GraphStep(nn.Module):
     def graph_step(self, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float):
         c = self.gnn_conv.forward_sorted(x, st, e) if isinstance(self.gnn_conv, PNAConvHetero) \
             else self.gnn_conv.forward_sorted(x, st.fwd, e)
-        x = (x + F.relu(self.gnn_norm(c))) / 2
+        x = BF.bn_relu_residual(self.gnn_norm.module, c, x)
         return x, edge_update_sorted(self.gnn_edge_update, x, st, e, alpha, beta)
 
 

@@ -248,7 +248,29 @@ def row_norm_bwd(g, x, sub, stats, p, seed, gamma):
     return gz.contiguous(), gsub, (g * zh).sum(0), g.sum(0)
 
 
+def bn_stats(c):
+    cd = c.double()
+    return torch.stack([cd.sum(0), (cd * cd).sum(0)])
+
+
+def bn_relu_res_fwd(c, x, gamma, beta, mean_rstd):
+    y = (c - mean_rstd[0]) * (mean_rstd[1] * gamma) + beta
+    return ((x + torch.relu(y)) * 0.5).contiguous()
+
+
+def bn_relu_res_bwd(g, c, gamma, beta, mean_rstd):
+    ch = (c - mean_rstd[0]) * mean_rstd[1]
+    y = (c - mean_rstd[0]) * (mean_rstd[1] * gamma) + beta
+    gr = torch.where(y > 0, 0.5 * g, torch.zeros_like(g))
+    m1, m2 = gr.double().mean(0).float(), (gr * ch).double().mean(0).float()
+    gc = gamma * mean_rstd[1] * (gr - m1 - ch * m2)
+    return gc.contiguous(), (0.5 * g).contiguous(), (gr * ch).double().sum(0).float(), gr.double().sum(0).float()
+
+
 _PATCHES = [
+    (BF, "_bn_stats", bn_stats),
+    (BF, "_bn_relu_res_fwd", bn_relu_res_fwd),
+    (BF, "_bn_relu_res_bwd", bn_relu_res_bwd),
     (BF, "_row_norm_fwd", row_norm_fwd),
     (BF, "_row_norm_bwd", row_norm_bwd),
     (BF, "_col_encode_fwd", col_encode_fwd),
