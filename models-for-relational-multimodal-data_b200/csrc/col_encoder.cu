@@ -51,13 +51,16 @@ __device__ __forceinline__ void ts_encode(const int64_t* __restrict__ f, float m
 __global__ void __launch_bounds__(256) col_encode_fwd_kernel(const __grid_constant__ EncArgs a, float* __restrict__ out) {
     __shared__ float enc_s[16][TS_K];
     const int lane = threadIdx.x & 15, grp = threadIdx.x >> 4;
-    const int64_t items = a.rows * a.S;
     const int C4 = a.C >> 2;
-    for (int64_t it0 = (int64_t)blockIdx.x * 16; it0 < items; it0 += (int64_t)gridDim.x * 16) {
-        const int64_t item = it0 + grp;
-        const bool valid = item < items;
-        const int64_t r = valid ? item / a.S : 0;
-        const int ci = (valid ? (int)(item - r * a.S) : 0) - a.tok0;
+    // a CTA iteration = 16 rows (one per lane group), tokens one after the other: every warp of the CTA works on the same
+    // column kind at the same time (mixing kinds in a warp serialised the 56-term timestamp loop with the one-line cases)
+    const int64_t chunks = (a.rows + 15) / 16;
+    for (int64_t chunk = blockIdx.x; chunk < chunks; chunk += gridDim.x)
+    for (int s = 0; s < a.S; ++s) {
+        const int64_t r = chunk * 16 + grp;
+        const bool valid = r < a.rows;
+        const int64_t item = r * a.S + s;
+        const int ci = s - a.tok0;
         const int kind = ci < 0 ? -1 : a.col[ci].kind;
         if (valid && kind == B200MP_COL_TIMESTAMP && lane < 14) {
             const int64_t* f = (const int64_t*)a.col[ci].feat + r * a.col[ci].stride + a.col[ci].offset;
@@ -261,8 +264,7 @@ extern "C" int b200mp_col_encode_fwd(const b200mp_column* cols, int ncol, const 
         if (!column_ok(cols[i])) return B200MP_EINVAL;
         a.col[i] = cols[i];
     }
-    const int64_t items = rows * a.S;
-    col_encode_fwd_kernel<<<enc_grid((items + 15) / 16), 256, 0, (cudaStream_t)stream>>>(a, out);
+    col_encode_fwd_kernel<<<enc_grid((rows + 15) / 16), 256, 0, (cudaStream_t)stream>>>(a, out);
     B200MP_LAUNCH_CHECK();
     return 0;
 }

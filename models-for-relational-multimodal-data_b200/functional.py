@@ -706,7 +706,7 @@ def _col_encode_bwd(cols: Sequence[EncColumn], has_cls: bool, rows: int, Cc: int
     n = len(cols)
     pw = (L.C.c_void_p * max(n, 1))(*[t.data_ptr() for t in g_weight])
     pb = (L.C.c_void_p * max(n, 1))(*[None if t is None else t.data_ptr() for t in g_bias])
-    with torch.cuda.device(g_out.device), _track("col_encode_bwd"):
+    with torch.cuda.device(g_out.device), _track("col_encode_bwd", n + int(has_cls)):
         L.check(L.lib().b200mp_col_encode_bwd(_enc_struct(cols), n, int(has_cls), rows, Cc, L.ptr(g_out), pw, pb, L.ptr(g_cls),
                                               L.stream()), "b200mp_col_encode_bwd")
 
@@ -835,7 +835,7 @@ def _bn_relu_res_bwd(g, c, gamma, beta, mean_rstd):
     N, H = c.shape
     sums = torch.zeros(2, H, device=c.device, dtype=torch.float64)
     gc, gx = torch.empty_like(c), torch.empty_like(c)
-    with torch.cuda.device(c.device), _track("bn_relu_res_bwd"):
+    with torch.cuda.device(c.device), _track("bn_relu_res_bwd", 2):
         L.check(L.lib().b200mp_bn_relu_res_bwd_reduce(L.ptr(g), L.ptr(c), N, H, L.ptr(gamma), L.ptr(beta), L.ptr(mean_rstd), L.ptr(sums),
                                                       L.stream()), "b200mp_bn_relu_res_bwd_reduce")
         gmeans = (sums / N).float()
