@@ -830,27 +830,39 @@ def _bn_relu_res_fwd(c, x, gamma, beta, mean_rstd):
     return out
 
 
-def _bn_relu_res_bwd(g, c, gamma, beta, mean_rstd):
-    """-> g_c, g_x, g_gamma, g_beta"""
+def _bn_bwd_reduce(g, c, gamma, beta, mean_rstd):
+    """-> fp64 [2, H]: (sum gr, sum gr chat) over the local rows = (g_beta, g_gamma)"""
     N, H = c.shape
     sums = torch.zeros(2, H, device=c.device, dtype=torch.float64)
-    gc, gx = torch.empty_like(c), torch.empty_like(c)
-    with torch.cuda.device(c.device), _track("bn_relu_res_bwd", 2):
+    with torch.cuda.device(c.device), _track("bn_relu_res_bwd_reduce"):
         L.check(L.lib().b200mp_bn_relu_res_bwd_reduce(L.ptr(g), L.ptr(c), N, H, L.ptr(gamma), L.ptr(beta), L.ptr(mean_rstd), L.ptr(sums),
                                                       L.stream()), "b200mp_bn_relu_res_bwd_reduce")
-        gmeans = (sums / N).float()
+    return sums
+
+
+def _bn_bwd_apply(g, c, gamma, beta, mean_rstd, gmeans):
+    """-> g_c, g_x"""
+    N, H = c.shape
+    gc, gx = torch.empty_like(c), torch.empty_like(c)
+    with torch.cuda.device(c.device), _track("bn_relu_res_bwd_apply"):
         L.check(L.lib().b200mp_bn_relu_res_bwd_apply(L.ptr(g), L.ptr(c), N, H, L.ptr(gamma), L.ptr(beta), L.ptr(mean_rstd), L.ptr(gmeans),
                                                      L.ptr(gc), L.ptr(gx), L.stream()), "b200mp_bn_relu_res_bwd_apply")
-    return gc, gx, sums[1].float(), sums[0].float()
+    return gc, gx
 
 
 class _BnReluRes(torch.autograd.Function):
+    """group / n_total: the rows of ALL ranks of a destination-range partition form the batch (the column sums are
+    all-reduced, fp64); the gamma / beta gradients returned are the LOCAL parts (summed with the other weight gradients)."""
+
     @staticmethod
-    def forward(ctx, c, x, gamma, beta, eps, bn):
+    def forward(ctx, c, x, gamma, beta, eps, bn, group, n_total):
         c, x, gamma, beta = map(_f32c, (c, x, gamma, beta))
         L.require_cuda(c, x, gamma, beta)
-        N = c.shape[0]
+        synced = n_total is not None                                   # group None = the default process group
+        N = int(n_total) if synced else c.shape[0]
         sums = _bn_stats(c)
+        if synced:
+            torch.distributed.all_reduce(sums, group=group)
         mean = sums[0] / N
         var = (sums[1] / N - mean * mean).clamp_min_(0.0)           # biased, fp64
         mean_rstd = torch.stack([mean, torch.rsqrt(var + eps)]).float()
@@ -861,21 +873,30 @@ class _BnReluRes(torch.autograd.Function):
                 bn.running_mean.mul_(1 - m).add_(mean.to(bn.running_mean.dtype), alpha=m)
                 bn.running_var.mul_(1 - m).add_((var * (N / max(N - 1, 1))).to(bn.running_var.dtype), alpha=m)
         ctx.save_for_backward(c, gamma, beta, mean_rstd)
+        ctx.group, ctx.N, ctx.synced = group, N, synced
         return _bn_relu_res_fwd(c, x, gamma, beta, mean_rstd)
 
     @staticmethod
     def backward(ctx, g):
         c, gamma, beta, mean_rstd = ctx.saved_tensors
-        gc, gx, gg, gb = _bn_relu_res_bwd(_f32c(g), c, gamma, beta, mean_rstd)
-        return gc, gx, gg, gb, None, None
+        g = _f32c(g)
+        sums = _bn_bwd_reduce(g, c, gamma, beta, mean_rstd)
+        gg, gb = sums[1].float(), sums[0].float()
+        if ctx.synced:
+            torch.distributed.all_reduce(sums, group=ctx.group)
+        gc, gx = _bn_bwd_apply(g, c, gamma, beta, mean_rstd, (sums / ctx.N).float())
+        return gc, gx, gg, gb, None, None, None, None
 
 
-def bn_relu_residual(bn: torch.nn.BatchNorm1d, c: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+def bn_relu_residual(bn: torch.nn.BatchNorm1d, c: torch.Tensor, x: torch.Tensor, group=None, n_total=None) -> torch.Tensor:
     """``(x + relu(bn(c))) / 2`` (gine.py:87, pna.py:96).  Training mode with affine parameters and H in {16, 32, 64, 128}:
     two kernel passes forward, two backward (csrc/node_norm.cu), running statistics updated as BatchNorm1d does;
-    eval mode / other shapes: torch's own ops."""
+    eval mode / other shapes: torch's own ops.  ``group`` / ``n_total``: synchronised statistics over the ranks of a
+    destination-range partition ("needs SyncBN-style statistics")."""
     H = c.shape[-1]
     if (bn.training or not bn.track_running_stats) and bn.affine and c.dim() == 2 and c.shape == x.shape \
-            and H in _ROW_NORM_C and c.shape[0] > 1:
-        return _BnReluRes.apply(c, x, bn.weight, bn.bias, bn.eps, bn)
+            and H in _ROW_NORM_C and (c.shape[0] > 1 or n_total is not None):
+        return _BnReluRes.apply(c, x, bn.weight, bn.bias, bn.eps, bn, group, n_total)
+    if n_total is not None:
+        raise ValueError("bn_relu_residual over a partition needs training mode, affine parameters and H in {16, 32, 64, 128}")
     return (x + torch.relu(bn(c))) / 2

@@ -111,7 +111,11 @@ class _Backbone(nn.Module):
         for i in range(self.num_gnn_layers):
             sink = BF.EdgeGradSink() if (self.edge_updates and e.requires_grad and torch.is_grad_enabled()) else None
             c = self.convs[i].forward_sorted(x, st.fwd, e, gather=gather, sink=sink)
-            x = (x + F.relu(PL.sync_batch_norm(self.batch_norms[i].module, c, part))) / 2
+            bn = self.batch_norms[i].module
+            if bn.training:
+                x = BF.bn_relu_residual(bn, c, x, group=part.group, n_total=part.num_nodes)
+            else:
+                x = (x + F.relu(PL.sync_batch_norm(bn, c, part))) / 2
             if self.edge_updates:
                 e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, gather=gather, sink=sink)
         return x, e

@@ -258,19 +258,28 @@ def bn_relu_res_fwd(c, x, gamma, beta, mean_rstd):
     return ((x + torch.relu(y)) * 0.5).contiguous()
 
 
-def bn_relu_res_bwd(g, c, gamma, beta, mean_rstd):
+def _bn_gr_ch(g, c, gamma, beta, mean_rstd):
     ch = (c - mean_rstd[0]) * mean_rstd[1]
     y = (c - mean_rstd[0]) * (mean_rstd[1] * gamma) + beta
-    gr = torch.where(y > 0, 0.5 * g, torch.zeros_like(g))
-    m1, m2 = gr.double().mean(0).float(), (gr * ch).double().mean(0).float()
-    gc = gamma * mean_rstd[1] * (gr - m1 - ch * m2)
-    return gc.contiguous(), (0.5 * g).contiguous(), (gr * ch).double().sum(0).float(), gr.double().sum(0).float()
+    return torch.where(y > 0, 0.5 * g, torch.zeros_like(g)), ch
+
+
+def bn_bwd_reduce(g, c, gamma, beta, mean_rstd):
+    gr, ch = _bn_gr_ch(g, c, gamma, beta, mean_rstd)
+    return torch.stack([gr.double().sum(0), (gr * ch).double().sum(0)])
+
+
+def bn_bwd_apply(g, c, gamma, beta, mean_rstd, gmeans):
+    gr, ch = _bn_gr_ch(g, c, gamma, beta, mean_rstd)
+    gc = gamma * mean_rstd[1] * (gr - gmeans[0] - ch * gmeans[1])
+    return gc.contiguous(), (0.5 * g).contiguous()
 
 
 _PATCHES = [
     (BF, "_bn_stats", bn_stats),
     (BF, "_bn_relu_res_fwd", bn_relu_res_fwd),
-    (BF, "_bn_relu_res_bwd", bn_relu_res_bwd),
+    (BF, "_bn_bwd_reduce", bn_bwd_reduce),
+    (BF, "_bn_bwd_apply", bn_bwd_apply),
     (BF, "_row_norm_fwd", row_norm_fwd),
     (BF, "_row_norm_bwd", row_norm_bwd),
     (BF, "_col_encode_fwd", col_encode_fwd),
