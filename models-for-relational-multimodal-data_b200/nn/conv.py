@@ -84,7 +84,16 @@ class GINEConv(nn.Module):
             raise ValueError("b200mp GINEConv kernels need edge_dim == in_channels")
         out = BF.gine_aggregate(gather(x) if gather is not None else x, e, self.lin.weight, self.lin.bias, seg, sink, e_eid)
         if self_term:
-            out = out + (1 + self.eps) * x
+            out = torch.addcmul(out, x, 1 + self.eps)
+        return self._apply_nn(out)
+
+    def _apply_nn(self, out: Tensor) -> Tensor:
+        """``self.nn`` (the reference builds Linear -> ReLU -> Linear, gine.py:66-70): its Linears run as node linears
+        on the tcgen05 kernels (functional.linear_group; library GEMM for shapes those do not cover)"""
+        if isinstance(self.nn, torch.nn.Sequential) and all(isinstance(m, (torch.nn.Linear, torch.nn.ReLU)) for m in self.nn):
+            for m in self.nn:
+                out = BF.linear_group(out, (m.weight,), (m.bias,))[0] if isinstance(m, torch.nn.Linear) else torch.relu(out)
+            return out
         return self.nn(out)
 
     def forward(self, x, edge_index: Tensor, edge_attr: Tensor) -> Tensor:
