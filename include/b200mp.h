@@ -219,6 +219,11 @@ int b200mp_add_dropout_layernorm_bwd(const float* g, const float* x, const float
                                      int C, float p_drop, uint64_t seed, const float* gamma, float* gx, float* gsub,
                                      float* ggamma, float* gbeta, void* stream);
 
+/* out = dropout(relu(x)) (g == NULL, first argument x) or its backward out = g * keep_scale where y > 0 (g != NULL, first
+ * argument the saved forward output y): the feed-forward's inner activation of the encoder layer.  numel % 4 == 0. */
+int b200mp_relu_dropout(const float* x_or_y, const float* g, int64_t numel, float p_drop, uint64_t seed, float* out,
+                        void* stream);
+
 /* ------------------------------------------------------------------ column (stype-wise) encoders
  * What the reference's StypeWiseFeatureEncoder call computes (src/utils.py:139-140,357-359, fused.py:71-72;
  * encoders chosen at src/datasets/ibm_transactions_for_aml.py:283-294): every column of every stype -> one

@@ -54,6 +54,7 @@ _SIGS = {
     "b200mp_bn_relu_res_bwd_apply": [_p, _p, _l, _i, _p, _p, _p, _p, _p, _p, _p],
     "b200mp_add_dropout_layernorm_fwd": [_p, _p, _l, _i, _f, C.c_uint64, _p, _p, _f, _p, _p, _p],
     "b200mp_add_dropout_layernorm_bwd": [_p, _p, _p, _p, _l, _i, _f, C.c_uint64, _p, _p, _p, _p, _p, _p],
+    "b200mp_relu_dropout": [_p, _p, _l, _f, C.c_uint64, _p, _p],
     "b200mp_col_encode_fwd": [_p, _i, _p, _l, _i, _p, _p],
     "b200mp_col_encode_bwd": [_p, _i, _i, _l, _i, _p, _p, _p, _p, _p],
     "b200mp_umma_selftest": [_i, _p, _p, _p, _p],

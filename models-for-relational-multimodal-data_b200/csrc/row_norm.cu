@@ -127,6 +127,25 @@ __global__ void __launch_bounds__(256) row_norm_bwd_kernel(RowNormArgs a, const 
     }
 }
 
+
+// y = dropout(relu(x)) (the feed-forward's inner activation, tabgnn.py:199-209) and its backward g_x = g * scale [y > 0]:
+// element-wise over quads, the mask is the same counter hash keyed by the flat quad index
+__global__ void __launch_bounds__(256) relu_dropout_kernel(const float* __restrict__ x, const float* __restrict__ g, int64_t quads,
+                                                           float p, uint64_t seed, float* __restrict__ out) {
+    const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < quads; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = ldg4(x + i * 4);                        // forward: x; backward: the saved output y
+        const float4 ds = p > 0.f ? drop4(seed, i, 0, p, inv_keep) : f4(1.f, 1.f, 1.f, 1.f);
+        if (!g) {
+            st4(out + i * 4, mul4(relu4(v), ds));
+        } else {
+            const float4 gv = ldg4(g + i * 4);
+            st4(out + i * 4, f4(v.x > 0.f ? gv.x * ds.x : 0.f, v.y > 0.f ? gv.y * ds.y : 0.f, v.z > 0.f ? gv.z * ds.z : 0.f,
+                                v.w > 0.f ? gv.w * ds.w : 0.f));
+        }
+    }
+}
+
 static int row_norm_grid(int64_t rows, int lpr) {
     const int64_t iters = (rows + 256 / lpr - 1) / (256 / lpr);
     const int64_t cap = (int64_t)device_info().sms * 8;
@@ -175,6 +194,19 @@ extern "C" int b200mp_add_dropout_layernorm_bwd(const float* g, const float* x, 
         case 16: row_norm_bwd_kernel<16><<<grid, 256, 0, st>>>(a, g, stats, gx, gsub, ggamma, gbeta); break;
         default: row_norm_bwd_kernel<32><<<grid, 256, 0, st>>>(a, g, stats, gx, gsub, ggamma, gbeta); break;
     }
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}
+
+/* x (forward) or the saved output y (backward, g != NULL): numel must be a multiple of 4 */
+extern "C" int b200mp_relu_dropout(const float* x_or_y, const float* g, int64_t numel, float p_drop, uint64_t seed, float* out,
+                                   void* stream) {
+    using namespace b200mp;
+    if (numel < 0 || (numel & 3) || p_drop < 0.f || p_drop >= 1.f) return B200MP_EINVAL;
+    if (numel == 0) return 0;
+    if (!x_or_y || !out) return B200MP_EINVAL;
+    const int64_t quads = numel / 4, want = (quads + 255) / 256, cap = (int64_t)device_info().sms * 16;
+    relu_dropout_kernel<<<(int)(want < cap ? want : cap), 256, 0, (cudaStream_t)stream>>>(x_or_y, g, quads, p_drop, seed, out);
     B200MP_LAUNCH_CHECK();
     return 0;
 }

@@ -642,7 +642,7 @@ def transformer_encoder_layer(layer: torch.nn.TransformerEncoderLayer, x: torch.
     container: same state_dict keys) over column tokens x [R, S, C]: the four projections run as node
     linears (tcgen05 kernels for C = 64, R S >= 4096), the attention core on col_attention.cu; residuals,
     LayerNorms with their dropouts on row_norm.cu (add_dropout_layernorm); the feed-forward's inner
-    activation + dropout are torch element-wise ops."""
+    activation + dropout is relu_dropout (one pass; other activations: torch ops)."""
     if layer.norm_first:
         raise ValueError("b200mp column attention implements the post-norm layer the reference builds")
     R, S, Cc = x.shape
@@ -656,8 +656,12 @@ def transformer_encoder_layer(layer: torch.nn.TransformerEncoderLayer, x: torch.
     sa = linear_group(att.reshape(R * S, Cc), (mha.out_proj.weight,), (mha.out_proj.bias,))[0]
     train = layer.training
     x2 = add_dropout_layernorm(x2, sa, float(layer.dropout1.p) if train else 0.0, layer.norm1)
-    hmid = layer.activation(linear_group(x2, (layer.linear1.weight,), (layer.linear1.bias,))[0])
-    ff = linear_group(layer.dropout(hmid), (layer.linear2.weight,), (layer.linear2.bias,))[0]
+    hmid = linear_group(x2, (layer.linear1.weight,), (layer.linear1.bias,))[0]
+    if layer.activation is torch.nn.functional.relu or isinstance(layer.activation, torch.nn.ReLU):
+        hmid = relu_dropout(hmid, float(layer.dropout.p) if train else 0.0)
+    else:
+        hmid = layer.dropout(layer.activation(hmid))
+    ff = linear_group(hmid, (layer.linear2.weight,), (layer.linear2.bias,))[0]
     x2 = add_dropout_layernorm(x2, ff, float(layer.dropout2.p) if train else 0.0, layer.norm2)
     return x2.view(R, S, Cc)
 
@@ -900,3 +904,39 @@ def bn_relu_residual(bn: torch.nn.BatchNorm1d, c: torch.Tensor, x: torch.Tensor,
     if n_total is not None:
         raise ValueError("bn_relu_residual over a partition needs training mode, affine parameters and H in {16, 32, 64, 128}")
     return (x + torch.relu(bn(c))) / 2
+
+
+# ----------------------------------------------------------------------------- relu + dropout
+def _relu_dropout(x_or_y, g, p, seed):
+    out = torch.empty_like(x_or_y)
+    with torch.cuda.device(x_or_y.device), _track("relu_dropout_bwd" if g is not None else "relu_dropout_fwd"):
+        L.check(L.lib().b200mp_relu_dropout(L.ptr(x_or_y), L.ptr(g), x_or_y.numel(), float(p), C_u64(seed), L.ptr(out), L.stream()),
+                "b200mp_relu_dropout")
+    return out
+
+
+class _ReluDropout(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, p):
+        x = _f32c(x)
+        L.require_cuda(x)
+        seed = 0
+        if p > 0.0:
+            _attn_calls[0] += 1
+            seed = torch.initial_seed() * 0x9E3779B97F4A7C15 + _attn_calls[0] * 0xD1342543DE82EF95
+        y = _relu_dropout(x, None, p, seed)
+        ctx.p, ctx.seed = float(p), seed
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        (y,) = ctx.saved_tensors
+        return _relu_dropout(y, _f32c(g), ctx.p, ctx.seed), None
+
+
+def relu_dropout(x: torch.Tensor, p: float) -> torch.Tensor:
+    """dropout(relu(x), p) in one pass each way (numel % 4 == 0; otherwise torch's ops)"""
+    if x.numel() % 4:
+        return torch.nn.functional.dropout(torch.relu(x), p, p > 0.0)
+    return _ReluDropout.apply(x, float(p))

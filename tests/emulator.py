@@ -275,7 +275,15 @@ def bn_bwd_apply(g, c, gamma, beta, mean_rstd, gmeans):
     return gc.contiguous(), (0.5 * g).contiguous()
 
 
+def relu_dropout_emul(x_or_y, g, p, seed):
+    m = _drop_mask(x_or_y, p, seed)
+    if g is None:
+        return (torch.relu(x_or_y) * m).contiguous()
+    return torch.where(x_or_y > 0, g * m, torch.zeros_like(g)).contiguous()
+
+
 _PATCHES = [
+    (BF, "_relu_dropout", relu_dropout_emul),
     (BF, "_bn_stats", bn_stats),
     (BF, "_bn_relu_res_fwd", bn_relu_res_fwd),
     (BF, "_bn_bwd_reduce", bn_bwd_reduce),

@@ -54,3 +54,20 @@ def test_dropout_mask_is_the_same_in_forward_and_backward():
     assert rel_err(y[~bad], ref[~bad]) < 1e-5
     y2, _ = BF._row_norm_fwd(x, sub, p, seed + 1, gamma, beta, 1e-5)
     assert not torch.equal(y, y2)
+
+
+def test_relu_dropout():
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(5000, 64, device="cuda", generator=g, requires_grad=True)
+    go = torch.randn(5000, 64, device="cuda", generator=g)
+    y = BF.relu_dropout(x, 0.0)
+    y.backward(go)
+    assert torch.equal(y, torch.relu(x.detach())) and torch.equal(x.grad, torch.where(x.detach() > 0, go, torch.zeros_like(go)))
+    y5 = BF._relu_dropout(x.detach(), None, 0.5, 77)
+    r = torch.relu(x.detach())
+    assert bool(((y5 == 0) | (y5 == 2 * r)).all())
+    kept = float((y5[r > 0] > 0).float().mean())
+    assert abs(kept - 0.5) < 0.01
+    gx = BF._relu_dropout(y5, go, 0.5, 77)
+    assert torch.equal(gx, torch.where(y5 > 0, 2 * go, torch.zeros_like(go)))
+    assert not torch.equal(y5, BF._relu_dropout(x.detach(), None, 0.5, 78))
