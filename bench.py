@@ -180,19 +180,21 @@ def cpu_reference_steps(kind, steps, warmup, threads=None):
         if it >= warmup:
             times.append(dt)
     sample = f"{e} edges / {n} nodes (hi_medium edge/node ratio, same generator), {warmup} warm-up + {steps} timed fwd+bwd steps"
-    return e * len(times) / sum(times), cores, sample, sum(times) / len(times)
+    return e * len(times) / sum(times), cores, sample, sum(times) / len(times), n, e
 
 
 def run_reference(args, rank, world):
     if rank != 0:
         return
     steps, warmup = max(1, min(args.steps, 3)), max(1, min(args.warmup, 1))
-    eps, cores, sample, sec = cpu_reference_steps(args.model, steps, warmup)
+    eps, cores, sample, sec, sample_n, sample_e = cpu_reference_steps(args.model, steps, warmup)
     line = {
         "impl": "reference", "metric": "message-passing edges/sec (fwd+bwd)", "value": eps, "unit": "edges/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, world),
+        "config": dict(workload_config(args, world), sampled=True, sample_edges=sample_e, sample_nodes=sample_n,
+                       sample_note="the CPU arm times a bounded sample of the workload (same generator, same edge/node "
+                                   "ratio); edges/s is a rate, so the two arms compare as rates, not as equal problem sizes"),
         "cpu_baseline": {"value": eps, "unit": "edges/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": eps, "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "CPU oracle port of the reference path (reference model files' layer loop over restated PyG 2.5.3 ops); "
@@ -236,13 +238,25 @@ def run_b200(args, rank, world, local_rank):
         _, deg_hist = b200mp.degree_histogram(st.fwd.ptr)
         n_loc, e_loc = n, e
     model = make_model(args.model, deg_hist.cpu(), dev)
-    g = torch.Generator(device=dev).manual_seed(seed + rank)
-    x = torch.randn(n_loc, H, generator=g, device=dev).requires_grad_(True)
-    ea = torch.randn(e_loc, H, generator=g, device=dev).requires_grad_(True)
-    gx = torch.randn(n_loc, H, generator=g, device=dev)
-    ge = torch.randn(e_loc, H, generator=g, device=dev)
+    # inputs are a function of the GLOBAL row id (every rank draws the full tensor from the same seed and keeps its
+    # shard), so the N = 1 / 2 / 4 / 8 runs compute the same function and their checksums are comparable
+    g = torch.Generator(device=dev).manual_seed(seed)
 
-    def step():
+    def draw(rows, shard):
+        full = torch.randn(rows, H, generator=g, device=dev)
+        if part is None:
+            return full
+        out = shard(full)
+        del full
+        return out
+
+    x = draw(n, lambda t: part.shard_nodes(t)).requires_grad_(True)
+    ea = draw(e, lambda t: part.shard_edges(t)).requires_grad_(True)
+    gx = draw(n, lambda t: part.shard_nodes(t))
+    ge = draw(e, lambda t: part.shard_edges(t))
+    torch.cuda.empty_cache()
+
+    def step(keep=False):
         if part is None:
             ox, oe = model.message_passing(x, ei, ea)
         else:
@@ -250,9 +264,19 @@ def run_b200(args, rank, world, local_rank):
         torch.autograd.backward([ox, oe], [gx, ge])
         if part is not None:
             PL.all_reduce_gradients(model, part)
+        res = None
+        if keep:          # checksum of one step (outside the timed region): fp64 sums over ALL ranks' rows
+            gw = torch.cat([p.grad.reshape(-1) for p in model.parameters() if p.grad is not None]).double()
+            loc = torch.stack([ox.detach().double().sum(), ox.detach().double().abs().sum(), oe.detach().double().sum(),
+                               oe.detach().double().abs().sum(), x.grad.double().abs().sum(), ea.grad.double().abs().sum()])
+            if world > 1:
+                dist.all_reduce(loc)
+            res = {"sum_x": float(loc[0]), "abs_x": float(loc[1]), "sum_e": float(loc[2]), "abs_e": float(loc[3]),
+                   "abs_grad_x": float(loc[4]), "abs_grad_e": float(loc[5]), "weight_grad_norm": float(gw.norm())}
         x.grad = None
         ea.grad = None
         model.zero_grad(set_to_none=True)
+        return res
 
     def barrier():
         if world > 1:
@@ -266,21 +290,25 @@ def run_b200(args, rank, world, local_rank):
     barrier()
     clocks.start()
     BF.set_kernel_stats(stats)
-    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t0.record()
-    for _ in range(args.steps):
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    marks[0].record()
+    for k in range(args.steps):
         step()
-    t1.record()
+        marks[k + 1].record()
     barrier()
     BF.set_kernel_stats(None)
     clk = clocks.stop()
-    ms = t0.elapsed_time(t1)
+    ms = marks[0].elapsed_time(marks[-1])
+    per_step = sorted(marks[k].elapsed_time(marks[k + 1]) for k in range(args.steps))
+    ms_median = per_step[len(per_step) // 2] if len(per_step) % 2 else 0.5 * (per_step[len(per_step) // 2 - 1] + per_step[len(per_step) // 2])
     if world > 1:
-        t = torch.tensor([ms], device=dev)
+        t = torch.tensor([ms, ms_median], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        ms, ms_median = float(t[0].item()), float(t[1].item())
     ms_step = ms / args.steps
     value = e / (ms_step * 1e-3)                 # N > 1: ONE graph partitioned over the ranks (strong scaling)
+    checksum = step(keep=True)
+    torch.cuda.synchronize()
 
     # per-kernel accounting -> roofline of the dominant kernel
     summ = stats.summary()
@@ -294,7 +322,9 @@ def run_b200(args, rank, world, local_rank):
     top = max(((k, v) for k, v in summ.items() if k in KERNEL_BYTES), key=lambda kv: kv[1][1])[0]
     achieved = kern[top]["achieved_gbs"]
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 4), "traffic": ncu_traffic(top, args.workload, world), "peak_source": peak_src,
+                "frac": round(achieved / peak, 4), "traffic": ncu_traffic(top, args.workload, world),
+                "traffic_source": "profiles/traffic.json: ncu --set full dram__bytes_read+write per launch, captured on the build named in that file (not this run)",
+                "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": KERNEL_BYTES[top] * e_loc}
     step_bytes = LAYERS * (e_loc * algorithmic_bytes_per_edge(args.model) + n_loc * 12 * 4 * H)
     step_roofline = {"algorithmic_bytes_per_step": step_bytes, "achieved_gbs": round(step_bytes / (ms_step * 1e-3) / 1e9, 1),
@@ -309,26 +339,29 @@ def run_b200(args, rank, world, local_rank):
         del st
         BG.clear_cache()
         hx, hea, hei = x.detach().cpu().pin_memory(), ea.detach().cpu().pin_memory(), ei.cpu().pin_memory()
-        del ea, ge, part
+        del ea, ge, part, gx
         torch.cuda.empty_cache()
         h2d = hx.numel() * 4 + hea.numel() * 4 + hei.numel() * 8
         e2e_steps = max(1, min(args.steps, 3))
 
         from b200mp import DeviceFeeder
         feeder = DeviceFeeder(dev)
-        host = (hx, hea, hei)
+        host = (hx, hea, hei) if world == 1 else (hx, hea)     # N > 1: the rank's shard; the partition is built once
 
         def e2e_step():
             # this step's inputs were staged during the previous step; start the NEXT step's copy now so that it
             # overlaps this step's kernels (one H2D of all inputs per step, on the copy stream)
-            dx, dea, dei = feeder.take()
+            bufs = feeder.take()
+            dx, dea, dei = bufs[0], bufs[1], (bufs[2] if world == 1 else None)
             feeder.stage(host)
             BG.clear_cache()
             dx, dea = dx.detach().requires_grad_(True), dea.detach().requires_grad_(True)
             if world == 1:
                 ox, oe = model.message_passing(dx, dei, dea)
             else:
-                p2 = PL.partition_graph(dei, n, rank, world)
+                # the partition (which rank owns which destination range, local CSC slice) is a property of the graph:
+                # built once, outside the timed steps; the per-step work is the shard's H2D + fwd + bwd
+                p2 = e2e_part[0]
                 ox, oe = model.message_passing_partitioned(dx, dea, p2)
             loss = ox.square().mean() + oe.square().mean()
             loss.backward()
@@ -338,6 +371,7 @@ def run_b200(args, rank, world, local_rank):
             feeder.release()
             return float(loss.item())          # D2H read of the step's result
 
+        e2e_part = [PL.partition_graph(ei, n, rank, world) if world > 1 else None]
         feeder.stage(host)
         e2e_step()
         barrier()
@@ -358,7 +392,9 @@ def run_b200(args, rank, world, local_rank):
         e2e = {"value": e / (ems / e2e_steps * 1e-3), "unit": "edges/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 4, "steps": e2e_steps, "ms_per_step": ems / e2e_steps,
                "includes": "H2D of x, edge_index, edge features from pinned host memory (one copy of all inputs per step, "
-                           "double-buffered on a copy stream: step i+1's copy overlaps step i's kernels); CSC build; fwd+bwd; loss D2H"}
+                           "double-buffered on a copy stream: step i+1's copy overlaps step i's kernels); CSC build; fwd+bwd; loss D2H"
+                           if world == 1 else "H2D of this rank's shard of x and the edge features from pinned host memory "
+                           "(double-buffered); fwd+bwd over the partition (built once, outside the timed steps); loss D2H"}
     except Exception as ex:          # reported, never silently dropped
         e2e = {"value": None, "unit": "edges/s", "error": f"{type(ex).__name__}: {ex}"[:300]}
 
@@ -366,12 +402,16 @@ def run_b200(args, rank, world, local_rank):
         return
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        eps, cores, sample, _ = cpu_reference_steps(args.model, 2, 1)
+        eps, cores, sample, *_ = cpu_reference_steps(args.model, 2, 1)
         cpu = {"value": eps, "unit": "edges/s", "cores": cores, "kind": "port", "sample": sample}
+        if cores > 4:          # BASELINE.md / benchmark.py:50: the reference's own benchmark pins 4 threads
+            eps4, *_ = cpu_reference_steps(args.model, 1, 1, threads=4)
+            cpu["value_4_threads"] = eps4
     line = {
         "metric": "message-passing edges/sec (fwd+bwd)", "value": value, "unit": "edges/s", "n_gpus": world,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-        "scaling": "weak" if world == 1 else "strong",
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "ms_per_step_median": ms_median,
+        "value_median": e / (ms_median * 1e-3), "higher_is_better": True,
+        "scaling": "weak" if world == 1 else "strong", "checksum": checksum,
         "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
         "clocks": clk, "e2e": e2e, "gpu_launches": stats.launches, "roofline": roofline, "step_roofline": step_roofline,
         "kernels": kern, "cpu_baseline": cpu,
@@ -400,7 +440,6 @@ def main():
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ["NCCL_DEBUG"] = "WARN"            # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
         run_b200(args, rank, world, local_rank)

@@ -10,6 +10,7 @@
 #include "common.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <cstdio>
 #include <cstdlib>
 
 namespace b200mp {
@@ -34,7 +35,15 @@ bool use_tensor_cores() {
 
 int persistent_grid(const void* kernel, size_t smem, int64_t work_items, int threads) {
     int per_sm = 1;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
+    cudaError_t oe = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem);
+    static const bool dbg = [] { const char* v = getenv("B200MP_DEBUG_OCC"); return v && v[0] == '1'; }();
+    if (dbg) {          // diagnostics: resident CTAs per SM of every persistent kernel (stderr)
+        cudaFuncAttributes fa{};
+        cudaFuncGetAttributes(&fa, kernel);
+        fprintf(stderr, "[b200mp occ] kernel %p: threads %d dyn smem %zu static smem %zu regs %d -> %d CTA/SM (%s)\n", kernel, threads,
+                smem, fa.sharedSizeBytes, fa.numRegs, per_sm, cudaGetErrorString(oe));
+    }
+    if (oe != cudaSuccess || per_sm < 1) { per_sm = 1; (void)cudaGetLastError(); }
     int64_t g = (int64_t)device_info().sms * per_sm;
     if (work_items < g) g = work_items;
     return (int)(g < 1 ? 1 : g);

@@ -32,3 +32,31 @@ def test_feeder_round_trip_and_errors():
         f.release()
     f.drain()
     assert f.bytes_staged == sum(a.numel() * 4 + b.numel() * 8 for a, b in batches)
+
+
+def test_feeder_varying_shapes_keep_their_bytes():
+    """sampled batches change shape every step (ibm_transactions_for_aml.py:61-112): the two arenas grow a few times and
+    are then re-used as views; no batch may be overwritten while the step that reads it is still running"""
+    dev = torch.device("cuda", 0)
+    f = b200mp.DeviceFeeder(dev)
+    g = torch.Generator().manual_seed(0)
+    sizes = [int(s) for s in torch.randint(50_000, 400_000, (12,), generator=g)]
+    batches = [(torch.randn(s, 64, generator=g).pin_memory(), torch.randint(0, 1000, (2, s), generator=g).pin_memory(),
+                torch.randn(s // 7, 3, generator=g).pin_memory()) for s in sizes]
+    f.stage(batches[0])
+    outs = []
+    for i, b in enumerate(batches):
+        x, ei, y = f.take()
+        if i + 1 < len(batches):
+            f.stage(batches[i + 1])
+        acc = x
+        for _ in range(30):                              # long-running consumer of THIS batch while the next copy is in flight
+            acc = acc * 1.0001 + 0.0
+        outs.append((acc.sum(), x.double().sum(), ei.sum(), y.double().sum()))
+        f.release()
+    f.drain()
+    torch.cuda.synchronize()
+    for (acc, sx, sei, sy), (hx, hei, hy) in zip(outs, batches):
+        assert float(sx) == pytest.approx(float(hx.double().sum()), rel=1e-12, abs=1e-9)
+        assert int(sei) == int(hei.sum()) and float(sy) == pytest.approx(float(hy.double().sum()), rel=1e-12, abs=1e-9)
+    assert f.reallocations <= 2 * 6                        # arenas grow geometrically, they are not rebuilt per batch
