@@ -279,6 +279,30 @@ int b200mp_sample_hop_fill(const int64_t* colptr, const int64_t* frontier, int64
 int b200mp_first_occurrence(const int64_t* cand, int64_t K, uint8_t* visited, uint64_t* first, uint8_t* flags,
                             void* stream);
 
+/* ------------------------------------------------------------------ read-out heads, ranking metric, pooled write-back
+ * (kernels in csrc/readout.cu)
+ *
+ * b200mp_pair_gather_act: first layer of the reference's edge read-out heads with its two node gathers
+ *   (src/nn/gnn/decoder.py:17-21 ClassifierHead.forward, :62-71 LinkPredHead.forward):
+ *     out[e] = act(Rs[src[e]] + Rd[dst[e]] + T[e]),  act = relu (relu != 0) or identity
+ *   with Rs = relu(x) Ws^T, Rd = relu(x) Wd^T ([N, W]) and T = edge_attr We^T + b ([E, W]) computed by the caller: relu is
+ *   element-wise, so this equals Linear([relu(x[src]) | relu(x[dst]) | edge_attr]) without ever building the [E, 3H]
+ *   concatenation.  Any of Rs / Rd / T may be NULL.  W % 4 == 0; src / dst int64 (edge_index rows).
+ * b200mp_rank_positive: SSMetric.mrr's ranking (src/utils/metric.py:30-43): rank[b] = position (1-based) of pos[b] in the
+ *   descending order of [neg[b, 0..K), pos[b]], the positive last among equal scores (a stable argsort of -combined).
+ * b200mp_segment_mean_blend_fwd / _bwd: pooled write-back of the fused layer (src/nn/models/fused.py:256-268):
+ *   index = target_edge_index.flatten() sorted by node with b200mp_csc_build (ptr [N+1], perm [R]);
+ *     out[n] = deg_n > 0 ? (x[n] + mean_{k in segment n} emb[perm[k]]) / 2 : x[n]
+ *   backward: gx[n] = g[n] * (deg_n > 0 ? 1/2 : 1),  gemb[r] = g[index[r]] / (2 deg_index[r])  (gx / gemb nullable).
+ * No atomics: all four are run-to-run identical. */
+int b200mp_pair_gather_act(const float* Rs, const float* Rd, const float* T, const int64_t* src, const int64_t* dst,
+                           int64_t E, int W, int relu, float* out, void* stream);
+int b200mp_rank_positive(const float* pos, const float* neg, int64_t B, int K, int32_t* rank, void* stream);
+int b200mp_segment_mean_blend_fwd(const float* x, const float* emb, const int64_t* ptr, const int64_t* perm, int64_t N,
+                                  int W, float* out, void* stream);
+int b200mp_segment_mean_blend_bwd(const float* g, const int64_t* ptr, const int64_t* index, int64_t N, int64_t R, int W,
+                                  float* gx, float* gemb, void* stream);
+
 /* ------------------------------------------------------------------ tensor-core self test
  * One-CTA check of the tcgen05 building blocks (csrc/umma.cuh) used by the per-edge kernels:
  *   mode 0: Y[128,64] = X[128,64] W[64,64]^T     mode 1: Y = X W      (3xTF32)

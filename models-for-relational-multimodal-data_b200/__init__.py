@@ -11,7 +11,9 @@ from .feeder import DeviceFeeder   # noqa: F401
 from .sampling import NeighborSampler, generate_negative_samples   # noqa: F401
 from .graph import (EdgeStructure, SegmentIndex, degree, degree_histogram, edge_structure,   # noqa: F401
                     relabel, to_csc)
-from .nn import (BatchNorm, GINe, GINEConv, GINEConvHetero, Linear, PNAConv, PNAConvHetero, PNAS,   # noqa: F401
-                 TABGNN, TABGNNFused, TABGNNInterleaved)
+from .nn import (CPNA, CPNATAB, BatchNorm, ClassifierHead, GINe, GINEConv, GINEConvHetero, Linear, LinkPredFusedHead,   # noqa: F401
+                 LinkPredHead, NodeClassificationHead, PNAConv, PNAConvHetero, PNAS, TABGNN, TABGNNFused, TABGNNInterleaved)
+from .losses import SSLoss      # noqa: F401
+from .metrics import SSMetric   # noqa: F401
 
 __version__ = "0.1.0"

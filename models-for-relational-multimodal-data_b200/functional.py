@@ -940,3 +940,137 @@ def relu_dropout(x: torch.Tensor, p: float) -> torch.Tensor:
     if x.numel() % 4:
         return torch.nn.functional.dropout(torch.relu(x), p, p > 0.0)
     return _ReluDropout.apply(x, float(p))
+
+
+# ----------------------------------------------------------------------------- read-out: pair gather, ranking, pooled write-back
+def _pair_gather_act(Rs, Rd, T, src, dst, E, W, relu):
+    dev = (T if T is not None else Rs if Rs is not None else Rd).device
+    out = torch.empty((E, W), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _track("pair_gather_act"):
+        L.check(L.lib().b200mp_pair_gather_act(L.ptr(Rs), L.ptr(Rd), L.ptr(T), L.ptr(src), L.ptr(dst), E, W, int(relu), L.ptr(out),
+                                               L.stream()), "b200mp_pair_gather_act")
+    return out
+
+
+def _segment_sum_rows(seg: SegmentIndex, rows_sorted):
+    """sum of the rows of each segment ([E, W] in segment order -> [N, W]); W in {16, 32, 64, 128}"""
+    return _segment_reduce(1, seg, rows_sorted, rows_sorted.shape[1])[0]
+
+
+_SEG_W = (16, 32, 64, 128)
+
+
+def _pad_width(W: int) -> int:
+    for w in _SEG_W:
+        if W <= w:
+            return w
+    raise L.B200MPError(f"read-out widths up to {_SEG_W[-1]} are supported, got {W}")
+
+
+class _PairGatherAct(torch.autograd.Function):
+    """act(Rs[src] + Rd[dst] + T) for [N, W] node tables and an [E, W] edge table (any may be None).  Backward without
+    atomics: the masked gradient is summed per destination over the CSC order and per source over the CSR order of
+    edge_index (the structure is built on first use and cached, graph.edge_structure)."""
+
+    @staticmethod
+    def forward(ctx, Rs, Rd, T, edge_index, relu):
+        Rs, Rd, T = (None if t is None else _f32c(t) for t in (Rs, Rd, T))
+        L.require_cuda(Rs, Rd, T, edge_index)
+        ref = T if T is not None else (Rs if Rs is not None else Rd)
+        if edge_index.dtype != torch.int64 or edge_index.dim() != 2 or edge_index.shape[0] != 2:
+            raise TypeError("edge_index must be int64 [2, E]")
+        ei = edge_index.contiguous()
+        E, W = int(ei.shape[1]), int(ref.shape[1])
+        if W not in _SEG_W:
+            raise L.B200MPError(f"pair_gather_act needs a width in {_SEG_W} (pad the weights), got {W}")
+        out = _pair_gather_act(Rs, Rd, T, ei[0], ei[1], E, W, relu)
+        ctx.relu, ctx.ei = bool(relu), ei
+        ctx.nS = None if Rs is None else Rs.shape[0]
+        ctx.nD = None if Rd is None else Rd.shape[0]
+        ctx.has_T = T is not None
+        ctx.save_for_backward(out if relu else None)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        from .graph import edge_structure
+        (out,) = ctx.saved_tensors
+        g = _f32c(g)
+        gz = _relu_dropout(out, g, 0.0, 0) if ctx.relu else g          # g where out > 0
+        gRs = gRd = None
+        n = max(ctx.nS or 0, ctx.nD or 0)
+        if (ctx.nS is not None and ctx.needs_input_grad[0]) or (ctx.nD is not None and ctx.needs_input_grad[1]):
+            st = edge_structure(ctx.ei, n, reverse=ctx.nS is not None and ctx.needs_input_grad[0])
+            if ctx.nD is not None and ctx.needs_input_grad[1]:
+                gRd = _segment_sum_rows(st.fwd, _permute(gz, st.fwd.perm, False))[: ctx.nD]
+            if ctx.nS is not None and ctx.needs_input_grad[0]:
+                gRs = _segment_sum_rows(st.rev, _permute(gz, st.rev.perm, False))[: ctx.nS]
+        return gRs, gRd, (gz if ctx.has_T and ctx.needs_input_grad[2] else None), None, None
+
+
+def pair_gather_act(Rs, Rd, T, edge_index, relu=True):
+    """``act(Rs[edge_index[0]] + Rd[edge_index[1]] + T)`` (decoder.py:17-21, :62-71 after hoisting the first Linear)."""
+    return _PairGatherAct.apply(Rs, Rd, T, edge_index, relu)
+
+
+def rank_positive(pos: torch.Tensor, neg: torch.Tensor, num_neg: int) -> torch.Tensor:
+    """int32 [B]: 1-based rank of every positive score among its ``num_neg`` negatives (metric.py:30-43), on the device."""
+    pos = pos.detach().reshape(-1).float().contiguous()
+    neg = neg.detach().reshape(-1).float().contiguous()
+    L.require_cuda(pos, neg)
+    B = pos.numel()
+    if neg.numel() != B * num_neg:
+        raise ValueError(f"expected {B} x {num_neg} negative scores, got {neg.numel()}")
+    return _rank_positive(pos, neg, B, int(num_neg))
+
+
+def _rank_positive(pos, neg, B, K):
+    rank = torch.empty(B, dtype=torch.int32, device=pos.device)
+    with torch.cuda.device(pos.device), _track("rank_positive"):
+        L.check(L.lib().b200mp_rank_positive(L.ptr(pos), L.ptr(neg), B, K, L.ptr(rank), L.stream()), "b200mp_rank_positive")
+    return rank
+
+
+def _segment_mean_blend_fwd(x, emb, ptr, perm):
+    out = torch.empty_like(x)
+    with torch.cuda.device(x.device), _track("segment_mean_blend_fwd"):
+        L.check(L.lib().b200mp_segment_mean_blend_fwd(L.ptr(x), L.ptr(emb), L.ptr(ptr), L.ptr(perm), x.shape[0], x.shape[1], L.ptr(out),
+                                                      L.stream()), "b200mp_segment_mean_blend_fwd")
+    return out
+
+
+def _segment_mean_blend_bwd(g, ptr, index, R, need_x, need_emb):
+    N, W = g.shape
+    gx = torch.empty_like(g) if need_x else None
+    gemb = torch.empty((R, W), dtype=torch.float32, device=g.device) if need_emb else None
+    with torch.cuda.device(g.device), _track("segment_mean_blend_bwd"):
+        L.check(L.lib().b200mp_segment_mean_blend_bwd(L.ptr(g), L.ptr(ptr), L.ptr(index), N, R, W, L.ptr(gx), L.ptr(gemb), L.stream()),
+                "b200mp_segment_mean_blend_bwd")
+    return gx, gemb
+
+
+class _SegmentMeanBlend(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, emb, index):
+        from .graph import build_segment_index
+        x, emb = _f32c(x), _f32c(emb)
+        L.require_cuda(x, emb, index)
+        index = index.contiguous().view(-1)
+        if index.numel() != emb.shape[0] or emb.shape[1] != x.shape[1] or x.shape[1] % 4:
+            raise ValueError("segment_mean_blend: emb must be [len(index), W] with x [N, W], W % 4 == 0")
+        seg = build_segment_index(index, index, x.shape[0])
+        ctx.save_for_backward(seg.ptr, index)
+        ctx.R = emb.shape[0]
+        return _segment_mean_blend_fwd(x, emb, seg.ptr, seg.perm)
+
+    @staticmethod
+    def backward(ctx, g):
+        ptr, index = ctx.saved_tensors
+        gx, gemb = _segment_mean_blend_bwd(_f32c(g), ptr, index, ctx.R, ctx.needs_input_grad[0], ctx.needs_input_grad[1])
+        return gx, gemb, None
+
+
+def segment_mean_blend(x: torch.Tensor, emb: torch.Tensor, index: torch.Tensor) -> torch.Tensor:
+    """rows of ``x`` named in ``index`` become ``(x[n] + mean of the emb rows with index == n) / 2``, the others are copied:
+    the ``unique`` / ``index_add_`` / ``bincount`` write-back of models/fused.py:256-268 as one pass without atomics."""
+    return _SegmentMeanBlend.apply(x, emb, index)

@@ -201,3 +201,101 @@ class PNAS(_Backbone):
         x = self.node_emb(x.view(x.shape[0], -1))
         e = self.edge_emb(edge_attr.view(edge_attr.shape[0], -1))
         return self._layers(x, edge_index, e)
+
+
+# ----------------------------------------------------------------------------- per-column PNA
+class _ColumnStacks(nn.Module):
+    """Shared body of ``CPNA`` (/root/reference/src/nn/gnn/pna.py:164-231) and ``CPNATAB`` (:233-304): one PNA stack per
+    edge COLUMN -- ``col_convs[c][i]``, ``col_batch_norms[c][i]``, ``col_emlps[c][i]`` -- run column after column over the
+    SAME node state x (column c + 1 starts from the x column c produced, pna.py:219-230), each updating only its own
+    [E, H] column of edge_attr.  The CSC structure is built once for all K * L conv calls; every column is read from and
+    written back to the caller's [E, K, H] layout through the kernels' row maps (no permutation passes for H = 64)."""
+
+    def _init_stacks(self, num_features, num_gnn_layers, n_hidden, edge_updates, edge_dim, final_dropout, deg, reverse_mp):
+        self.n_hidden = n_hidden
+        self.num_gnn_layers = num_gnn_layers
+        self.edge_updates = edge_updates
+        self.final_dropout = final_dropout
+        self.reverse_mp = reverse_mp
+        self.num_cols = edge_dim // n_hidden
+        aggregators = ['mean', 'min', 'max', 'std']
+        scalers = ['identity', 'amplification', 'attenuation']
+        self.node_emb = nn.Linear(num_features, n_hidden)
+        self.col_convs = nn.ModuleList()
+        self.col_emlps = nn.ModuleList()
+        self.col_batch_norms = nn.ModuleList()
+        for _ in range(self.num_cols):
+            convs, emlps, batch_norms = nn.ModuleList(), nn.ModuleList(), nn.ModuleList()
+            for _ in range(num_gnn_layers):
+                kw = dict(in_channels=n_hidden, out_channels=n_hidden, aggregators=aggregators, scalers=scalers, deg=deg,
+                          edge_dim=n_hidden, towers=1, pre_layers=1, post_layers=1, divide_input=False)
+                convs.append(PNAConvHetero(n_hidden=n_hidden, **kw) if reverse_mp else PNAConv(**kw))
+                if edge_updates:
+                    emlps.append(nn.Sequential(nn.Linear(3 * n_hidden, n_hidden), nn.ReLU(), nn.Linear(n_hidden, n_hidden)))
+                batch_norms.append(BatchNorm(n_hidden))
+            self.col_convs.append(convs)
+            self.col_emlps.append(emlps)
+            self.col_batch_norms.append(batch_norms)
+
+    def _columns(self, x, edge_index, edge_attr):
+        """-> (x, [K] list of updated [E, H] columns in the caller's edge order)"""
+        x = self.node_emb(x.view(x.shape[0], -1))
+        st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
+        L = self.num_gnn_layers
+        fast = (not self.reverse_mp) and x.shape[1] == 64 and BF.row_maps_available()
+        perm32 = st.fwd.perm32() if fast else None
+        cols = []
+        for c in range(self.num_cols):
+            e_in = e = edge_attr[:, c, :].contiguous()
+            if not fast:
+                e = BF.gather_rows(e, st.fwd.perm)
+            for i in range(L):
+                sink = BF.EdgeGradSink() if (self.edge_updates and e.requires_grad and torch.is_grad_enabled()) else None
+                bn = self.col_batch_norms[c][i].module
+                if fast:
+                    e_eid = perm32 if (i == 0 or not self.edge_updates) else None
+                    out_eid = perm32 if i == L - 1 else None
+                    x = BF.bn_relu_residual(bn, self.col_convs[c][i].forward_sorted(x, st.fwd, e, sink=sink, e_eid=e_eid), x)
+                    if self.edge_updates:
+                        e = edge_update_sorted(self.col_emlps[c][i], x, st, e, 1.0, 0.5, sink=sink, e_eid=e_eid, out_eid=out_eid)
+                else:
+                    x = BF.bn_relu_residual(bn, _conv_sorted(self.col_convs[c][i], x, st, e, sink), x)
+                    if self.edge_updates:
+                        e = edge_update_sorted(self.col_emlps[c][i], x, st, e, 1.0, 0.5, sink=sink)
+            if not self.edge_updates:
+                e = e_in
+            elif not fast:
+                e = BF.scatter_rows(e, st.fwd.perm)
+            cols.append(e)
+        return x, cols
+
+
+class CPNA(_ColumnStacks):
+    def __init__(self, num_features, num_gnn_layers, n_classes=2, n_hidden=128, edge_updates=True, edge_dim=None, dropout=0.0,
+                 final_dropout=0.5, deg=None, reverse_mp=False):
+        super().__init__()
+        self._init_stacks(num_features, num_gnn_layers, n_hidden, edge_updates, edge_dim, final_dropout, deg, reverse_mp)
+
+    def forward(self, x, edge_index, edge_attr):
+        x, cols = self._columns(x, edge_index, edge_attr)
+        return x, torch.stack(cols, dim=1)          # the reference writes the columns back in place (pna.py:230)
+
+
+class CPNATAB(_ColumnStacks):
+    def __init__(self, num_features, num_gnn_layers, n_classes=2, n_hidden=128, edge_updates=True, edge_dim=None, dropout=0.0,
+                 final_dropout=0.5, deg=None, reverse_mp=False):
+        super().__init__()
+        self._init_stacks(num_features, num_gnn_layers, n_hidden, edge_updates, edge_dim, final_dropout, deg, reverse_mp)
+        self.row_atts = nn.ModuleList()
+        self.row_norms = nn.ModuleList()
+        for _ in range(self.num_cols):               # one per COLUMN, indexed by LAYER in forward: pna.py:279-280, 299-300
+            self.row_norms.append(nn.LayerNorm(n_hidden))
+            self.row_atts.append(nn.TransformerEncoderLayer(n_hidden, nhead=8, batch_first=True))
+
+    def forward(self, x, edge_index, edge_attr):
+        x, cols = self._columns(x, edge_index, edge_attr)
+        tok = torch.stack(cols, dim=1)
+        for i in range(self.num_gnn_layers):         # attention over the K column tokens of every edge row (pna.py:299-300)
+            att = BF.transformer_encoder_layer(self.row_atts[i], tok)
+            tok = (tok + BF.add_dropout_layernorm(att, None, 0.0, self.row_norms[i])) / 2
+        return x, tok

@@ -282,11 +282,8 @@ class FTTransformerPNAFusedLayer(_MixedLayer):
             z = torch.cat([cls, x[target_edge_index[0]], x[target_edge_index[1]]], dim=-1)
             z = (z + self.fuse_norm(self.fuse(z))) / 2
             x_tab = torch.cat([((cls + z[:, :C]) / 2).unsqueeze(1), x_tab[:, 1:, :]], dim=1)
-            index = target_edge_index.reshape(-1)
-            emb = torch.cat([z[:, C:C + H], z[:, C + H:]], dim=0)
-            summed = torch.zeros_like(x).index_add_(0, index, emb)
-            count = torch.bincount(index, minlength=x.shape[0]).to(x.dtype).unsqueeze(1)
-            x = torch.where(count > 0, (x + summed / count.clamp(min=1)) / 2, x)
+            # mean of the target-edge embeddings per node, averaged into x (:260-268): one kernel pass, no unique / atomics
+            x = BF.segment_mean_blend(x, torch.cat([z[:, C:C + H], z[:, C + H:]], dim=0), target_edge_index.reshape(-1))
         return x_tab, x, e
 
     def forward(self, x_tab, x_gnn, edge_index, edge_attr, target_edge_index, lp=False):

@@ -229,6 +229,85 @@ def tabgnn_fused(p: Params, x: Tensor, edge_index: Tensor, edge_attr: Tensor,
     return x_gnn, e, tgt
 
 
+# ----------------------------------------------------------------- per-column PNA (f4)
+def _column_stacks(p: Params, x, edge_index, edge_attr, num_layers, edge_updates, reverse_mp, training):
+    """The column loop shared by CPNA.forward (src/nn/gnn/pna.py:215-231) and CPNATAB.forward (:284-297): the node state
+    x runs through the K column stacks one after the other; column c's stack only touches edge_attr[:, c, :]."""
+    x = _lin(p, "node_emb", x.reshape(x.shape[0], -1))
+    src, dst = edge_index[0], edge_index[1]
+    cols = []
+    for c in range(edge_attr.shape[1]):
+        e = edge_attr[:, c, :]
+        for i in range(num_layers):
+            h = _conv(p, f"col_convs.{c}.{i}.", "pna", reverse_mp, x, edge_index, e, AGG_PNAS)
+            h = PF.batch_norm(sub_inplace(p, f"col_batch_norms.{c}.{i}."), h, training)
+            x = (x + F.relu(h)) / 2
+            if edge_updates:
+                e = e + _emlp(p, f"col_emlps.{c}.{i}.", torch.cat([x[src], x[dst], e], dim=-1)) / 2
+        cols.append(e)
+    return x, torch.stack(cols, dim=1)
+
+
+def cpna(p: Params, x, edge_index, edge_attr, num_layers, edge_updates=True, reverse_mp=False, training=True):
+    """CPNA.forward, src/nn/gnn/pna.py:215-231."""
+    return _column_stacks(p, x, edge_index, edge_attr, num_layers, edge_updates, reverse_mp, training)
+
+
+def cpnatab(p: Params, x, edge_index, edge_attr, num_layers, edge_updates=True, reverse_mp=False, training=True, nhead=8):
+    """CPNATAB.forward, src/nn/gnn/pna.py:284-302 (dropout 0 / eval): column stacks, then num_layers rounds of attention over
+    the K column tokens of every edge row, (t + row_norms[i](row_atts[i](t))) / 2."""
+    x, t = _column_stacks(p, x, edge_index, edge_attr, num_layers, edge_updates, reverse_mp, training)
+    C = t.shape[-1]
+    for i in range(num_layers):
+        a = transformer_encoder_layer(p, f"row_atts.{i}.", t, nhead)
+        t = (t + F.layer_norm(a, (C,), p[f"row_norms.{i}.weight"], p[f"row_norms.{i}.bias"])) / 2
+    return x, t
+
+
+# ----------------------------------------------------------------- self-supervised losses / ranking metric (f3)
+def lp_loss(pos_pred, neg_pred):
+    """SSLoss.lp_loss, src/utils/loss.py:11-12."""
+    return -torch.log(pos_pred + 1e-12).mean() - torch.log(1 - neg_pred + 1e-12).mean()
+
+
+def mcm_loss(cat_out, num_out, y, num_numerical):
+    """SSLoss.mcm_loss, src/utils/loss.py:41-72, sample by sample as the reference loops."""
+    cat_loss = torch.zeros((), dtype=num_out.dtype)
+    num_loss = torch.zeros((), dtype=num_out.dtype)
+    acc = t_c = t_n = 0
+    for i in range(y.shape[0]):
+        val, idx = y[i, 0], int(y[i, 1])
+        if idx >= num_numerical:
+            logits = cat_out[idx - num_numerical][i]
+            cat_loss = cat_loss + F.cross_entropy(logits.unsqueeze(0), val.long().reshape(1), reduction="sum")
+            acc += int(torch.argmax(logits) == val.long())
+            t_c += 1
+        else:
+            num_loss = num_loss + (num_out[i, idx] - val) ** 2
+            t_n += 1
+    if t_c == 0:
+        total = torch.sqrt(num_loss / t_n)
+    elif t_n == 0:
+        total = cat_loss / t_c
+    else:
+        total = cat_loss / t_c + torch.sqrt(num_loss / t_n)
+    return total, (cat_loss, t_c, acc), (num_loss, t_n)
+
+
+def mrr(pos_pred, neg_pred, ks, num_neg):
+    """SSMetric.mrr, src/utils/metric.py:11-52: rank of each positive in the descending order of [negatives, positive]
+    (stable sort: the positive comes last among equal scores); returns (mrr, {hits@k})."""
+    import numpy as np
+    pos = pos_pred.detach().cpu().numpy().flatten()
+    neg = neg_pred.detach().cpu().numpy().flatten().reshape(len(pos), num_neg)
+    ranks = []
+    for pz, ng in zip(pos, neg):
+        comb = np.concatenate([ng, [pz]])
+        ranks.append(int((-comb).argsort(kind="stable").argsort(kind="stable")[-1]) + 1)
+    ranks = np.asarray(ranks)
+    return float(np.mean(1.0 / ranks)), {f"hits@{k}": float(np.mean(ranks <= k)) for k in ks}, ranks
+
+
 # ----------------------------------------------------------------- read-out heads
 def classifier_head(p: Params, x: Tensor, edge_index: Tensor, edge_attr: Tensor) -> Tensor:
     """ClassifierHead.forward (eval / dropout 0), src/nn/gnn/decoder.py:17-21; keys mlp.{0,3,6}."""

@@ -59,10 +59,18 @@ def load():
     inter = _load("refsrc.nn.models.inteleaved", "src/nn/models/inteleaved.py")
     ns = types.SimpleNamespace(
         GINe=gine.GINe, GINEConvHetero=gine.GINEConvHetero,
-        PNAS=pna.PNAS, PNAConvHetero=pna.PNAConvHetero,
+        PNAS=pna.PNAS, PNAConvHetero=pna.PNAConvHetero, CPNA=pna.CPNA, CPNATAB=pna.CPNATAB,
         ClassifierHead=dec.ClassifierHead, LinkPredHead=dec.LinkPredHead,
         NodeClassificationHead=dec.NodeClassificationHead,
         TABGNN=tabgnn.TABGNN, TABGNNFused=fused.TABGNNFused,
         TABGNNInterleaved=inter.TABGNNInterleaved,
     )
     return ns
+
+
+def load_loss_metric():
+    """The reference's own SSLoss / SSMetric (src/utils/loss.py, src/utils/metric.py: plain torch / numpy files, loaded by
+    path so that src/utils/__init__.py is never executed)."""
+    loss = _load("refsrc_utils_loss", "src/utils/loss.py")
+    metric = _load("refsrc_utils_metric", "src/utils/metric.py")
+    return loss.SSLoss, metric.SSMetric

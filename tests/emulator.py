@@ -282,7 +282,39 @@ def relu_dropout_emul(x_or_y, g, p, seed):
     return torch.where(x_or_y > 0, g * m, torch.zeros_like(g)).contiguous()
 
 
+def pair_gather_act(Rs, Rd, T, src, dst, E, W, relu):
+    out = torch.zeros((E, W), dtype=torch.float32) if T is None else T.clone()
+    if Rs is not None:
+        out = out + Rs[src]
+    if Rd is not None:
+        out = out + Rd[dst]
+    return (torch.relu(out) if relu else out).contiguous()
+
+
+def rank_positive(pos, neg, B, K):
+    return (1 + (neg.view(B, K) >= pos.view(B, 1)).sum(1)).to(torch.int32)
+
+
+def segment_mean_blend_fwd(x, emb, ptr, perm):
+    cnt = (ptr[1:] - ptr[:-1])
+    node = torch.repeat_interleave(torch.arange(x.shape[0]), cnt)
+    s = torch.zeros_like(x).index_add_(0, node, emb[perm])
+    has = (cnt > 0).unsqueeze(1)
+    return torch.where(has, 0.5 * (x + s / cnt.clamp(min=1).unsqueeze(1).float()), x).contiguous()
+
+
+def segment_mean_blend_bwd(g, ptr, index, R, need_x, need_emb):
+    cnt = (ptr[1:] - ptr[:-1])
+    gx = torch.where((cnt > 0).unsqueeze(1), 0.5 * g, g).contiguous() if need_x else None
+    gemb = (g[index] * (0.5 / cnt[index].float()).unsqueeze(1)).contiguous() if need_emb else None
+    return gx, gemb
+
+
 _PATCHES = [
+    (BF, "_pair_gather_act", pair_gather_act),
+    (BF, "_rank_positive", rank_positive),
+    (BF, "_segment_mean_blend_fwd", segment_mean_blend_fwd),
+    (BF, "_segment_mean_blend_bwd", segment_mean_blend_bwd),
     (BF, "_relu_dropout", relu_dropout_emul),
     (BF, "_bn_stats", bn_stats),
     (BF, "_bn_relu_res_fwd", bn_relu_res_fwd),

@@ -34,6 +34,18 @@ def build_module(meta, rec):
         deg = torch.bincount(torch.bincount(ei[1], minlength=n))
         m = b200mp.PNAS(num_features=H, num_gnn_layers=Lyr, n_hidden=H, edge_updates=meta["edge_updates"],
                         edge_dim=K * H, deg=deg, reverse_mp=meta["reverse_mp"])
+    elif kind in ("CPNA", "CPNATAB"):
+        ei = rec["in"]["edge_index"]
+        n = rec["in"]["x"].shape[0]
+        deg = torch.bincount(torch.bincount(ei[1], minlength=n))
+        cls = b200mp.CPNA if kind == "CPNA" else b200mp.CPNATAB
+        m = cls(num_features=H, num_gnn_layers=Lyr, n_hidden=H, edge_updates=meta["edge_updates"], edge_dim=K * H, deg=deg,
+                reverse_mp=meta["reverse_mp"])
+        for mod in m.modules():                      # as the fixture generator: the row attention's default dropout off
+            if isinstance(mod, torch.nn.Dropout):
+                mod.p = 0.0
+            if isinstance(mod, torch.nn.MultiheadAttention):
+                mod.dropout = 0.0
     elif kind in ("TABGNN", "TABGNNInterleaved", "TABGNNFused"):
         ei = rec["in"]["edge_index"]
         n = rec["in"]["x"].shape[0]
@@ -57,6 +69,11 @@ def oracle_fn(meta):
         return lambda p, i: OM.gine(p, i["x"], i["edge_index"], i["edge_attr"], meta["L"], meta["edge_updates"], meta["reverse_mp"])
     if meta["model"] == "PNAS":
         return lambda p, i: OM.pnas(p, i["x"], i["edge_index"], i["edge_attr"], meta["L"], meta["edge_updates"], meta["reverse_mp"])
+    if meta["model"] == "CPNA":
+        return lambda p, i: OM.cpna(p, i["x"], i["edge_index"], i["edge_attr"], meta["L"], meta["edge_updates"], meta["reverse_mp"])
+    if meta["model"] == "CPNATAB":
+        return lambda p, i: OM.cpnatab(p, i["x"], i["edge_index"], i["edge_attr"], meta["L"], meta["edge_updates"], meta["reverse_mp"],
+                                       nhead=meta["nhead"])
     if meta["model"] == "TABGNN":
         return lambda p, i: OM.tabgnn(p, i["x"], i["edge_index"], i["edge_attr"], meta["L"], meta["nhead"])
     if meta["model"] == "TABGNNInterleaved":

@@ -7,7 +7,7 @@ import torch
 from tests.emulator import emulated_kernels
 from tests.parity import check_fixture
 
-NAMES = ["gine_eu", "gine_eu_rev", "gine_noeu", "pnas_eu", "pnas_eu_rev", "pnas_h64", "tabgnn", "interleaved", "fused_mcm", "fused_lp"]
+NAMES = ["gine_eu", "gine_eu_rev", "gine_noeu", "pnas_eu", "pnas_eu_rev", "pnas_h64", "tabgnn", "interleaved", "fused_mcm", "fused_lp", "cpna", "cpnatab"]
 
 
 @pytest.fixture(autouse=True)

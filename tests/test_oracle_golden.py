@@ -1,10 +1,12 @@
 """Pins oracle/models.py (the functional restatement) to the fixtures produced by the
 reference's own model files (oracle/gen_golden.py).  CPU only."""
+import os
+
 import pytest
 import torch
 
 from oracle import models as OM
-from tests.util import load_golden, rel_err
+from tests.util import GOLDEN, load_golden, rel_err
 
 TOL = 2e-6   # same arithmetic, same library kernels: only reassociation noise is expected
 
@@ -88,6 +90,30 @@ def test_interleaved():
 def test_fused(name):
     _run(name, lambda p, i, m: OM.tabgnn_fused(p, i["x"], i["edge_index"], i["edge_attr"], i["target_edge_index"],
                                                 i["target_edge_attr"], m["L"], m["node_dim"], lp=m["lp"], nhead=m["nhead"]))
+
+
+@pytest.mark.parametrize("name", ["cpna", "cpnatab"])
+def test_column_stacks(name):
+    fn = OM.cpna if name == "cpna" else OM.cpnatab
+    _run(name, lambda p, i, m: fn(p, i["x"], i["edge_index"], i["edge_attr"], m["L"], m["edge_updates"], m["reverse_mp"]))
+
+
+def test_losses_and_ranking_metric_pinned_to_reference_vectors():
+    """tests/golden/ss_loss_metric.npz holds outputs of the reference's OWN loss.py / metric.py (oracle/gen_golden_r2.py)"""
+    import numpy as np
+    z = np.load(os.path.join(GOLDEN, "ss_loss_metric.npz"))
+    t = lambda k: torch.from_numpy(z[k])
+    nn_, K = int(z["num_numerical"]), int(z["num_neg"])
+    assert abs(float(OM.lp_loss(t("pos"), t("neg"))) - float(z["lp_loss"])) < 1e-6
+    cat_out = [t(f"cat_out_{c}") for c in range(3)]
+    total, (cl, tc, acc), (nl, tn) = OM.mcm_loss(cat_out, t("num_out"), t("y"), nn_)
+    assert (tc, tn, acc) == (int(z["mcm_t_c"]), int(z["mcm_t_n"]), int(z["mcm_acc"]))
+    for got, key in ((total, "mcm_total"), (cl, "mcm_cat_loss"), (nl, "mcm_num_loss")):
+        assert abs(float(got) - float(z[key])) < 1e-5 * max(1.0, abs(float(z[key])))
+    mrr, hits, _ = OM.mrr(t("pos"), t("neg"), [1, 2, 5, 10], K)
+    # the reference's numpy argsort is unstable on the tied scores of sample 0: every other rank is pinned exactly
+    B = t("pos").shape[0]
+    assert abs(mrr - float(z["mrr"])) <= 1.0 / B and np.allclose([hits[f"hits@{k}"] for k in (1, 2, 5, 10)], z["hits"], atol=1.0 / B)
 
 
 def test_heads():
