@@ -310,7 +310,30 @@ def segment_mean_blend_bwd(g, ptr, index, R, need_x, need_emb):
     return gx, gemb
 
 
+def node_linear64(xs, Wcat, bias, ysplit):
+    y = torch.cat(list(xs), dim=1) @ Wcat.t()
+    if bias is not None:
+        y = y + bias
+    return [c.contiguous() for c in y.split(64, dim=1)] if ysplit else y.contiguous()
+
+
+def node_pair_wgrad(g0, g1, x):
+    return g0.t() @ x, g1.t() @ x
+
+
+def node_linear(x, W, b):
+    return torch.nn.functional.linear(x, W, b)
+
+
+def node_wgrad(x, y):
+    return x.t() @ y
+
+
 _PATCHES = [
+    (BF, "_node_linear64", node_linear64),
+    (BF, "_node_pair_wgrad", node_pair_wgrad),
+    (BF, "_node_linear", node_linear),
+    (BF, "_node_wgrad", node_wgrad),
     (BF, "_pair_gather_act", pair_gather_act),
     (BF, "_rank_positive", rank_positive),
     (BF, "_segment_mean_blend_fwd", segment_mean_blend_fwd),

@@ -42,7 +42,7 @@ def make_encoder(C, stats, names, seed=1):
 def oracle_blocks(enc, tf, dtype=torch.float64):
     """the encoder's parameters as oracle/stype_encoders.py blocks (leaf tensors of ``dtype`` requiring grad)"""
     e = enc.encoder_dict
-    leaf = lambda t: t.detach().cpu().to(dtype).requires_grad_(True)
+    leaf = lambda t: t.detach().cpu().to(dtype).clone().requires_grad_(True)
     P = {"num_w": leaf(e["numerical"].weight), "num_b": leaf(e["numerical"].bias),
          "ts_w": leaf(e["timestamp"].weight), "ts_b": leaf(e["timestamp"].bias),
          "tabs": [leaf(m.weight) for m in e["categorical"].embs]}

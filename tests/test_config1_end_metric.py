@@ -1,0 +1,116 @@
+"""BASELINE.json config 1 end to end: GINe edge classification on the reference's bundled
+data/Over-Sampled_Tiny_Trans-c.csv (fixture tests/golden/config1_tiny.npz, made by oracle/gen_config1_fixture.py: 5 198
+transactions, 8 989 accounts, K = 5 columns), trained full-graph for K Adam steps from IDENTICAL initial parameters
+
+  * on the drop-ins (column encoders -> GINe, 2 layers, hidden 64, edge updates -> ClassifierHead; CUDA kernels), and
+  * on the CPU oracle (oracle/stype_encoders.py -> oracle/models.gine -> oracle/models.classifier_head),
+
+with the loop shape of main.py:33-102 (weighted cross entropy main.py:335, Adam main.py:336, lr / loss weights of main.py:174,182,
+F1 of the positive class as main.py:93-95).  Tolerances (stated here, north_star "final F1"): every step's loss within 2e-3
+relative of the oracle's, final F1 within 0.02 absolute.
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import b200mp
+from b200mp.nn import (EmbeddingEncoder, LinearEncoder, StatType, StypeWiseFeatureEncoder, TensorFrame, TimestampEncoder, stype)
+from oracle import models as OM
+from oracle import stype_encoders as OS
+from tests.enc_util import oracle_blocks
+from tests.util import GOLDEN
+
+H, LAYERS, LR, LOSS_W = 64, 2, 0.0006116418195373612, (1.0, 9.23)
+
+
+def _load():
+    z = np.load(f"{GOLDEN}/config1_tiny.npz")
+    t = lambda k: torch.from_numpy(z[k])
+    names = {stype.numerical: ["Amount Paid"], stype.categorical: ["Receiving Currency", "Payment Currency", "Payment Format"],
+             stype.timestamp: ["Timestamp"]}
+    amount = t("amount")
+    stats = {"Amount Paid": {StatType.MEAN: float(amount.mean()), StatType.STD: float(amount.std())},
+             "Timestamp": {StatType.YEAR_RANGE: [int(t("ts7")[..., 0].min()), int(t("ts7")[..., 0].max())]}}
+    for n, c in zip(names[stype.categorical], z["ncat"]):
+        stats[n] = {StatType.COUNT: (list(range(int(c))), [1] * int(c))}
+    tf = TensorFrame({stype.numerical: amount, stype.categorical: t("cat"), stype.timestamp: t("ts7")}, names, y=t("y"))
+    return tf, stats, names, t("edge_index"), int(z["num_nodes"])
+
+
+def f1_binary(pred, y):
+    tp = float(((pred == 1) & (y == 1)).sum())
+    fp = float(((pred == 1) & (y == 0)).sum())
+    fn = float(((pred == 0) & (y == 1)).sum())
+    return 2 * tp / max(2 * tp + fp + fn, 1.0)
+
+
+def train_both(device, steps):
+    tf, stats, names, ei, n = _load()
+    y = tf.y.long()
+    torch.manual_seed(20240718)
+    enc = StypeWiseFeatureEncoder(H, stats, names, {stype.categorical: EmbeddingEncoder(), stype.numerical: LinearEncoder(),
+                                                   stype.timestamp: TimestampEncoder()})
+    gnn = b200mp.GINe(num_features=1, num_gnn_layers=LAYERS, n_hidden=H, edge_updates=True, edge_dim=5 * H)
+    head = b200mp.ClassifierHead(n_classes=2, n_hidden=H, dropout=0.0)
+    x = torch.ones(n, 1)
+    w = torch.tensor(LOSS_W)
+
+    # ---- oracle (CPU fp32), parameters = copies of the initial values
+    blocks, P = oracle_blocks(enc, tf, dtype=torch.float32)
+    pg = {k: v.detach().clone() for k, v in gnn.state_dict().items()}
+    for k, v in pg.items():
+        v.requires_grad_(v.is_floating_point() and "running" not in k and not k.endswith("eps"))
+    ph = {k: v.detach().clone().requires_grad_(True) for k, v in head.state_dict().items()}
+    leaves = [P["num_w"], P["num_b"], P["ts_w"], P["ts_b"], *P["tabs"]] + [v for v in pg.values() if v.requires_grad] + list(ph.values())
+    opt_o = torch.optim.Adam(leaves, lr=LR)
+    loss_o, f1_o = [], 0.0
+    for _ in range(steps):
+        opt_o.zero_grad()
+        ea = OS.stype_wise_encode(blocks)
+        xo, eo = OM.gine(pg, x, ei, ea, LAYERS, True, False, True)
+        out = OM.classifier_head(ph, xo, ei, eo)
+        loss = F.cross_entropy(out, y, weight=w)
+        loss.backward()
+        opt_o.step()
+        loss_o.append(float(loss))
+        f1_o = f1_binary(out.argmax(1), y)
+
+    # ---- drop-ins on `device`
+    enc, gnn, head = enc.to(device).train(), gnn.to(device).train(), head.to(device).train()
+    tfd, eid, xd, yd, wd = tf.to(device), ei.to(device), x.to(device), y.to(device), w.to(device)
+    opt = torch.optim.Adam([*enc.parameters(), *gnn.parameters(), *head.parameters()], lr=LR)
+    loss_k, f1_k = [], 0.0
+    for _ in range(steps):
+        opt.zero_grad()
+        ea, _ = enc(tfd)
+        xo, eo = gnn(xd, eid, ea)
+        out = head(xo, eid, eo)
+        loss = F.cross_entropy(out, yd, weight=wd)
+        loss.backward()
+        opt.step()
+        loss_k.append(float(loss))
+        f1_k = f1_binary(out.argmax(1), yd)
+    return loss_o, f1_o, loss_k, f1_k
+
+
+def _compare(device, steps):
+    lo, fo, lk, fk = train_both(device, steps)
+    worst = max(abs(a - b) / abs(a) for a, b in zip(lo, lk))
+    print(f"config 1 ({device}, {steps} Adam steps): loss {lo[0]:.5f} -> {lo[-1]:.5f} (oracle) / {lk[-1]:.5f} (drop-ins), "
+          f"worst relative loss gap {worst:.2e}; F1 {fo:.4f} (oracle) / {fk:.4f} (drop-ins)")
+    assert lo[-1] < lo[0]                     # it trains
+    assert worst < 2e-3, (lo, lk)
+    assert abs(fo - fk) <= 0.02, (fo, fk)
+
+
+def test_config1_host_logic_emulated():
+    """the same loop with the kernels emulated in plain PyTorch: checks the composition, not the kernels (5 steps)"""
+    from tests.emulator import emulated_kernels
+    with emulated_kernels():
+        _compare("cpu", 5)
+
+
+@pytest.mark.gpu
+def test_config1_loss_curve_and_f1():
+    _compare("cuda", 50)
