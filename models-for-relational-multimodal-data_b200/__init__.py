@@ -6,7 +6,8 @@ valid Python identifier; ``b200mp/__init__.py`` at the repo root aliases it).
 Host code is Python/PyTorch (device memory, streams, autograd plumbing) over hand-written CUDA
 kernels behind the C ABI in ``include/b200mp.h``; there is no CPU / PyTorch fallback.
 """
-from . import _lib, functional, graph, parallel, sampling   # noqa: F401
+from . import _lib, batch, functional, graph, parallel, sampling   # noqa: F401
+from .batch import BatchBuilder, addEgoIDs   # noqa: F401
 from .feeder import DeviceFeeder   # noqa: F401
 from .sampling import NeighborSampler, generate_negative_samples   # noqa: F401
 from .graph import (EdgeStructure, SegmentIndex, degree, degree_histogram, edge_structure,   # noqa: F401
