@@ -35,6 +35,9 @@ bool use_tensor_cores() {
 
 int persistent_grid(const void* kernel, size_t smem, int64_t work_items, int threads) {
     int per_sm = 1;
+    // Without this the driver picks the SMALLEST shared-memory carve-out that holds one CTA (measured on B200, round 2:
+    // every 97 KB kernel reported -- and ran -- 1 CTA per SM although two fit in the 228 KB of an SM).
+    (void)cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
     cudaError_t oe = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem);
     static const bool dbg = [] { const char* v = getenv("B200MP_DEBUG_OCC"); return v && v[0] == '1'; }();
     if (dbg) {          // diagnostics: resident CTAs per SM of every persistent kernel (stderr)

@@ -607,7 +607,12 @@ def C_u64(x):
     return L.C.c_uint64(int(x) & (2 ** 64 - 1))
 
 
-_attn_calls = [0]
+def _next_seed(salt: int) -> int:
+    """Seed of one dropout mask, drawn from torch's default (CPU) generator: ``torch.manual_seed`` reproduces the masks,
+    ``get_rng_state`` / ``set_rng_state`` and activation checkpointing's RNG preservation (torch.utils.checkpoint,
+    row_chunked below) replay them, and no device synchronisation is involved.  ``salt`` separates the three mask users."""
+    return (int(torch.randint(0, 2 ** 62, (1,)).item()) * 2 + 1) ^ salt
+
 
 
 class _ColAttention(torch.autograd.Function):
@@ -620,8 +625,7 @@ class _ColAttention(torch.autograd.Function):
         L.require_cuda(q, k, v)
         seed = 0
         if p > 0.0:
-            _attn_calls[0] += 1
-            seed = torch.initial_seed() * 0x9E3779B97F4A7C15 + _attn_calls[0]
+            seed = _next_seed(0x9E3779B97F4A7C15)
         ctx.nhead, ctx.p, ctx.seed = int(nhead), float(p), seed
         ctx.save_for_backward(q, k, v)
         return _col_attention_fwd(q, k, v, ctx.nhead, ctx.p, seed)
@@ -788,8 +792,7 @@ class _AddDropoutLayerNorm(torch.autograd.Function):
         p = float(p) if sub is not None else 0.0
         seed = 0
         if p > 0.0:
-            _attn_calls[0] += 1
-            seed = torch.initial_seed() * 0x9E3779B97F4A7C15 + _attn_calls[0] * 0x632BE59BD9B4E019
+            seed = _next_seed(0x632BE59BD9B4E019)
         y, stats = _row_norm_fwd(x, sub, p, seed, gamma, beta, eps)
         ctx.p, ctx.seed, ctx.has_sub = p, seed, sub is not None
         ctx.save_for_backward(x, sub, stats, gamma)
@@ -922,8 +925,7 @@ class _ReluDropout(torch.autograd.Function):
         L.require_cuda(x)
         seed = 0
         if p > 0.0:
-            _attn_calls[0] += 1
-            seed = torch.initial_seed() * 0x9E3779B97F4A7C15 + _attn_calls[0] * 0xD1342543DE82EF95
+            seed = _next_seed(0xD1342543DE82EF95)
         y = _relu_dropout(x, None, p, seed)
         ctx.p, ctx.seed = float(p), seed
         ctx.save_for_backward(y)
@@ -1074,3 +1076,57 @@ def segment_mean_blend(x: torch.Tensor, emb: torch.Tensor, index: torch.Tensor) 
     """rows of ``x`` named in ``index`` become ``(x[n] + mean of the emb rows with index == n) / 2``, the others are copied:
     the ``unique`` / ``index_add_`` / ``bincount`` write-back of models/fused.py:256-268 as one pass without atomics."""
     return _SegmentMeanBlend.apply(x, emb, index)
+
+
+# ----------------------------------------------------------------------------- row-chunked recompute
+class _RowChunked(torch.autograd.Function):
+    """y = fn(x) for a ROW-LOCAL fn (row r of y depends on row r of x and on the parameters only): the column-attention
+    layer over [rows, S, C] tokens.  Forward runs chunk by chunk without recording the graph; backward re-runs each chunk
+    with the graph, so at most one chunk's intermediates are alive (SURVEY.md section 7 "hard parts": a [E, 6, 64] token tensor
+    is 49 GB at HI-Medium and the layer keeps ~10 tensors of that size for backward).  The CPU generator state of every
+    chunk is recorded and replayed, so dropout masks match between the two runs."""
+
+    @staticmethod
+    def forward(ctx, fn, chunk_rows, x, *params):
+        ctx.fn, ctx.chunk_rows = fn, int(chunk_rows)
+        ctx.save_for_backward(x, *params)
+        ctx.rng = []
+        outs = []
+        with torch.no_grad():
+            for r0 in range(0, x.shape[0], ctx.chunk_rows):
+                ctx.rng.append(torch.get_rng_state())
+                outs.append(fn(x[r0:r0 + ctx.chunk_rows]))
+        return torch.cat(outs, dim=0) if len(outs) != 1 else outs[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        x, *params = ctx.saved_tensors
+        gx = torch.empty_like(x) if ctx.needs_input_grad[2] else None
+        gp = [None] * len(params)
+        keep = torch.get_rng_state()
+        for i, r0 in enumerate(range(0, x.shape[0], ctx.chunk_rows)):
+            torch.set_rng_state(ctx.rng[i])
+            with torch.enable_grad():
+                xc = x[r0:r0 + ctx.chunk_rows].detach().requires_grad_(gx is not None)
+                yc = ctx.fn(xc)
+                need = [p for p in params if p.requires_grad]
+                grads = torch.autograd.grad(yc, ([xc] if gx is not None else []) + need, g[r0:r0 + ctx.chunk_rows], allow_unused=True)
+            if gx is not None:
+                gx[r0:r0 + ctx.chunk_rows] = grads[0]
+                grads = grads[1:]
+            it = iter(grads)
+            for j, p in enumerate(params):
+                if p.requires_grad:
+                    gj = next(it)
+                    if gj is not None:
+                        gp[j] = gj if gp[j] is None else gp[j] + gj
+        torch.set_rng_state(keep)
+        return (None, None, gx, *gp)
+
+
+def row_chunked(fn, x: torch.Tensor, params, chunk_rows: int) -> torch.Tensor:
+    """``fn(x)`` evaluated in chunks of ``chunk_rows`` rows with recompute in backward; ``params``: the tensors fn closes over
+    that need gradients (e.g. ``list(module.parameters())``).  One chunk (or fewer rows than a chunk): plain ``fn(x)``."""
+    if chunk_rows is None or chunk_rows <= 0 or x.shape[0] <= chunk_rows:
+        return fn(x)
+    return _RowChunked.apply(fn, chunk_rows, x, *params)

@@ -43,10 +43,18 @@ class _ColumnAttention(nn.Module):
                                                    activation=activation, batch_first=True)
         self.tab_norm = nn.LayerNorm(channels)
 
-    def attend(self, t: Tensor) -> Tensor:
+    #: rows per chunk of the recomputing evaluation (functional.row_chunked): above this many token rows the layer is run
+    #: chunk by chunk and re-run in backward, so that only one chunk's ~12 intermediate [rows, S, C] tensors are alive
+    chunk_rows = 1 << 20
+
+    def _attend_rows(self, t: Tensor) -> Tensor:
         # tab_conv holds the parameters (state_dict keys of nn.TransformerEncoderLayer); the math runs on
         # the b200mp kernels (functional.transformer_encoder_layer)
         return BF.add_dropout_layernorm(BF.transformer_encoder_layer(self.tab_conv, t), None, 0.0, self.tab_norm)
+
+    def attend(self, t: Tensor) -> Tensor:
+        params = [*self.tab_conv.parameters(), *self.tab_norm.parameters()]
+        return BF.row_chunked(self._attend_rows, t, params, self.chunk_rows if torch.is_grad_enabled() else 0)
 
     def _reset_attention(self):
         _xavier(self.tab_conv)
@@ -68,11 +76,25 @@ class _GraphStep(nn.Module):
         self.gnn_norm.reset_parameters()
         _xavier(self.gnn_edge_update)
 
-    def graph_step(self, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float):
-        c = self.gnn_conv.forward_sorted(x, st, e) if isinstance(self.gnn_conv, PNAConvHetero) \
-            else self.gnn_conv.forward_sorted(x, st.fwd, e)
-        x = BF.bn_relu_residual(self.gnn_norm.module, c, x)
-        return x, edge_update_sorted(self.gnn_edge_update, x, st, e, alpha, beta)
+    def graph_step(self, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float, part=None):
+        """part (parallel.Partition): x = the owned node rows, e = the owned edges in local CSC order; source-side node tables
+        are all-gathered, BatchNorm statistics synchronised (as _Backbone.message_passing_partitioned)"""
+        if part is None:
+            c = self.gnn_conv.forward_sorted(x, st, e) if isinstance(self.gnn_conv, PNAConvHetero) \
+                else self.gnn_conv.forward_sorted(x, st.fwd, e)
+            x = BF.bn_relu_residual(self.gnn_norm.module, c, x)
+            return x, edge_update_sorted(self.gnn_edge_update, x, st, e, alpha, beta)
+        from .. import parallel as PL
+        if isinstance(self.gnn_conv, PNAConvHetero):
+            raise NotImplementedError("reverse_mp is not supported on a partitioned graph")
+        gather = lambda t: PL.all_gather_rows(t, part)
+        c = self.gnn_conv.forward_sorted(x, part.st.fwd, e, gather=gather)
+        bn = self.gnn_norm.module
+        if bn.training:
+            x = BF.bn_relu_residual(bn, c, x, group=part.group, n_total=part.num_nodes)
+        else:
+            x = (x + F.relu(PL.sync_batch_norm(bn, c, part))) / 2
+        return x, edge_update_sorted(self.gnn_edge_update, x, part.st, e, alpha, beta, gather=gather)
 
 
 class _SharedParams:
@@ -107,8 +129,8 @@ class PNALayer(_GraphStep):
     def reset_parameters(self):
         self._reset_graph()
 
-    def forward_sorted(self, x, st, e):
-        return self.graph_step(x, st, e, 1.0, 0.5)                  # e + emlp(.)/2  (tabgnn.py:190)
+    def forward_sorted(self, x, st, e, part=None):
+        return self.graph_step(x, st, e, 1.0, 0.5, part)            # e + emlp(.)/2  (tabgnn.py:190)
 
     def forward(self, x_gnn, edge_index, edge_attr):
         st = edge_structure(edge_index, x_gnn.shape[0], reverse=self.reverse_mp)
@@ -159,6 +181,21 @@ class TABGNN(_SharedParams, nn.Module):
         for layer in self.gnn_backbone:
             x, e = layer.forward_sorted(x, st, e)
         return x, BF.scatter_rows(e, st.fwd.perm)
+
+    def forward_partitioned(self, x_local, edge_attr_local, part):
+        """One rank of a destination-range partition (parallel.Partition): x_local = token rows of the owned accounts,
+        edge_attr_local = token rows of the owned transactions in local CSC order (part.shard_edges).  The column attention is
+        row-local, so it shards with the rows; the graph half exchanges source-side node tables per layer.
+        Returns the owned rows of (x, edge_attr) in the same orders."""
+        x, e = self._with_cls(x_local), self._with_cls(edge_attr_local)
+        tx, te = x, e
+        for layer in self.tabular_backbone:
+            tx, te = layer(tx), layer(te)
+        x = self.node_emb(((x + tx) / 2).reshape(x.shape[0], -1))
+        e = self.edge_emb(((e + te) / 2).reshape(e.shape[0], -1))
+        for layer in self.gnn_backbone:
+            x, e = layer.forward_sorted(x, None, e, part)
+        return x, e
 
 
 # ----------------------------------------------------------------------------- shared top level of the two mixed models
@@ -216,10 +253,10 @@ class FTTransformerPNAInterleavedLayer(_MixedLayer):
         self._reset_attention()
         self._reset_graph()
 
-    def forward_sorted(self, x, st, tok):
+    def forward_sorted(self, x, st, tok, part=None):
         """tok [E,S,C] in CSC order; the CLS token is the edge feature of the PNA step."""
         tok = tok + self.attend(tok) / 2                              # inteleaved.py:219
-        x, cls = self.graph_step(x, st, tok[:, 0, :].contiguous(), 0.5, 0.5)   # (e + emlp(.))/2, :225
+        x, cls = self.graph_step(x, st, tok[:, 0, :].contiguous(), 0.5, 0.5, part)   # (e + emlp(.))/2, :225
         return x, torch.cat([cls.unsqueeze(1), tok[:, 1:, :]], dim=1)
 
     def forward(self, x_gnn, edge_index, edge_attr):
@@ -253,6 +290,16 @@ class TABGNNInterleaved(_TabGraphModel):
             x, tok = layer.forward_sorted(x, st, tok)
         cls = ((tok + tok0) / 2)[:, 0, :].contiguous()               # :161-162
         return x, BF.scatter_rows(cls, st.fwd.perm)
+
+    def forward_partitioned(self, x_local, edge_attr_local, part):
+        """as TABGNN.forward_partitioned: owned node rows / owned edge token rows in local CSC order in, the same out"""
+        x = self.node_emb(x_local.reshape(-1, self.node_dim))
+        tok0 = self._with_cls(edge_attr_local)
+        tok0 = (tok0 + self.attend(tok0)) / 2
+        tok = tok0
+        for layer in self.backbone:
+            x, tok = layer.forward_sorted(x, None, tok, part)
+        return x, ((tok + tok0) / 2)[:, 0, :].contiguous()
 
 
 # ----------------------------------------------------------------------------- TABGNNFused

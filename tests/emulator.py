@@ -160,11 +160,13 @@ def pna_coef(ptr, g_agg, agg, tie, need_gA):
 
 
 def col_attention_fwd(q, k, v, nhead, p, seed):
-    assert p == 0.0, "the emulator has no dropout stream"
     R, S, C = q.shape
     hd = C // nhead
     sp = lambda t: t.view(R, S, nhead, hd).transpose(1, 2)
-    a = torch.softmax(sp(q) @ sp(k).transpose(-1, -2) / hd ** 0.5, -1) @ sp(v)
+    prob = torch.softmax(sp(q) @ sp(k).transpose(-1, -2) / hd ** 0.5, -1)
+    if p > 0.0:          # a mask stream of the emulator's own (the kernel's hash is not restated): same seed, same mask
+        prob = prob * _drop_mask(prob.detach(), p, seed)
+    a = prob @ sp(v)
     return a.transpose(1, 2).reshape(R, S, C)
 
 

@@ -22,35 +22,69 @@ def _free_port():
     return p
 
 
+def _report(what, got, want, forward):
+    """max error, share of elements beyond 1e-5 and relative L2, all relative to the tensor's scale (SURVEY.md section 8(e):
+    "G-GPU == 1-GPU within fp32 reassociation (1e-5 rel)").  The max norm is bounded for forward values; gradients may have a
+    few elements on the other side of a relu / min / max / std-clamp kink, so their bound is on the relative L2 error and on
+    the share of elements beyond 1e-5."""
+    got, want = got.detach().double().cpu(), want.detach().double().cpu()
+    scale = max(float(want.abs().max()), 1e-30)
+    d = (got - want).abs() / scale
+    mx, frac = float(d.max()) if d.numel() else 0.0, float((d > 1e-5).double().mean()) if d.numel() else 0.0
+    l2 = float((got - want).norm() / max(float(want.norm()), 1e-30))
+    print(f"partition parity {what}: max {mx:.2e} frac>1e-5 {frac:.2e} relL2 {l2:.2e}")
+    assert l2 < 1e-5, (what, mx, frac, l2)
+    assert frac < 1e-3, (what, mx, frac, l2)
+    if forward:
+        assert mx < 2e-5, (what, mx)
+
+
 def run_case(kind, rank, world, device, emulate):
     import contextlib
 
     import b200mp
     from b200mp import parallel as PL
-    from tests.util import make_graph, rel_err
+    from tests.util import make_graph
     ctx = contextlib.nullcontext()
     if emulate:
         from tests.emulator import emulated_kernels
         ctx = emulated_kernels()
-    n, e, H = 240, 2600, 16 if emulate else 64
+    tab = kind in ("tabgnn", "interleaved")
+    n, e, H = (1500, 20000, 16) if emulate else (20000, 400000, 64)
+    if tab and emulate:
+        n, e = 600, 5000
+    K = 3
     with ctx:
         ei = make_graph(n, e, 5).to(device)
         deg = torch.bincount(torch.bincount(ei[1].cpu(), minlength=n))
         torch.manual_seed(3)
+        g = torch.Generator().manual_seed(11)
         if kind == "pna":
             model = b200mp.PNAS(num_features=H, num_gnn_layers=2, n_hidden=H, edge_updates=True, edge_dim=H, deg=deg)
-        else:
+        elif kind == "gine":
             model = b200mp.GINe(num_features=H, num_gnn_layers=2, n_hidden=H, edge_updates=True, edge_dim=H)
+        elif kind == "tabgnn":
+            model = b200mp.TABGNN(channels=H, num_layers=2, deg=deg, node_dim=H, nhidden=H, edge_dim=K * H, nhead=8, dropout=0.0)
+        else:
+            model = b200mp.TABGNNInterleaved(channels=H, num_layers=2, deg=deg, node_dim=H, nhidden=H, edge_dim=K * H, nhead=8, dropout=0.0)
         model = model.to(device).train()
+        if tab:
+            for m in model.modules():
+                if hasattr(m, "chunk_rows"):
+                    m.chunk_rows = 257                    # exercise the recomputing (row-chunked) attention path too
         sd0 = {k: v.clone() for k, v in model.state_dict().items()}
-        g = torch.Generator().manual_seed(11)
-        x = torch.randn(n, H, generator=g).to(device)
-        ea = torch.randn(e, H, generator=g).to(device)
+        if kind == "tabgnn":
+            x = torch.randn(n, 1, H, generator=g).to(device)
+        else:
+            x = torch.randn(n, H, generator=g).to(device)
+        ea = (torch.randn(e, K, H, generator=g) if tab else torch.randn(e, H, generator=g)).to(device)
         wx, we = torch.randn(n, H, generator=g).to(device), torch.randn(e, H, generator=g).to(device)
+        single = (lambda a, b: model(a, ei, b)) if tab else (lambda a, b: model.message_passing(a, ei, b))
+        parted = (lambda a, b, p: model.forward_partitioned(a, b, p)) if tab else (lambda a, b, p: model.message_passing_partitioned(a, b, p))
 
         # single-process truth
         x1, e1 = x.clone().requires_grad_(True), ea.clone().requires_grad_(True)
-        ox, oe = model.message_passing(x1, ei, e1)
+        ox, oe = single(x1, e1)
         ((ox * wx).sum() + (oe * we).sum()).backward()
         ref_g = {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}
         ref_sd = {k: v.clone() for k, v in model.state_dict().items()}
@@ -62,21 +96,20 @@ def run_case(kind, rank, world, device, emulate):
         assert int(part.bounds[-1]) == n and part.st.num_edges > 0
         xl = part.shard_nodes(x).requires_grad_(True)
         el = part.shard_edges(ea).requires_grad_(True)
-        px, pe = model.message_passing_partitioned(xl, el, part)
+        px, pe = parted(xl, el, part)
         ((px * part.shard_nodes(wx)).sum() + (pe * part.shard_edges(we)).sum()).backward()
         PL.all_reduce_gradients(model, part)
 
-        assert rel_err(px, ox[part.lo:part.hi]) < 2e-5, ("x", rel_err(px, ox[part.lo:part.hi]))
-        assert rel_err(pe, oe[part.edge_ids]) < 2e-5
-        assert rel_err(xl.grad, x1.grad[part.lo:part.hi]) < 5e-4
-        assert rel_err(el.grad, e1.grad[part.edge_ids]) < 5e-4
-        gmax = max(float(v.abs().max()) for v in ref_g.values())
-        for k, p in model.named_parameters():
-            if k in ref_g:
-                assert rel_err(p.grad, ref_g[k], 1e-2 * gmax) < 5e-4, (k, rel_err(p.grad, ref_g[k], 1e-2 * gmax))
+        _report(f"{kind} x'", px, ox[part.lo:part.hi], True)
+        _report(f"{kind} e'", pe, oe[part.edge_ids], True)
+        _report(f"{kind} dL/dx", xl.grad, x1.grad[part.lo:part.hi], False)
+        _report(f"{kind} dL/de", el.grad, e1.grad[part.edge_ids], False)
+        keys = [k for k, p in model.named_parameters() if k in ref_g]
+        _report(f"{kind} dL/dW (all parameters, concatenated)", torch.cat([dict(model.named_parameters())[k].grad.reshape(-1) for k in keys]),
+                torch.cat([ref_g[k].reshape(-1) for k in keys]), False)
         for k, v in model.state_dict().items():
             if "running" in k:
-                assert rel_err(v, ref_sd[k]) < 1e-5, k
+                _report(f"{kind} {k}", v, ref_sd[k], True)
 
 
 def _worker(rank, world, port, kind):
@@ -90,6 +123,6 @@ def _worker(rank, world, port, kind):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("kind", ["pna", "gine"])
+@pytest.mark.parametrize("kind", ["pna", "gine", "tabgnn", "interleaved"])
 def test_partition_matches_single_process(kind):
     mp.spawn(_worker, args=(WORLD, _free_port(), kind), nprocs=WORLD, join=True)
