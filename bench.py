@@ -72,6 +72,8 @@ def algorithmic_bytes_per_edge(kind):
 KERNEL_BYTES = {
     "pna_message_fwd": 3 * 4 * H + 8,      # read e, gather B[src], write m (+ A[dst] cached) ; src,dst ids
     "gine_message_fwd": 3 * 4 * H + 4,
+    "pna_message_fwd_reduce": 3 * 4 * H + 12,   # the same pass with the segmented reduction fused in (m written, never re-read)
+    "gine_message_fwd_reduce": 3 * 4 * H + 8,
     "segment_reduce_pna": 1 * 4 * H,       # read m
     "segment_reduce_sum": 1 * 4 * H,
     "edge_update_fwd": 4 * 4 * H + 8,      # read e, gather P[src], write h, write e'

@@ -132,6 +132,20 @@ int b200mp_segment_reduce_fwd(int kind, int H, int64_t N, const int64_t* ptr, co
                               int64_t n_chunks, const int32_t* chunk_heavy, const int64_t* chunk_begin,
                               float* partial /* [n_chunks, 6H] */, void* stream);
 
+/* Fused message forward + reduction for H = 64 on the tensor-core path (csrc/msg_reduce_umma.cu): what
+ * b200mp_edge_linear_fwd modes 0 / 1 followed by b200mp_segment_reduce_fwd kinds 0 / 1 compute, in one pass over the
+ * edges -- the messages m are written once (the backward reads them) and never read back; no atomics.
+ *   kind 0 (PNA):  m_k = e[row(k)] W^T + b + T1[idx1[k]] + T2[seg[k]];  agg [N,256] = mean|min|max|std, tie [N,128]
+ *   kind 1 (GINE): m_k = relu(e[row(k)] W^T + b + T1[idx1[k]]);          agg [N,64] = sum (tie, T2 unused)
+ * seg[k] = aggregation node of sorted edge k (non-decreasing), ptr = the segment boundaries [N+1].
+ * part / meta: scratch of the sizes b200mp_message_reduce_workspace reports (records of the segments cut by tile
+ * boundaries, stitched by a second kernel in tile order). */
+int b200mp_message_reduce_workspace(int kind, int64_t E, size_t* part_floats, size_t* meta_ints);
+int b200mp_message_fwd_reduce(int kind, int H, int64_t E, int64_t N, const int64_t* ptr, const float* e,
+                              const int32_t* eid, const float* W, const float* b, const float* T1,
+                              const int32_t* idx1, const float* T2, const int32_t* seg, float* m, float* agg,
+                              float* tie, float* part, int32_t* meta, void* stream);
+
 /* ------------------------------------------------------------------ node-level PNA glue
  * Degree scalers of PyG DegreeScalerAggregation (constructed at pna.py:71-74)
  * commuted past post_nn's Linear:  out[N,F] = base + sum_s f_s(deg) Z[:, s*F:(s+1)*F],

@@ -33,6 +33,8 @@ _SIGS = {
     "b200mp_edge_linear_fwd": [_i, _i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p],
     "b200mp_segment_reduce_fwd": [_i, _i, _l, _p, _p, _p, _p, _l, _l, _l, _p, _p, _l, _p, _p, _p, _p],
     "b200mp_message_bwd": [_i, _i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p, _p],
+    "b200mp_message_reduce_workspace": [_i, _l, _p, _p],
+    "b200mp_message_fwd_reduce": [_i, _i, _l, _l, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "b200mp_pna_scale_fwd": [_i, _l, _p, _p, _p, _i, _p, _p, _p, _p, _p],
     "b200mp_pna_scale_bwd": [_i, _l, _p, _p, _i, _p, _p, _p, _p, _p],
     "b200mp_pna_coef": [_i, _l, _p, _p, _p, _p, _p, _p, _p],

@@ -11,7 +11,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200mp.so")
-SOURCES = ["graph.cu", "edge_fwd.cu", "seg_reduce.cu", "edge_bwd.cu", "umma_selftest.cu", "edge_fwd_umma.cu", "edge_bwd_umma.cu", "node_ops.cu", "node_gemm_umma.cu", "sampling.cu", "col_attention.cu", "col_encoder.cu", "row_norm.cu", "node_norm.cu", "readout.cu"]
+SOURCES = ["graph.cu", "edge_fwd.cu", "seg_reduce.cu", "edge_bwd.cu", "umma_selftest.cu", "edge_fwd_umma.cu", "edge_bwd_umma.cu", "node_ops.cu", "node_gemm_umma.cu", "sampling.cu", "col_attention.cu", "col_encoder.cu", "row_norm.cu", "node_norm.cu", "readout.cu", "msg_reduce_umma.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
 

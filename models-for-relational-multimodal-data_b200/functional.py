@@ -365,6 +365,36 @@ def _segment_reduce(kind, seg: SegmentIndex, m, H):
     return agg, tie
 
 
+def fused_reduce_available(H: int) -> bool:
+    """The fused message + segmented-reduction kernel (csrc/msg_reduce_umma.cu) covers H = 64 on the tensor-core path;
+    B200MP_FUSED_REDUCE=0 switches back to the two-kernel path (A/B runs)."""
+    import os
+    return H == 64 and row_maps_available() and os.environ.get("B200MP_FUSED_REDUCE", "1") != "0"
+
+
+def _message_fwd_reduce(kind, seg: SegmentIndex, e, eid, W, b, T1, T2):
+    """messages + their aggregation over the segments of ``seg``: kind 0 (PNA) m = e W^T + b + T1[nbr] + T2[seg] ->
+    (m, agg [N,4H] = mean|min|max|std, tie [N,2H]); kind 1 (GINE) m = relu(e W^T + b + T1[nbr]) -> (m, agg [N,H], None)."""
+    E, H = e.shape
+    if not fused_reduce_available(H):
+        m, _ = _edge_linear_fwd(kind, e, eid, W, b, T1, seg.nbr32, T2, seg.seg32 if T2 is not None else None)
+        agg, tie = _segment_reduce(kind, seg, m, H)
+        return m, agg, tie
+    N, dev = seg.num_nodes, e.device
+    m = torch.empty((E, H), dtype=torch.float32, device=dev)
+    agg = torch.empty((N, 4 * H if kind == 0 else H), dtype=torch.float32, device=dev)
+    tie = torch.empty((N, 2 * H), dtype=torch.float32, device=dev) if kind == 0 else None
+    nf, ni = L.C.c_size_t(0), L.C.c_size_t(0)
+    L.check(L.lib().b200mp_message_reduce_workspace(kind, E, L.C.byref(nf), L.C.byref(ni)), "b200mp_message_reduce_workspace")
+    part = torch.empty(max(nf.value, 1), dtype=torch.float32, device=dev)
+    meta = torch.empty(max(ni.value, 4), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev), _track("pna_message_fwd_reduce" if kind == 0 else "gine_message_fwd_reduce", 3):
+        L.check(L.lib().b200mp_message_fwd_reduce(kind, H, E, N, L.ptr(seg.ptr), L.ptr(e), L.ptr(eid), L.ptr(W), L.ptr(b), L.ptr(T1),
+                                                  L.ptr(seg.nbr32), L.ptr(T2), L.ptr(seg.seg32), L.ptr(m), L.ptr(agg), L.ptr(tie),
+                                                  L.ptr(part), L.ptr(meta), L.stream()), "b200mp_message_fwd_reduce")
+    return m, agg, tie
+
+
 class EdgeGradSink:
     """Lets the two consumers of one edge tensor (the conv's message and the edge update of the
     same layer) produce ONE gradient buffer: the edge update's backward, which autograd always
@@ -495,8 +525,7 @@ class _PNAAggregate(torch.autograd.Function):
         A, B, e, W, b = map(_f32c, (A, B, e, W, b))
         L.require_cuda(A, B, e, W, b)
         H = _H(e)
-        m, _ = _edge_linear_fwd(0, e, seg.eid32 if e_eid is None else e_eid, W, b, B, seg.nbr32, A, seg.seg32)
-        agg, tie = _segment_reduce(0, seg, m, H)
+        m, agg, tie = _message_fwd_reduce(0, seg, e, seg.eid32 if e_eid is None else e_eid, W, b, B, A)
         ctx.seg, ctx.nB, ctx.sink, ctx.e_eid = seg, B.shape[0], sink, e_eid
         ctx.save_for_backward(m, e, W, agg, tie)
         ctx.mark_non_differentiable(tie)
@@ -530,8 +559,7 @@ class _GINEAggregate(torch.autograd.Function):
         x, e, W, b = map(_f32c, (x, e, W, b))
         L.require_cuda(x, e, W, b)
         H = _H(e)
-        m, _ = _edge_linear_fwd(1, e, seg.eid32 if e_eid is None else e_eid, W, b, x, seg.nbr32, None, None)
-        agg, _ = _segment_reduce(1, seg, m, H)
+        m, agg, _ = _message_fwd_reduce(1, seg, e, seg.eid32 if e_eid is None else e_eid, W, b, x, None)
         ctx.seg, ctx.nx, ctx.sink, ctx.e_eid = seg, x.shape[0], sink, e_eid
         ctx.save_for_backward(m, e, W)
         return agg

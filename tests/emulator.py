@@ -332,6 +332,7 @@ def node_wgrad(x, y):
 
 
 _PATCHES = [
+    (BF, "fused_reduce_available", lambda H: False),          # the fused kernel's two halves are emulated separately
     (BF, "_node_linear64", node_linear64),
     (BF, "_node_pair_wgrad", node_pair_wgrad),
     (BF, "_node_linear", node_linear),

@@ -1,0 +1,71 @@
+"""-m gpu: the fused message-forward + segmented-reduction kernel (csrc/msg_reduce_umma.cu) against the two-kernel path it
+replaces (edge_fwd_umma.cu + seg_reduce.cu, themselves checked against the emulation / oracle elsewhere): messages bit for
+bit, min / max / tie counts bit for bit, mean / std / sums to fp32 re-association.  Graphs: hubs crossing thousands of tiles,
+empty segments, runs ending exactly on tile and quarter boundaries, E below one tile."""
+import os
+
+import pytest
+import torch
+
+from b200mp import functional as BF
+from b200mp import graph as G
+from tests.util import rel_err
+
+pytestmark = pytest.mark.gpu
+H = 64
+
+
+def _graph(kind, n, e, seed):
+    g = torch.Generator().manual_seed(seed)
+    src = torch.randint(0, n, (e,), generator=g)
+    if kind == "uniform":
+        dst = torch.randint(0, n, (e,), generator=g)
+    elif kind == "hubs":                       # heavy tail: a few destinations own most edges, many own none
+        dst = (torch.rand(e, generator=g) ** 6 * n).long().clamp_(max=n - 1)
+    elif kind == "blocks":                     # every segment exactly 32 rows: runs end on quarter and tile boundaries
+        dst = torch.arange(e) // 32
+    else:                                      # one segment
+        dst = torch.full((e,), n // 2)
+    return torch.stack([src, dst]).cuda()
+
+
+def _both(kind_id, seg, e, eid, W, b, T1, T2):
+    os.environ["B200MP_FUSED_REDUCE"] = "0"
+    ref = BF._message_fwd_reduce(kind_id, seg, e, eid, W, b, T1, T2)
+    os.environ["B200MP_FUSED_REDUCE"] = "1"
+    got = BF._message_fwd_reduce(kind_id, seg, e, eid, W, b, T1, T2)
+    return ref, got
+
+
+@pytest.mark.parametrize("graph,n,e", [("uniform", 5000, 60000), ("hubs", 3000, 400001), ("blocks", 4096, 131072), ("single", 10, 70000),
+                                       ("uniform", 50, 37), ("hubs", 200000, 3000000)])
+@pytest.mark.parametrize("kind_id", [0, 1])
+@pytest.mark.parametrize("rowmap", [False, True])
+def test_fused_equals_two_kernels(graph, n, e, kind_id, rowmap):
+    if rowmap and e > 500000:
+        pytest.skip("row-map variant covered at the smaller sizes")
+    ei = _graph(graph, n, e, n + e)
+    seg = G.edge_structure(ei, n).fwd
+    g = torch.Generator(device="cuda").manual_seed(1)
+    ea = torch.randn(e, H, device="cuda", generator=g)
+    W = torch.randn(H, H, device="cuda", generator=g) / 8
+    b = torch.randn(H, device="cuda", generator=g)
+    T1 = torch.randn(n, H, device="cuda", generator=g)
+    T2 = torch.randn(n, H, device="cuda", generator=g) if kind_id == 0 else None
+    if rowmap:
+        e_in, eid = ea, seg.perm32()                       # e in the caller's order, read through the CSC permutation
+    else:
+        e_in, eid = BF.gather_rows(ea, seg.perm), None
+    (m0, a0, t0), (m1, a1, t1) = _both(kind_id, seg, e_in, eid, W, b, T1, T2)
+    assert torch.equal(m0, m1)
+    if kind_id == 0:
+        assert torch.equal(a0[:, H:3 * H], a1[:, H:3 * H])                      # min | max
+        assert torch.equal(t0, t1)                                              # tie counts
+        assert rel_err(a1[:, :H], a0[:, :H]) < 2e-6 and rel_err(a1[:, 3 * H:], a0[:, 3 * H:]) < 2e-5
+        deg = seg.ptr[1:] - seg.ptr[:-1]
+        assert float(a1[deg == 0].abs().max() if bool((deg == 0).any()) else 0.0) == 0.0
+    else:
+        assert rel_err(a1, a0) < 2e-6
+    # run-to-run identical (no atomics)
+    again = BF._message_fwd_reduce(kind_id, seg, e_in, eid, W, b, T1, T2)
+    assert torch.equal(again[1], a1) and (kind_id == 1 or torch.equal(again[2], t1))
