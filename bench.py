@@ -35,6 +35,7 @@ WORKLOADS = {   # name: (nodes, edges, seed)  -- SURVEY.md section 8(d)
     "tiny": (8_989, 5_198 * 16, 20240718),
 }
 H, LAYERS = 64, 2
+K_COLS = 5                     # edge columns of the AML table (3 categorical + 1 numerical + 1 timestamp)
 CPU_SAMPLE_EDGES = 1_000_000
 
 
@@ -56,6 +57,8 @@ def make_model(kind, deg_hist, device):
     torch.manual_seed(1234)
     if kind == "pna":
         m = b200mp.PNAS(num_features=H, num_gnn_layers=LAYERS, n_hidden=H, edge_updates=True, edge_dim=H, deg=deg_hist)
+    elif kind == "tabgnn":      # BASELINE.json config 5: PNA + FT-Transformer (column attention over the K + 1 tokens of every row)
+        m = b200mp.TABGNN(channels=H, num_layers=LAYERS, deg=deg_hist, node_dim=H, nhidden=H, edge_dim=K_COLS * H, nhead=8, dropout=0.0)
     else:
         m = b200mp.GINe(num_features=H, num_gnn_layers=LAYERS, n_hidden=H, edge_updates=True, edge_dim=H)
     return m.to(device).train()
@@ -64,7 +67,14 @@ def make_model(kind, deg_hist, device):
 def algorithmic_bytes_per_edge(kind):
     """compulsory [E,H]-row touches per layer fwd+bwd, fp32."""
     s = 4
-    return (22 if kind == "pna" else 19) * s * H + 64
+    return (22 if kind in ("pna", "tabgnn") else 19) * s * H + 64
+
+
+def tab_bytes_per_row(S):
+    """Column-attention layer (tab_conv + tab_norm) per token row, fwd + bwd, with the row-chunked recompute: forward reads the
+    tokens and writes the result (2 S C s); backward reads the incoming gradient and the saved input and writes the input
+    gradient (3 S C s)."""
+    return 5 * S * H * 4
 
 
 # algorithmic bytes per edge of each kernel (DESIGN.md "kernels"): [E,H] rows read/written or
@@ -157,26 +167,32 @@ def cpu_reference_steps(kind, steps, warmup, threads=None):
     cores = threads or os.cpu_count() or 1
     torch.set_num_threads(cores)
     n_full, e_full, seed = WORKLOADS["hi_medium"]
-    e = CPU_SAMPLE_EDGES
+    e = CPU_SAMPLE_EDGES // 4 if kind == "tabgnn" else CPU_SAMPLE_EDGES      # the attention rows cost ~4x the graph half on a CPU
     n = max(2, int(round(n_full * e / e_full)))
     ei = synth_graph(n, e, seed, "cpu")
     deg_hist = torch.bincount(torch.bincount(ei[1], minlength=n))
     torch.manual_seed(1234)
     if kind == "pna":
         mod = b200mp.PNAS(num_features=H, num_gnn_layers=LAYERS, n_hidden=H, edge_updates=True, edge_dim=H, deg=deg_hist)
+    elif kind == "tabgnn":
+        mod = b200mp.TABGNN(channels=H, num_layers=LAYERS, deg=deg_hist, node_dim=H, nhidden=H, edge_dim=K_COLS * H, nhead=8, dropout=0.0)
     else:
         mod = b200mp.GINe(num_features=H, num_gnn_layers=LAYERS, n_hidden=H, edge_updates=True, edge_dim=H)
     p = {k: v.clone() for k, v in mod.state_dict().items()}
     for k, v in p.items():
         v.requires_grad_(v.is_floating_point() and "running" not in k and "avg_deg" not in k and not k.endswith("eps"))
     g = torch.Generator().manual_seed(seed)
-    x = torch.randn(n, H, generator=g).requires_grad_(True)
-    ea = torch.randn(e, H, generator=g).requires_grad_(True)
+    tab = kind == "tabgnn"
+    x = torch.randn(n, *((1, H) if tab else (H,)), generator=g).requires_grad_(True)
+    ea = torch.randn(e, *((K_COLS, H) if tab else (H,)), generator=g).requires_grad_(True)
     gx, ge = torch.randn(n, H, generator=g), torch.randn(e, H, generator=g)
     times = []
     for it in range(warmup + steps):
         t0 = time.perf_counter()
-        ox, oe = OM.mp_stack(p, kind, x, ei, ea, LAYERS, True, False, True)
+        if tab:
+            ox, oe = OM.tabgnn(p, x, ei, ea, LAYERS, 8)
+        else:
+            ox, oe = OM.mp_stack(p, kind, x, ei, ea, LAYERS, True, False, True)
         torch.autograd.backward([ox, oe], [gx, ge])
         dt = time.perf_counter() - t0
         if it >= warmup:
@@ -207,10 +223,13 @@ def run_reference(args, rank, world):
 
 def workload_config(args, world):
     n, e, _ = WORKLOADS[args.workload]
-    return {"workload": f"{args.model.upper()} backbone ({LAYERS} layers, H={H}, edge updates) fwd+bwd on synthetic "
+    what = (f"TABGNN: {LAYERS} column-attention layers (FT-Transformer, nhead 8, {K_COLS} columns + CLS) over node and edge tokens, "
+            f"node/edge embeddings, {LAYERS} PNA layers (H={H}, edge updates)") if args.model == "tabgnn" else \
+        f"{args.model.upper()} backbone ({LAYERS} layers, H={H}, edge updates)"
+    return {"workload": f"{what} fwd+bwd on synthetic "
                         f"{args.workload} shape: {n} accounts, {e} transactions"
                         + ("" if world == 1 else f", ONE graph partitioned by destination range over {world} GPUs"),
-            "nodes": n, "edges": e, "layers": LAYERS, "hidden": H, "model": "PNAS" if args.model == "pna" else "GINe",
+            "nodes": n, "edges": e, "layers": LAYERS, "hidden": H, "model": {"pna": "PNAS", "gine": "GINe", "tabgnn": "TABGNN"}[args.model],
             "parallelism": "single GPU" if world == 1 else f"dst-range partition x{world}: per layer NCCL all-gather of source-side node tables, all-reduce of BatchNorm sums; backward reduce-scatter + weight-gradient all-reduce",
             "l2": "inputs exceed L2 (every [E,H] tensor >> 126 MB)"}
 
@@ -244,22 +263,27 @@ def run_b200(args, rank, world, local_rank):
     # shard), so the N = 1 / 2 / 4 / 8 runs compute the same function and their checksums are comparable
     g = torch.Generator(device=dev).manual_seed(seed)
 
-    def draw(rows, shard):
-        full = torch.randn(rows, H, generator=g, device=dev)
+    tab = args.model == "tabgnn"
+
+    def draw(rows, shard, inner=(H,)):
+        full = torch.randn(rows, *inner, generator=g, device=dev)
         if part is None:
             return full
         out = shard(full)
         del full
         return out
 
-    x = draw(n, lambda t: part.shard_nodes(t)).requires_grad_(True)
-    ea = draw(e, lambda t: part.shard_edges(t)).requires_grad_(True)
+    # tabgnn: the inputs are the column TOKENS (stand-in for the encoder output): x [N, 1, C], edge_attr [E, K, C]
+    x = draw(n, lambda t: part.shard_nodes(t), (1, H) if tab else (H,)).requires_grad_(True)
+    ea = draw(e, lambda t: part.shard_edges(t), (K_COLS, H) if tab else (H,)).requires_grad_(True)
     gx = draw(n, lambda t: part.shard_nodes(t))
     ge = draw(e, lambda t: part.shard_edges(t))
     torch.cuda.empty_cache()
 
     def step(keep=False):
-        if part is None:
+        if tab:
+            ox, oe = model(x, ei, ea) if part is None else model.forward_partitioned(x, ea, part)
+        elif part is None:
             ox, oe = model.message_passing(x, ei, ea)
         else:
             ox, oe = model.message_passing_partitioned(x, ea, part)
@@ -329,9 +353,13 @@ def run_b200(args, rank, world, local_rank):
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": KERNEL_BYTES[top] * e_loc}
     step_bytes = LAYERS * (e_loc * algorithmic_bytes_per_edge(args.model) + n_loc * 12 * 4 * H)
+    formula = "L*(E*(22*s*H+64) + N*12*s*H), SURVEY.md 8(d)"
+    if tab:      # + L column-attention layers over the (K+1)-token edge rows and the 2-token node rows, + edge_emb / node_emb
+        step_bytes += LAYERS * (e_loc * tab_bytes_per_row(K_COLS + 1) + n_loc * tab_bytes_per_row(2))
+        step_bytes += 2 * 4 * (e_loc * ((K_COLS + 1) * H + H) + n_loc * (2 * H + H))
+        formula += " + L*(E*5*(K+1)*C*s + N*5*2*C*s) [column attention, recomputing] + 2*s*(E*((K+1)*C+H) + N*(2*C+H)) [embeddings fwd+bwd]"
     step_roofline = {"algorithmic_bytes_per_step": step_bytes, "achieved_gbs": round(step_bytes / (ms_step * 1e-3) / 1e9, 1),
-                     "frac": round(step_bytes / (ms_step * 1e-3) / 1e9 / peak, 4),
-                     "formula": "L*(E*(22*s*H+64) + N*12*s*H), SURVEY.md 8(d)"}
+                     "frac": round(step_bytes / (ms_step * 1e-3) / 1e9 / peak, 4), "formula": formula}
 
     # end-to-end: pinned host buffers -> device -> CSC build -> fwd+bwd -> loss to host, every step
     e2e = None
@@ -343,7 +371,6 @@ def run_b200(args, rank, world, local_rank):
         hx, hea, hei = x.detach().cpu().pin_memory(), ea.detach().cpu().pin_memory(), ei.cpu().pin_memory()
         del ea, ge, part, gx
         torch.cuda.empty_cache()
-        h2d = hx.numel() * 4 + hea.numel() * 4 + hei.numel() * 8
         e2e_steps = max(1, min(args.steps, 3))
 
         from b200mp import DeviceFeeder
@@ -358,7 +385,10 @@ def run_b200(args, rank, world, local_rank):
             feeder.stage(host)
             BG.clear_cache()
             dx, dea = dx.detach().requires_grad_(True), dea.detach().requires_grad_(True)
-            if world == 1:
+            if tab:
+                ox, oe = model(dx, dei, dea) if world == 1 else model.forward_partitioned(dx, dea, e2e_part[0])
+                p2 = e2e_part[0]
+            elif world == 1:
                 ox, oe = model.message_passing(dx, dei, dea)
             else:
                 # the partition (which rank owns which destination range, local CSC slice) is a property of the graph:
@@ -426,14 +456,18 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="hi_medium", choices=sorted(WORKLOADS))
-    ap.add_argument("--model", default="pna", choices=["pna", "gine"])
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+                    help="default: hi_medium (BASELINE.json's metric config); tabgnn on ONE GPU: hi_small -- hi_medium's [E, 6, 64] "
+                         "token tensors (49 GB each) only fit partitioned over 8 GPUs, which is how config 5 is worded")
+    ap.add_argument("--model", default="pna", choices=["pna", "gine", "tabgnn"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer arm")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.workload is None:
+        args.workload = "hi_small" if (args.model == "tabgnn" and world < 8) else "hi_medium"
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
