@@ -76,25 +76,28 @@ class _GraphStep(nn.Module):
         self.gnn_norm.reset_parameters()
         _xavier(self.gnn_edge_update)
 
-    def graph_step(self, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float, part=None):
+    def graph_step(self, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float, part=None, e_eid=None, out_eid=None):
         """part (parallel.Partition): x = the owned node rows, e = the owned edges in local CSC order; source-side node tables
-        are all-gathered, BatchNorm statistics synchronised (as _Backbone.message_passing_partitioned)"""
+        are all-gathered, BatchNorm statistics synchronised (as _Backbone.message_passing_partitioned).  e_eid / out_eid: int32
+        row maps when e comes in / e' goes out in the caller's edge order instead of CSC order (H = 64 kernels).  Conv and
+        edge update read the same e: their gradients meet in one buffer (functional.EdgeGradSink)."""
+        sink = BF.EdgeGradSink() if (e.requires_grad and torch.is_grad_enabled()) else None
         if part is None:
-            c = self.gnn_conv.forward_sorted(x, st, e) if isinstance(self.gnn_conv, PNAConvHetero) \
-                else self.gnn_conv.forward_sorted(x, st.fwd, e)
+            c = self.gnn_conv.forward_sorted(x, st, e, sink=sink) if isinstance(self.gnn_conv, PNAConvHetero) \
+                else self.gnn_conv.forward_sorted(x, st.fwd, e, sink=sink, e_eid=e_eid)
             x = BF.bn_relu_residual(self.gnn_norm.module, c, x)
-            return x, edge_update_sorted(self.gnn_edge_update, x, st, e, alpha, beta)
+            return x, edge_update_sorted(self.gnn_edge_update, x, st, e, alpha, beta, sink=sink, e_eid=e_eid, out_eid=out_eid)
         from .. import parallel as PL
         if isinstance(self.gnn_conv, PNAConvHetero):
             raise NotImplementedError("reverse_mp is not supported on a partitioned graph")
         gather = lambda t: PL.all_gather_rows(t, part)
-        c = self.gnn_conv.forward_sorted(x, part.st.fwd, e, gather=gather)
+        c = self.gnn_conv.forward_sorted(x, part.st.fwd, e, gather=gather, sink=sink)
         bn = self.gnn_norm.module
         if bn.training:
             x = BF.bn_relu_residual(bn, c, x, group=part.group, n_total=part.num_nodes)
         else:
             x = (x + F.relu(PL.sync_batch_norm(bn, c, part))) / 2
-        return x, edge_update_sorted(self.gnn_edge_update, x, part.st, e, alpha, beta, gather=gather)
+        return x, edge_update_sorted(self.gnn_edge_update, x, part.st, e, alpha, beta, gather=gather, sink=sink)
 
 
 class _SharedParams:
@@ -129,8 +132,8 @@ class PNALayer(_GraphStep):
     def reset_parameters(self):
         self._reset_graph()
 
-    def forward_sorted(self, x, st, e, part=None):
-        return self.graph_step(x, st, e, 1.0, 0.5, part)            # e + emlp(.)/2  (tabgnn.py:190)
+    def forward_sorted(self, x, st, e, part=None, e_eid=None, out_eid=None):
+        return self.graph_step(x, st, e, 1.0, 0.5, part, e_eid, out_eid)            # e + emlp(.)/2  (tabgnn.py:190)
 
     def forward(self, x_gnn, edge_index, edge_attr):
         st = edge_structure(edge_index, x_gnn.shape[0], reverse=self.reverse_mp)
@@ -177,6 +180,12 @@ class TABGNN(_SharedParams, nn.Module):
         x = self.node_emb(((x + tx) / 2).reshape(x.shape[0], -1))
         e = self.edge_emb(((e + te) / 2).reshape(e.shape[0], -1))
         st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
+        if not self.reverse_mp and x.shape[1] == 64 and BF.row_maps_available():
+            # e stays in the caller's order at both ends: first layer reads / last layer writes through the CSC permutation
+            perm32, L = st.fwd.perm32(), len(self.gnn_backbone)
+            for i, layer in enumerate(self.gnn_backbone):
+                x, e = layer.forward_sorted(x, st, e, e_eid=perm32 if i == 0 else None, out_eid=perm32 if i == L - 1 else None)
+            return x, e
         e = BF.gather_rows(e, st.fwd.perm)
         for layer in self.gnn_backbone:
             x, e = layer.forward_sorted(x, st, e)
