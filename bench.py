@@ -234,6 +234,125 @@ def workload_config(args, world):
             "l2": "inputs exceed L2 (every [E,H] tensor >> 126 MB)"}
 
 
+def run_eth_lp(args, rank, world, local_rank):
+    """BASELINE.json config 4: link prediction with neighbour sampling on a synthetic ETH-phishing-shaped graph
+    (N = 2 973 489, E = 13 551 303, K = 5: 4 numerical + 1 timestamp), the loop of fused.py:98-125 (train_lp): per step B = 200
+    seed edges -> lp_inputs on the device (2-hop in-neighbour sample, fan-out [100, 100], relabel, x64 attribute replication, 64
+    negatives per positive) -> column encoders -> TABGNNFused(lp=True) -> LinkPredHead -> lp_loss -> backward.  Reports the
+    sampler (batch construction) and the model (encoders + fwd + bwd) separately, in edges/s of the sampled batch graphs.
+    N > 1: mini-batches are independent -> replicas (every rank runs its own batches; value = sum over ranks)."""
+    import torch.distributed as dist
+
+    import b200mp
+    from b200mp.batch import BatchBuilder
+    from b200mp.nn import LinearEncoder, StatType, StypeWiseFeatureEncoder, TensorFrame, TimestampEncoder, stype
+
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    n, e, seed = 2_973_489, 13_551_303, 20240720
+    B, NEG, FAN = 200, 64, (100, 100)
+    ei = synth_graph(n, e, seed, dev)
+    g = torch.Generator(device=dev).manual_seed(seed + 1)
+    num = torch.rand(e, 4, generator=g, device=dev)
+    ts7 = torch.stack([torch.randint(2015, 2020, (e,), generator=g, device=dev), torch.randint(0, 12, (e,), generator=g, device=dev),
+                       torch.randint(0, 28, (e,), generator=g, device=dev), torch.randint(0, 7, (e,), generator=g, device=dev),
+                       torch.randint(0, 24, (e,), generator=g, device=dev), torch.randint(0, 60, (e,), generator=g, device=dev),
+                       torch.randint(0, 60, (e,), generator=g, device=dev)], 1).unsqueeze(1)
+    names = {stype.numerical: ["value", "gas", "gas_price", "nonce"], stype.timestamp: ["timestamp"]}
+    stats = {nm: {StatType.MEAN: 0.5, StatType.STD: 0.2887} for nm in names[stype.numerical]}
+    stats["timestamp"] = {StatType.YEAR_RANGE: [2015, 2019]}
+    tf = TensorFrame({stype.numerical: num, stype.timestamp: ts7}, names)
+    bb = BatchBuilder(ei, n, tf, FAN)
+    deg_hist = torch.bincount(torch.bincount(ei[1], minlength=n)).cpu()
+    torch.manual_seed(1234)
+    enc = StypeWiseFeatureEncoder(H, stats, names, {stype.numerical: LinearEncoder(), stype.timestamp: TimestampEncoder()}).to(dev).train()
+    model = b200mp.TABGNNFused(channels=H, num_layers=LAYERS, encoder=enc, deg=deg_hist, node_dim=1, nhidden=H, edge_dim=K_COLS * H,
+                               nhead=8, dropout=0.0).to(dev).train()
+    head = b200mp.LinkPredHead(n_classes=1, n_hidden=H, dropout=0.0).to(dev).train()
+    params = [*enc.parameters(), *model.parameters(), *head.parameters()]
+    opt = torch.optim.Adam(params, lr=5e-4)
+    gs = torch.Generator(device=dev).manual_seed(seed + 7 + rank)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    stats_k = b200mp.functional.KernelStats(timing=False)
+
+    def step(timers=None):
+        ids = torch.randint(0, e, (B,), generator=gs, device=dev)
+        seeds = torch.stack([ei[0, ids], ei[1, ids], ids], 1)
+        t0, t1, t2 = ev(), ev(), ev()
+        t0.record()
+        node_feats, _, _, nei, nea, tei, tea = bb.lp_inputs(seeds, NEG, ego=False)
+        t1.record()
+        nea_t, _ = enc(nea)
+        tea_t, _ = enc(tea)
+        x_gnn, _, tgt = model(node_feats, nei, nea_t, tei, tea_t, True)
+        pos, neg = head(x_gnn, tei[:, :B], tgt[:B], tei[:, B:], tgt[B:])
+        loss = b200mp.SSLoss.lp_loss(pos, neg)
+        opt.zero_grad(set_to_none=True)
+        loss.backward()
+        opt.step()
+        t2.record()
+        if timers is not None:
+            timers.append((t0, t1, t2, int(nei.shape[1]) + int(tei.shape[1]), int(node_feats.shape[0])))
+        return loss
+
+    for _ in range(args.warmup):
+        step()
+    clocks = ClockSampler(local_rank)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks.start()
+    b200mp.functional.set_kernel_stats(stats_k)
+    timers = []
+    a, b = ev(), ev()
+    a.record()
+    for _ in range(args.steps):
+        loss = step(timers)
+    lval = float(loss.item())                   # D2H of the step result
+    b.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    b200mp.functional.set_kernel_stats(None)
+    clk = clocks.stop()
+    ms = a.elapsed_time(b)
+    ms_s = sum(t0.elapsed_time(t1) for t0, t1, _, _, _ in timers)
+    ms_m = sum(t1.elapsed_time(t2) for _, t1, t2, _, _ in timers)
+    edges = sum(t[3] for t in timers)
+    nodes = sum(t[4] for t in timers)
+    tot = torch.tensor([ms, ms_s, ms_m, float(edges), float(nodes)], device=dev, dtype=torch.float64)
+    if world > 1:
+        mx = tot[:3].clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tot[3:].clone()
+        dist.all_reduce(sm)
+        tot = torch.cat([mx, sm])
+    ms, ms_s, ms_m, edges, nodes = (float(v) for v in tot)
+    if rank != 0:
+        return
+    line = {
+        "metric": "message-passing edges/sec (fwd+bwd)", "value": edges / (ms_m * 1e-3), "unit": "edges/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"link prediction with neighbour sampling (fused.py train_lp loop) on a synthetic ETH-phishing-shaped graph: {n} "
+                               f"accounts, {e} transactions, K = {K_COLS} columns; B = {B} seed edges / step, fan-out {list(FAN)}, {NEG} negatives per "
+                               "positive; TABGNNFused(lp) + LinkPredHead, Adam", "nodes": n, "edges": e, "layers": LAYERS, "hidden": H,
+                   "model": "TABGNNFused + LinkPredHead", "parallelism": "single GPU" if world == 1 else f"{world} replicas (independent mini-batches)",
+                   "l2": "batch graphs are small (tens of thousands of edges): L2-resident by nature, as in the reference's loop"},
+        "clocks": clk,
+        "batch": {"edges_per_step": edges / args.steps / world, "nodes_per_step": nodes / args.steps / world},
+        "sampler": {"value": edges / (ms_s * 1e-3), "unit": "edges/s", "ms_per_step": ms_s / args.steps,
+                    "what": "BatchBuilder.lp_inputs: 2-hop CSC neighbour sample, seed drop, relabel, attribute row gathers, x64 replication, negative sampling"},
+        "model": {"value": edges / (ms_m * 1e-3), "unit": "edges/s", "ms_per_step": ms_m / args.steps,
+                  "what": "column encoders (neighbour + target rows), TABGNNFused fwd+bwd, LinkPredHead, lp_loss, Adam step"},
+        "e2e": {"value": edges / (ms * 1e-3), "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4,
+                "includes": "sampler + model + the loss read on the host; the transaction table lives on the device, nothing is copied per step"},
+        "gpu_launches": stats_k.launches, "loss": lval, "cpu_baseline": None,
+        "note": "extra line (BASELINE.json config 4); the headline line is the default workload",
+    }
+    print(json.dumps(line), flush=True)
+
+
 def run_b200(args, rank, world, local_rank):
     import torch.distributed as dist
 
@@ -456,7 +575,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS) + ["eth_lp"],
                     help="default: hi_medium (BASELINE.json's metric config); tabgnn on ONE GPU: hi_small -- hi_medium's [E, 6, 64] "
                          "token tensors (49 GB each) only fit partitioned over 8 GPUs, which is how config 5 is worded")
     ap.add_argument("--model", default="pna", choices=["pna", "gine", "tabgnn"])
@@ -469,6 +588,11 @@ def main():
     if args.workload is None:
         args.workload = "hi_small" if (args.model == "tabgnn" and world < 8) else "hi_medium"
     if args.impl == "reference":
+        if args.workload == "eth_lp":
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable": "the eth_lp extra line has no CPU arm: the oracle's sampler restatement covers "
+                                  "the take-all regime only (pyg-lib's sub-sampling RNG is not reproducible, SURVEY.md App. A.3)"}), flush=True)
+            return
         run_reference(args, rank, world)
         return
     if args.warmup < 3:
@@ -478,7 +602,10 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
-        run_b200(args, rank, world, local_rank)
+        if args.workload == "eth_lp":
+            run_eth_lp(args, rank, world, local_rank)
+        else:
+            run_b200(args, rank, world, local_rank)
     finally:
         if world > 1:
             import torch.distributed as dist
