@@ -6,6 +6,7 @@
 //                                             are fetched coalesced while the MMAs run
 //   mode 0: out1 = z     mode 1: out1 = relu(z)
 //   mode 2: out1 = h = relu(z);  out2[row] = alpha e + beta (h W2^T + b2)     U (tmem cols 64..127)
+#include <cstdlib>
 #include "umma_edge.cuh"
 
 namespace b200mp {
@@ -180,6 +181,164 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
 // backward.  10.9 ms vs 9.2 ms on hi_medium -- the forward has no weight-gradient MMAs to hide, and M = 64 MMAs and
 // half-filled tensor-memory loads double the per-edge cost of the phases it does have.)
 
+
+// ---- edge update, software-pipelined over two operand sets -----------------------------------------------------------
+// The kernel above runs one tile as a serial chain (split e -> MMA1 -> epilogue 1 -> MMA2 -> epilogue 2): ncu put its
+// loads in flight for ~1.5 us of the ~5.6 us a tile takes.  Here the NEXT tile's e rows are split into a second operand
+// set while this tile is in its first epilogue, and its MMA1 is issued right behind this tile's MMA2, so that at the top of
+// an iteration the first product is already in tensor memory: split / fence / barrier / MMA1 leave the critical path.
+// Shared memory: two e / h operand sets (4 x 32 KB), staging tile (32 KB), weights (64 KB) = 224 KB, one CTA per SM.
+// The residual rows e[row(k)] are re-read (L2) behind MMA2 instead of being held in registers for a whole iteration:
+// the register budget (512 threads x 128) has room for four row sets -- prefetch, residual, two gathered tables.
+__global__ void __launch_bounds__(512, 1) edge_update_fwd_pipe_kernel(EdgeFwdUArgs a) {
+    constexpr int NTH = 512;
+    constexpr int CW = HH / (NTH / TE);
+    constexpr int NP = RowRegs<NTH>::NP;
+    extern __shared__ __align__(128) float smem_raw[];
+    float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;
+    auto EBhi = [&](uint32_t set) { return smem + set * 2 * RT::FLOATS; };                 // operand set: hi tile, lo tile
+    auto EBlo = [&](uint32_t set) { return smem + set * 2 * RT::FLOATS + RT::FLOATS; };
+    float* ST = smem + 4 * RT::FLOATS;
+    float* W1_hi = ST + RT::FLOATS;
+    float* W1_lo = W1_hi + WT::FLOATS;
+    float* W2_hi = W1_lo + WT::FLOATS;
+    float* W2_lo = W2_hi + WT::FLOATS;
+    __shared__ TileSync sync;
+    __shared__ int sidx[2][TE];               // [src | dst][row] of the tile whose gathers are issued next
+
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int t = tid & (TE - 1), ch = tid >> 7;
+    const int j = tid & 15, g = tid >> 4;
+    if (warp == 0) tmem_alloc(&sync.tmem_base, 128);
+    if (tid == 0) { mbar_init(&sync.bar[0], 1); mbar_init(&sync.bar[1], 1); mbar_fence_init(); }
+    load_weight_tiles<false, NTH>(W1_hi, W1_lo, a.W1, tid);
+    load_weight_tiles<false, NTH>(W2_hi, W2_lo, a.W2, tid);
+    fence_async_smem();
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const uint32_t tm = sync.tmem_base;
+    const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t T_Z = tm + lane_off + ch * CW, T_U = tm + 64 + lane_off + ch * CW;
+    const float4 bias1 = ldg4(a.b1 + j * 4), bias2 = ldg4(a.b2 + j * 4);
+    const int64_t ntiles = (a.E + TE - 1) / TE;
+    const int32_t* idx_src = ch == 0 ? a.idx1 : ch == 1 ? a.idx2 : nullptr;
+
+    RowRegs<NTH> Rp, Rr, G, G2;               // prefetched e rows of a later tile | residual rows of this tile | gathered tables
+    int idx_pf = 0;
+    int64_t tile = blockIdx.x;
+    if (tile < ntiles) {                      // prologue: first tile's e -> set 0, its MMA1, its gathers; second tile's rows in flight
+        const int nrows = (int)min64(TE, a.E - tile * TE);
+        load_rows(Rp, a.e, a.eid, tile * TE, nrows, tid);
+        if (idx_src) idx_pf = __ldg(idx_src + tile * TE + min(t, nrows - 1));
+        store_rows_split(Rp, EBhi(0), EBlo(0), nrows, tid);
+        if (ch < 2) sidx[ch][t] = idx_pf;
+        fence_async_smem();
+        fence_before();
+        __syncthreads();
+        fence_after();
+        if (tid == 0) {
+            gemm3_data(tm, EBhi(0), EBlo(0), W1_hi, W1_lo, 0);
+            mma_commit(&sync.bar[0]);
+        }
+        gather_rows_issue(G, G2, a.T1, sidx[0], a.T2, sidx[1], tid);
+        const int64_t nt = tile + gridDim.x;
+        if (nt < ntiles) {
+            const int nn = (int)min64(TE, a.E - nt * TE);
+            load_rows(Rp, a.e, a.eid, nt * TE, nn, tid);
+            if (idx_src) idx_pf = __ldg(idx_src + nt * TE + min(t, nn - 1));
+        }
+    }
+
+    uint32_t it = 0;
+    for (; tile < ntiles; tile += gridDim.x, ++it) {
+        const int64_t row0 = tile * TE, nt = tile + gridDim.x;
+        const int nrows = (int)min64(TE, a.E - row0);
+        const bool has_next = nt < ntiles;
+        const int nrows_next = has_next ? (int)min64(TE, a.E - nt * TE) : 0;
+        const uint32_t s = it & 1, par = it & 1;
+        float* E_hi = EBhi(s);
+        float* E_lo = EBlo(s);
+
+        // ---- Z = e W1^T is (long) done: accumulator rows -> staging tile
+        mbar_wait(&sync.bar[0], par);
+        fence_after();
+        stage_from_tmem<NTH>(T_Z, ST, t, ch);
+        __syncthreads();
+
+        // ---- epilogue 1: h = relu(z + b1 + P[src] + Q[dst]) -> global and -> this set (MMA2 operand); next tile's e -> other set
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            const int r = g * NP + i;
+            float4 v = relu4(lds4(ST + stage_off(r, j)) + bias1 + (G.v[i] + G2.v[i]));
+            if (r < nrows) st4(a.out1 + (row0 + r) * HH + j * 4, v);
+            float4 hh, hl;
+            split4(r < nrows ? v : f4(0.f, 0.f, 0.f, 0.f), hh, hl);
+            const int o = RT::off(r, j);
+            st4(E_hi + o, hh);
+            st4(E_lo + o, hl);
+        }
+        if (has_next) {
+            store_rows_split(Rp, EBhi(s ^ 1), EBlo(s ^ 1), nrows_next, tid);
+            if (ch < 2) sidx[ch][t] = idx_pf;
+        }
+        fence_async_smem();
+        fence_before();
+        __syncthreads();
+        fence_after();
+        if (tid == 0) {
+            gemm3_data(tm + 64, E_hi, E_lo, W2_hi, W2_lo, 0);
+            mma_commit(&sync.bar[1]);
+            if (has_next) {                   // the next tile's first product queues right behind
+                gemm3_data(tm, EBhi(s ^ 1), EBlo(s ^ 1), W1_hi, W1_lo, 0);
+                mma_commit(&sync.bar[0]);
+            }
+        }
+        // ---- behind the MMAs: residual rows of this tile (L2), next tile's gathered rows, the tile after's e rows
+        load_rows(Rr, a.e, a.eid, row0, nrows, tid);
+        int64_t orow[NP];
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            const int r = g * NP + i;
+            orow[i] = (a.out_eid && r < nrows) ? (int64_t)__ldg(a.out_eid + row0 + r) : row0 + r;
+        }
+        if (has_next) {
+            gather_rows_issue(G, G2, a.T1, sidx[0], a.T2, sidx[1], tid);
+            const int64_t n2 = nt + gridDim.x;
+            if (n2 < ntiles) {
+                const int nn = (int)min64(TE, a.E - n2 * TE);
+                load_rows(Rp, a.e, a.eid, n2 * TE, nn, tid);
+                if (idx_src) idx_pf = __ldg(idx_src + n2 * TE + min(t, nn - 1));
+            }
+        }
+        mbar_wait(&sync.bar[1], par);
+        fence_after();
+        stage_from_tmem<NTH>(T_U, ST, t, ch);
+        __syncthreads();
+        // ---- epilogue 2: e' = alpha e + beta (h W2^T + b2)
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            const int r = g * NP + i;
+            const float4 v = a.alpha * Rr.v[i] + a.beta * (lds4(ST + stage_off(r, j)) + bias2);
+            if (r < nrows) st4(a.out2 + orow[i] * HH + j * 4, v);
+        }
+        __syncthreads();                      // the staging tile is free for the next iteration's Z rows
+    }
+    fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tm, 128);
+}
+
+static int launch_update_fwd_pipe(const EdgeFwdUArgs& a, cudaStream_t st) {
+    const size_t smem = 5 * RT::BYTES + 4 * WT::BYTES + 1024;
+    B200MP_CUDA(cudaFuncSetAttribute(edge_update_fwd_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t ntiles = (a.E + TE - 1) / TE;
+    int grid = persistent_grid((const void*)edge_update_fwd_pipe_kernel, smem, ntiles, 512);
+    edge_update_fwd_pipe_kernel<<<grid, 512, smem, st>>>(a);
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}
+
 template <int MODE>
 static int launch_fwd_umma_mode(const EdgeFwdUArgs& a, cudaStream_t st) {
     const size_t smem = (MODE == 2 ? 3 * RT::BYTES + 4 * WT::BYTES : 2 * RT::BYTES + 2 * WT::BYTES) + 1024;
@@ -201,7 +360,12 @@ int launch_edge_fwd_umma(int mode, int64_t E, const float* e, const int32_t* eid
     switch (mode) {
         case 0: return launch_fwd_umma_mode<0>(a, st);
         case 1: return launch_fwd_umma_mode<1>(a, st);
-        case 2: return launch_fwd_umma_mode<2>(a, st);
+        case 2: {
+            // B200MP_UPD_PIPE=0: the one-tile-at-a-time kernel (A/B runs)
+            const char* v = getenv("B200MP_UPD_PIPE");
+            const bool pipe = !(v && v[0] == '0');
+            return pipe ? launch_update_fwd_pipe(a, st) : launch_fwd_umma_mode<2>(a, st);
+        }
     }
     return B200MP_EINVAL;
 }

@@ -69,3 +69,24 @@ def test_fused_equals_two_kernels(graph, n, e, kind_id, rowmap):
     # run-to-run identical (no atomics)
     again = BF._message_fwd_reduce(kind_id, seg, e_in, eid, W, b, T1, T2)
     assert torch.equal(again[1], a1) and (kind_id == 1 or torch.equal(again[2], t1))
+
+
+@pytest.mark.parametrize("e,n", [(37, 50), (128, 10), (100_001, 9000), (2_000_000, 150_000)])
+@pytest.mark.parametrize("maps", [False, True])
+def test_update_forward_pipelined_equals_serial(e, n, maps):
+    """the software-pipelined edge-update forward (two operand sets, next tile's first product issued behind this tile's second)
+    computes exactly what the one-tile-at-a-time kernel computes: same operands, same MMA order per tile -> bit for bit"""
+    g = torch.Generator(device="cuda").manual_seed(e)
+    ei = torch.stack([torch.randint(0, n, (e,), device="cuda", generator=g), torch.randint(0, n, (e,), device="cuda", generator=g)])
+    st = G.edge_structure(ei, n)
+    ea = torch.randn(e, H, device="cuda", generator=g)
+    W1, W2 = torch.randn(H, H, device="cuda", generator=g) / 8, torch.randn(H, H, device="cuda", generator=g) / 8
+    b1, b2 = torch.randn(H, device="cuda", generator=g), torch.randn(H, device="cuda", generator=g)
+    P, Q = torch.randn(n, H, device="cuda", generator=g), torch.randn(n, H, device="cuda", generator=g)
+    eid = st.fwd.perm32() if maps else None
+    outs = []
+    for flag in ("0", "1"):
+        os.environ["B200MP_UPD_PIPE"] = flag
+        outs.append(BF._edge_linear_fwd(2, ea, eid, W1, b1, P, st.src32, Q, st.dst32, W2, b2, 0.5, 0.5, eid))
+    os.environ.pop("B200MP_UPD_PIPE")
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
