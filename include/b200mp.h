@@ -293,6 +293,19 @@ int b200mp_sample_hop_fill(const int64_t* colptr, const int64_t* frontier, int64
 int b200mp_first_occurrence(const int64_t* cand, int64_t K, uint8_t* visited, uint64_t* first, uint8_t* flags,
                             void* stream);
 
+/* Atomic-free variants of the two backward kernels (H = 64, tensor-core path): the per-edge gradient rows that
+ * b200mp_message_bwd / b200mp_edge_update_bwd scatter into node tables with vector REDs are written once as [E,H] in
+ * segment order instead (G_rows: d loss / d m_k; Gh_rows: the gradient at the edge update's hidden layer), and the caller sums
+ * them per node over the CSC / CSR orders with b200mp_segment_reduce_fwd kind 1.  Everything else (g_e, weight / bias partials,
+ * row maps, g_acc) as in the scattering entry points.  Results are bit-identical from run to run. */
+int b200mp_message_bwd_rows(int kind, int64_t E, const float* m, const float* e, const int32_t* eid,
+                            const float* node_in, const int32_t* seg, const float* W, float* g_e, int accumulate,
+                            float* G_rows, float* gW_part, float* gb_part, int n_part, const float* g_acc, void* stream);
+int b200mp_edge_update_bwd_rows(int64_t E, const float* g_out, const float* h, const float* e, const float* W1,
+                                const float* W2, float alpha, float beta, float* g_e, float* Gh_rows, float* gW1_part,
+                                float* gb1_part, float* gW2_part, float* gb2_part, int n_part, const int32_t* g_eid,
+                                const int32_t* e_eid, const int32_t* src, const int32_t* dst, void* stream);
+
 /* ------------------------------------------------------------------ read-out heads, ranking metric, pooled write-back
  * (kernels in csrc/readout.cu)
  *

@@ -242,11 +242,11 @@ static int launch_upd_bwd(const UpdBwdArgs& a, int n_part, cudaStream_t st) {
 
 int launch_msg_bwd_umma(int kind, int64_t E, const float* m, const float* e, const int32_t* eid, const float* node_in,
                         const int32_t* seg, const int32_t* nbr, const float* W, float* g_e, int accumulate, float* gT1,
-                        float* gW_part, float* gb_part, int n_part, const float* g_acc, cudaStream_t st);
+                        float* gW_part, float* gb_part, int n_part, const float* g_acc, cudaStream_t st, float* G_out = nullptr);
 int launch_upd_bwd_umma(int64_t E, const float* g_out, const float* h, const float* e, const int32_t* src, const int32_t* dst,
                         const float* W1, const float* W2, float alpha, float beta, float* g_e, float* gP, float* gQ,
                         float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part,
-                        const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st);
+                        const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st, float* gh_out = nullptr);
 
 }  // namespace b200mp
 
@@ -293,4 +293,30 @@ extern "C" int b200mp_edge_update_bwd(int H, int64_t E,
         case 128: return launch_upd_bwd<128>(a, n_part, st);
     }
     return B200MP_EINVAL;
+}
+
+// Atomic-free variants for H = 64 (tensor-core path): instead of scattering the per-edge gradient rows into the node tables with
+// vector REDs, the kernels write them once as [E,H] (segment order) and the caller sums them per node over the CSC / CSR orders
+// with the segmented-sum kernels -- bit-identical from run to run (SURVEY.md section 7 "atomic-free determinism both directions").
+extern "C" int b200mp_message_bwd_rows(int kind, int64_t E, const float* m, const float* e, const int32_t* eid,
+                                       const float* node_in, const int32_t* seg, const float* W, float* g_e, int accumulate,
+                                       float* G_rows, float* gW_part, float* gb_part, int n_part, const float* g_acc, void* stream) {
+    using namespace b200mp;
+    if (E < 0 || n_part <= 0 || !W || !gW_part || !gb_part || (kind != 0 && kind != 1)) return B200MP_EINVAL;
+    if (E > 0 && (!g_e || !m || !e || !node_in || !seg || !G_rows)) return B200MP_EINVAL;
+    if (!use_tensor_cores()) return B200MP_EINVAL;
+    return launch_msg_bwd_umma(kind, E, m, e, eid, node_in, seg, nullptr, W, g_e, accumulate, nullptr, gW_part, gb_part, n_part, g_acc,
+                               (cudaStream_t)stream, G_rows);
+}
+
+extern "C" int b200mp_edge_update_bwd_rows(int64_t E, const float* g_out, const float* h, const float* e, const float* W1,
+                                           const float* W2, float alpha, float beta, float* g_e, float* Gh_rows, float* gW1_part,
+                                           float* gb1_part, float* gW2_part, float* gb2_part, int n_part, const int32_t* g_eid,
+                                           const int32_t* e_eid, const int32_t* src, const int32_t* dst, void* stream) {
+    using namespace b200mp;
+    if (E < 0 || n_part <= 0 || !W1 || !W2 || !gW1_part || !gb1_part || !gW2_part || !gb2_part) return B200MP_EINVAL;
+    if (E > 0 && (!g_e || !g_out || !h || !e || !Gh_rows || !src || !dst)) return B200MP_EINVAL;
+    if (!use_tensor_cores()) return B200MP_EINVAL;
+    return launch_upd_bwd_umma(E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, nullptr, nullptr, gW1_part, gb1_part, gW2_part, gb2_part,
+                               n_part, g_eid, e_eid, (cudaStream_t)stream, Gh_rows);
 }

@@ -23,6 +23,7 @@ struct UpdBwdUArgs {
     float* g_e; float* gP; float* gQ;
     float* gW1_part; float* gb1_part; float* gW2_part; float* gb2_part;
     const int32_t* g_eid; const int32_t* e_eid;       // storage rows of g_out / e for segment position k (null = k)
+    float* gh_out;                                    // optional [E,H] (segment order): Gh rows, for the atomic-free node gradients
 };
 
 constexpr int NTB = 512;                  // threads per CTA of the backward kernels (one CTA per SM)
@@ -171,6 +172,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
                 accb1 = accb1 + Gh[i];
                 if (valid) accb2 = accb2 + Rg.v[i];
                 if (valid && a.gP) red_add4(a.gP + (int64_t)srow[i] * HH + j * 4, Gh[i]);
+                if (valid && a.gh_out) st4(a.gh_out + (row0 + r) * HH + j * 4, Gh[i]);
                 float4 gh, gl;
                 split4(Gh[i], gh, gl);
                 const int o = RG_T::off(r, j);
@@ -234,8 +236,8 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
 int launch_upd_bwd_umma(int64_t E, const float* g_out, const float* h, const float* e, const int32_t* src, const int32_t* dst,
                         const float* W1, const float* W2, float alpha, float beta, float* g_e, float* gP, float* gQ,
                         float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part,
-                        const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st) {
-    UpdBwdUArgs a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, g_eid, e_eid};
+                        const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st, float* gh_out) {
+    UpdBwdUArgs a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, g_eid, e_eid, gh_out};
     const size_t smem = 8 * dual::RG_T::BYTES + 4 * WT::BYTES + 1024;
     B200MP_CUDA(cudaFuncSetAttribute(edge_update_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     edge_update_bwd_umma_kernel<<<(n_part + 1) / 2, NTB, smem, st>>>(a, n_part);   // two 64-edge pipelines (partial rows) per CTA
@@ -254,6 +256,7 @@ struct MsgBwdUArgs {
     const float* W; float* g_e; int accumulate; float* gT1;
     float* gW_part; float* gb_part;
     const float* g_acc;                               // optional [E,H] in segment order added to g_e
+    float* G_out;                                     // optional [E,H] (segment order): per-edge gradient rows G
 };
 
 // PNA per-edge gradient from the saved message and the destination's coefficient rows
@@ -345,6 +348,7 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
                 }
                 if (r >= nrows) G = f4(0.f, 0.f, 0.f, 0.f);
                 if (r < nrows && a.gT1) red_add4(a.gT1 + (int64_t)nbr_pf[i] * HH + j * 4, G);
+                if (r < nrows && a.G_out) st4(a.G_out + (row0 + r) * HH + j * 4, G);
                 accb = accb + G;
                 Gv[i] = G;
             }
@@ -413,8 +417,8 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
 
 int launch_msg_bwd_umma(int kind, int64_t E, const float* m, const float* e, const int32_t* eid, const float* node_in,
                         const int32_t* seg, const int32_t* nbr, const float* W, float* g_e, int accumulate, float* gT1,
-                        float* gW_part, float* gb_part, int n_part, const float* g_acc, cudaStream_t st) {
-    MsgBwdUArgs a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, g_acc};
+                        float* gW_part, float* gb_part, int n_part, const float* g_acc, cudaStream_t st, float* G_out) {
+    MsgBwdUArgs a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, g_acc, G_out};
     const size_t smem = 4 * RT::BYTES + 2 * WT::BYTES + 1024;
     auto kern = kind == 0 ? message_bwd_umma_kernel<0> : message_bwd_umma_kernel<1>;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

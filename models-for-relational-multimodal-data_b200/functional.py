@@ -412,6 +412,42 @@ class EdgeGradSink:
         return b
 
 
+_DETERMINISTIC = [None]
+
+
+def set_deterministic(flag: Optional[bool]):
+    """Atomic-free backward for the H = 64 kernels: per-edge gradient rows are written once and summed per node over the CSC / CSR
+    orders instead of being scattered with vector REDs -- bit-identical gradients from run to run, at the price of ~4 extra [E,H]
+    passes per kernel.  ``None``: follow the environment variable B200MP_DETERMINISTIC (default off)."""
+    _DETERMINISTIC[0] = flag
+
+
+def deterministic_backward() -> bool:
+    if _DETERMINISTIC[0] is not None:
+        return bool(_DETERMINISTIC[0])
+    import os
+    return os.environ.get("B200MP_DETERMINISTIC", "0") == "1"
+
+
+def _sum_rows_by_neighbour(seg: SegmentIndex, rows, num_rows):
+    """rows [E,H] in ``seg`` order -> [num_rows, H]: sum of the rows of every neighbour id, in a fixed order (no atomics)"""
+    byn = seg.by_neighbour(num_rows)
+    return _segment_sum_rows(byn, _permute(rows, byn.perm, False))
+
+
+def _message_bwd_rows(kind, seg, m, e, node_in, W, g_e, accumulate, g_acc, eid, npart):
+    E, H = m.shape
+    dev = m.device
+    G = torch.empty((E, H), dtype=torch.float32, device=dev)
+    gW = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
+    gb = torch.empty((npart, H), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev), _track("pna_message_bwd" if kind == 0 else "gine_message_bwd"):
+        L.check(L.lib().b200mp_message_bwd_rows(kind, E, L.ptr(m), L.ptr(e), L.ptr(eid), L.ptr(node_in), L.ptr(seg.seg32), L.ptr(W),
+                                                L.ptr(g_e), accumulate, L.ptr(G), L.ptr(gW), L.ptr(gb), npart, L.ptr(g_acc), L.stream()),
+                "b200mp_message_bwd_rows")
+    return G, gW, gb
+
+
 def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N, g_e=None, eid=None):
     """g_e: optional [E,H] gradient (segment order) the result is added to.  eid: storage row of e
     (and of the returned gradient) for segment position k (default seg.eid32)."""
@@ -425,8 +461,11 @@ def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N, g_e=None
         accumulate = 1
     if g_e is None:
         g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
-    gT1 = torch.zeros((N, H), dtype=torch.float32, device=dev) if need_T1 else None
     npart = L.n_part(E, H)
+    if need_T1 and E > 0 and H == 64 and row_maps_available() and deterministic_backward():
+        G, gW, gb = _message_bwd_rows(kind, seg, m, e, node_in, W, g_e, accumulate, g_acc, eid, npart)
+        return g_e, _sum_rows_by_neighbour(seg, G, N), gW.sum(0), gb.sum(0)
+    gT1 = torch.zeros((N, H), dtype=torch.float32, device=dev) if need_T1 else None
     gW = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
     gb = torch.empty((npart, H), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev), _track("pna_message_bwd" if kind == 0 else "gine_message_bwd"):
@@ -442,13 +481,23 @@ def _edge_update_bwd(st: EdgeStructure, g_out, h, e, W1, W2, alpha, beta, need_P
     E, H = e.shape
     dev = e.device
     g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
-    gP = torch.zeros((nP or st.num_nodes, H), dtype=torch.float32, device=dev) if need_P else None
-    gQ = torch.zeros((nQ or st.num_nodes, H), dtype=torch.float32, device=dev) if need_Q else None
     npart = L.n_part(E, H)
     gW1 = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
     gW2 = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
     gb1 = torch.empty((npart, H), dtype=torch.float32, device=dev)
     gb2 = torch.empty((npart, H), dtype=torch.float32, device=dev)
+    if (need_P or need_Q) and E > 0 and H == 64 and row_maps_available() and deterministic_backward():
+        Gh = torch.empty((E, H), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev), _track("edge_update_bwd"):
+            L.check(L.lib().b200mp_edge_update_bwd_rows(E, L.ptr(g_out), L.ptr(h), L.ptr(e), L.ptr(W1), L.ptr(W2), alpha, beta, L.ptr(g_e),
+                                                        L.ptr(Gh), L.ptr(gW1), L.ptr(gb1), L.ptr(gW2), L.ptr(gb2), npart, L.ptr(g_eid),
+                                                        L.ptr(e_eid), L.ptr(st.src32), L.ptr(st.dst32), L.stream()),
+                    "b200mp_edge_update_bwd_rows")
+        gQ = _segment_sum_rows(st.fwd, Gh)[: (nQ or st.num_nodes)] if need_Q else None
+        gP = _sum_rows_by_neighbour(st.fwd, Gh, nP or st.num_nodes) if need_P else None
+        return g_e, gP, gQ, gW1.sum(0), gb1.sum(0), gW2.sum(0), gb2.sum(0)
+    gP = torch.zeros((nP or st.num_nodes, H), dtype=torch.float32, device=dev) if need_P else None
+    gQ = torch.zeros((nQ or st.num_nodes, H), dtype=torch.float32, device=dev) if need_Q else None
     with torch.cuda.device(dev), _track("edge_update_bwd"):
         L.check(L.lib().b200mp_edge_update_bwd(H, E, L.ptr(g_out), L.ptr(h), L.ptr(e), L.ptr(st.src32),
                                                L.ptr(st.dst32), L.ptr(W1), L.ptr(W2), alpha, beta,

@@ -35,6 +35,17 @@ class SegmentIndex:
     eid32: Optional[torch.Tensor] = None   # int32 [E] row of edge k in e-storage (None = k)
     _heavy: Optional[tuple] = field(default=None, repr=False)
     _perm32: Optional[torch.Tensor] = field(default=None, repr=False)
+    _by_nbr: Optional[dict] = field(default=None, repr=False)
+
+    def by_neighbour(self, num_rows: int) -> "SegmentIndex":
+        """The sorted edges grouped (stably) by their OTHER end point: ``perm`` = positions in this index's order, ``ptr`` over
+        ``num_rows`` neighbour ids.  Used by the atomic-free backward (functional.set_deterministic): gradient rows written in
+        this index's order are summed per neighbour row without scatters.  Built once per structure and row count."""
+        if self._by_nbr is None:
+            self._by_nbr = {}
+        if num_rows not in self._by_nbr:
+            self._by_nbr[num_rows] = build_segment_index(self.other, self.other, int(num_rows))
+        return self._by_nbr[num_rows]
 
     def perm32(self):
         """perm as int32 (row map for kernels that read / write the caller's edge order)."""
