@@ -43,8 +43,19 @@ int persistent_grid(const void* kernel, size_t smem, int64_t work_items, int thr
     if (dbg) {          // diagnostics: resident CTAs per SM of every persistent kernel (stderr)
         cudaFuncAttributes fa{};
         cudaFuncGetAttributes(&fa, kernel);
-        fprintf(stderr, "[b200mp occ] kernel %p: threads %d dyn smem %zu static smem %zu regs %d -> %d CTA/SM (%s)\n", kernel, threads,
-                smem, fa.sharedSizeBytes, fa.numRegs, per_sm, cudaGetErrorString(oe));
+        int dev = 0, smem_sm = 0, smem_res = 0, regs_sm = 0, blk_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+        cudaDeviceGetAttribute(&smem_res, cudaDevAttrReservedSharedMemoryPerBlock, dev);
+        cudaDeviceGetAttribute(&regs_sm, cudaDevAttrMaxRegistersPerMultiprocessor, dev);
+        cudaDeviceGetAttribute(&blk_sm, cudaDevAttrMaxBlocksPerMultiprocessor, dev);
+        int probe[4] = {0, 0, 0, 0};
+        const size_t tries[4] = {48 * 1024, 80 * 1024, 96 * 1024, 110 * 1024};
+        for (int i = 0; i < 4; ++i) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&probe[i], kernel, threads, tries[i]);
+        fprintf(stderr, "[b200mp occ] kernel %p: threads %d dyn smem %zu static smem %zu regs %d maxDyn %d carveout %d -> %d CTA/SM (%s); "
+                "SM: smem %d reserved/block %d regs %d blocks %d; occupancy at 48/80/96/110 KB: %d %d %d %d\n", kernel, threads,
+                smem, fa.sharedSizeBytes, fa.numRegs, fa.maxDynamicSharedSizeBytes, fa.preferredShmemCarveout, per_sm, cudaGetErrorString(oe),
+                smem_sm, smem_res, regs_sm, blk_sm, probe[0], probe[1], probe[2], probe[3]);
     }
     if (oe != cudaSuccess || per_sm < 1) { per_sm = 1; (void)cudaGetLastError(); }
     int64_t g = (int64_t)device_info().sms * per_sm;
