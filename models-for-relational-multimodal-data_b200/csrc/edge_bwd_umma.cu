@@ -29,6 +29,8 @@ struct UpdBwdUArgs {
 constexpr int NTB = 512;                  // threads per CTA of the backward kernels (one CTA per SM)
 constexpr int CWB = HH / (NTB / TE);      // 16 accumulator columns per tensor-memory thread
 constexpr int NPB = RowRegs<NTB>::NP;     // 4 adjacent rows per thread in the coalesced mapping
+constexpr uint32_t FLUSH_U = WGRAD_FLUSH_EDGES / 64;      // tiles between drains: update backward (64-edge tiles)
+constexpr uint32_t FLUSH_M = WGRAD_FLUSH_EDGES / TE;      // message backward (128-edge tiles)
 
 // One RED per run of equal node ids among a thread's adjacent rows (edges are sorted by
 // destination, so runs are the rule on that side); when the whole warp (8 adjacent rows) is one
@@ -146,7 +148,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
         fence_after();
         if (lt == 0) {
             gemm3_data64(T_U, G_hi, G_lo, W2_hi, W2_lo, 0);
-            gemm3_wgrad64(T_GW2, G_hi, G_lo, H_hi, H_lo, it > 0);
+            gemm3_wgrad64(T_GW2, G_hi, G_lo, H_hi, H_lo, (it % FLUSH_U) != 0);
             mma_commit(&bar[0]);
         }
         load_rows(Re, a.e, a.e_eid, row0, nrows, lt);                 // e tile in flight during the MMAs
@@ -191,7 +193,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
         // ---- phase B: ACC2 = Gh W1; GW1 += Gh^T e
         if (lt == 0) {
             gemm3_data64(T_ACC2, H_hi, H_lo, W1_hi, W1_lo, 0);
-            gemm3_wgrad64(T_GW1, H_hi, H_lo, G_hi, G_lo, it > 0);
+            gemm3_wgrad64(T_GW1, H_hi, H_lo, G_hi, G_lo, (it % FLUSH_U) != 0);
             mma_commit(&bar[1]);
         }
         int nrows_next = 0;
@@ -216,15 +218,21 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
 #pragma unroll
         for (int i = 0; i < NP; ++i) Rg.v[i] = Re.v[i];
         nrows_pf = nrows_next;
+        if ((it % FLUSH_U) == FLUSH_U - 1) {             // drain the two weight-gradient accumulators (both products are complete)
+            store_wgrad_partial(T_GW1, a.gW1_part + v0 * HH * HH, 1.f, true, lt, it >= FLUSH_U);
+            store_wgrad_partial(T_GW2, a.gW2_part + v0 * HH * HH, a.beta, true, lt, it >= FLUSH_U);
+        }
         fence_before();
         group_sync(grp);
         fence_after();
     }
 
     if (active) {
-        const bool any = it > 0;
-        store_wgrad_partial(T_GW1, a.gW1_part + v0 * HH * HH, 1.f, any, lt);
-        store_wgrad_partial(T_GW2, a.gW2_part + v0 * HH * HH, a.beta, any, lt);
+        const bool any = (it % FLUSH_U) != 0, flushed = it >= FLUSH_U;        // tiles since the last drain | drained before
+        if (any || !flushed) {
+            store_wgrad_partial(T_GW1, a.gW1_part + v0 * HH * HH, 1.f, any, lt, flushed);
+            store_wgrad_partial(T_GW2, a.gW2_part + v0 * HH * HH, a.beta, any, lt, flushed);
+        }
         group_column_sums(G_hi, accb1, a.gb1_part + v0 * HH, 1.f, lt, grp);
         group_column_sums(G_hi, accb2, a.gb2_part + v0 * HH, a.beta, lt, grp);
     }
@@ -367,7 +375,7 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
         fence_after();
         if (tid == 0) {
             gemm3_data(tm, G_hi, G_lo, W_hi, W_lo, 0);
-            gemm3_wgrad(T_GW, G_hi, G_lo, E_hi, E_lo, it > 0);
+            gemm3_wgrad(T_GW, G_hi, G_lo, E_hi, E_lo, (it % FLUSH_M) != 0);
             mma_commit(&sync.bar[0]);
         }
         int64_t orow[NP];
@@ -403,12 +411,15 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a)
             v = v + prev[i];
             if (r < nrows) st4(a.g_e + orow[i] * HH + j * 4, v);
         }
+        if ((it % FLUSH_M) == FLUSH_M - 1)                // drain the weight-gradient accumulator
+            store_wgrad_partial(T_GW, a.gW_part + (int64_t)blockIdx.x * HH * HH, 1.f, true, tid, it >= FLUSH_M);
         fence_before();
         __syncthreads();
         fence_after();
     }
 
-    store_wgrad_partial(T_GW, a.gW_part + (int64_t)blockIdx.x * HH * HH, 1.f, it > 0, tid);
+    if ((it % FLUSH_M) != 0 || it < FLUSH_M)
+        store_wgrad_partial(T_GW, a.gW_part + (int64_t)blockIdx.x * HH * HH, 1.f, (it % FLUSH_M) != 0, tid, it >= FLUSH_M);
     cta_column_sums(G_hi, accb, a.gb_part + (int64_t)blockIdx.x * HH, 1.f, tid);
     fence_before();
     __syncthreads();

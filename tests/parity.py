@@ -143,6 +143,8 @@ def check_fixture(name, device):
         if sel is not None:
             cond = max(cond, yard(sel, truth, floor))
         tol = max(FP32_TOL, 4 * cond)
+        if what.endswith("bias") and what.startswith("grad."):
+            tol = max(tol, 2 * FP32_TOL)      # biases ahead of a BatchNorm: an exactly-zero true gradient, judged against a floor
         err = rel_err(got, want, floor)
         worst[what] = (err, tol)
         assert tol < 1e-3, f"{name} {what}: fixture itself is {tol / 4:.2e} from fp64"

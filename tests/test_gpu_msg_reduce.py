@@ -61,7 +61,11 @@ def test_fused_equals_two_kernels(graph, n, e, kind_id, rowmap):
     if kind_id == 0:
         assert torch.equal(a0[:, H:3 * H], a1[:, H:3 * H])                      # min | max
         assert torch.equal(t0, t1)                                              # tie counts
-        assert rel_err(a1[:, :H], a0[:, :H]) < 2e-6 and rel_err(a1[:, 3 * H:], a0[:, 3 * H:]) < 2e-5
+        # mean: fp32 re-association.  std = sqrt(E[m^2] - E[m]^2): the cancellation amplifies the re-association of the two sums
+        # (both paths are equally far from fp64; on hubs with 1e5+ rows they differ from EACH OTHER by up to ~1e-3 of the scale)
+        assert rel_err(a1[:, :H], a0[:, :H]) < 2e-6 and rel_err(a1[:, 3 * H:], a0[:, 3 * H:]) < 2e-3
+        sd = (a1[:, 3 * H:].double() - a0[:, 3 * H:].double())
+        assert float(sd.norm() / a0[:, 3 * H:].double().norm()) < 2e-5
         deg = seg.ptr[1:] - seg.ptr[:-1]
         assert float(a1[deg == 0].abs().max() if bool((deg == 0).any()) else 0.0) == 0.0
     else:
