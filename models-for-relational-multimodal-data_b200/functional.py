@@ -728,6 +728,10 @@ def transformer_encoder_layer(layer: torch.nn.TransformerEncoderLayer, x: torch.
         raise ValueError("b200mp column attention implements the post-norm layer the reference builds")
     R, S, Cc = x.shape
     mha = layer.self_attn
+    if S > 8 or Cc % mha.num_heads or (Cc // mha.num_heads) not in (1, 2, 4, 8, 16):
+        # shapes the attention kernels do not cover (more than 8 tokens per row, head widths other than 1..16): torch's own
+        # layer on the device, as add_dropout_layernorm / bn_relu_residual do for their uncovered shapes
+        return layer(x)
     x2 = x.reshape(R * S, Cc)
     Wq, Wk, Wv = mha.in_proj_weight.chunk(3)
     bq, bk, bv = mha.in_proj_bias.chunk(3)
