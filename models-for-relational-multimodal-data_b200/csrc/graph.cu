@@ -58,6 +58,10 @@ int persistent_grid(const void* kernel, size_t smem, int64_t work_items, int thr
                 smem_sm, smem_res, regs_sm, blk_sm, probe[0], probe[1], probe[2], probe[3]);
     }
     if (oe != cudaSuccess || per_sm < 1) { per_sm = 1; (void)cudaGetLastError(); }
+    if (const char* f = getenv("B200MP_FORCE_CTAS_PER_SM")) {      // experiment switch: grid = SMs x this, whatever the occupancy query says
+        const int v = atoi(f);
+        if (v >= 1 && v <= 8) per_sm = v;
+    }
     int64_t g = (int64_t)device_info().sms * per_sm;
     if (work_items < g) g = work_items;
     return (int)(g < 1 ? 1 : g);

@@ -366,10 +366,11 @@ def _segment_reduce(kind, seg: SegmentIndex, m, H):
 
 
 def fused_reduce_available(H: int) -> bool:
-    """The fused message + segmented-reduction kernel (csrc/msg_reduce_umma.cu) covers H = 64 on the tensor-core path;
-    B200MP_FUSED_REDUCE=0 switches back to the two-kernel path (A/B runs)."""
+    """The fused message + segmented-reduction kernel (csrc/msg_reduce_umma.cu) covers H = 64 on the tensor-core path.  OPT-IN
+    (B200MP_FUSED_REDUCE=1): measured on B200 it is slower than the two kernels it replaces (hi_small: 3.05 ms against
+    1.03 + 0.76 ms) -- with one 8-warp CTA per SM the in-tile reduction is serial latency that nothing hides."""
     import os
-    return H == 64 and row_maps_available() and os.environ.get("B200MP_FUSED_REDUCE", "1") != "0"
+    return H == 64 and row_maps_available() and os.environ.get("B200MP_FUSED_REDUCE", "0") == "1"
 
 
 def _message_fwd_reduce(kind, seg: SegmentIndex, e, eid, W, b, T1, T2):
