@@ -5,6 +5,7 @@
 // Per tile of 128 edges the per-edge GEMMs run on the tensor cores with accumulators in tensor
 // memory; the two weight gradients accumulate in tensor memory across ALL tiles of the CTA and
 // are written once as a per-CTA partial.
+#include <cstdlib>
 #include "umma_edge.cuh"
 
 namespace b200mp {
@@ -29,8 +30,14 @@ struct UpdBwdUArgs {
 constexpr int NTB = 512;                  // threads per CTA of the backward kernels (one CTA per SM)
 constexpr int CWB = HH / (NTB / TE);      // 16 accumulator columns per tensor-memory thread
 constexpr int NPB = RowRegs<NTB>::NP;     // 4 adjacent rows per thread in the coalesced mapping
-constexpr uint32_t FLUSH_U = WGRAD_FLUSH_EDGES / 64;      // tiles between drains: update backward (64-edge tiles)
-constexpr uint32_t FLUSH_M = WGRAD_FLUSH_EDGES / TE;      // message backward (128-edge tiles)
+// edges between drains of the weight-gradient accumulators (B200MP_WGRAD_FLUSH overrides; 0 = never: round-1 behaviour)
+static uint32_t wgrad_flush_edges() {
+    if (const char* v = getenv("B200MP_WGRAD_FLUSH")) {
+        const long n = atol(v);
+        return n <= 0 ? 0x40000000u : (uint32_t)n;
+    }
+    return WGRAD_FLUSH_EDGES;
+}
 
 // One RED per run of equal node ids among a thread's adjacent rows (edges are sorted by
 // destination, so runs are the rule on that side); when the whole warp (8 adjacent rows) is one
@@ -82,7 +89,7 @@ __device__ __forceinline__ void cta_column_sums(float* red, float4 acc, float* _
 
 // (namespace dual -- the two-pipelines-per-CTA helpers -- lives in umma_edge.cuh: the update forward uses it too)
 
-__global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArgs a, int n_virtual) {
+__global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArgs a, int n_virtual, uint32_t FLUSH_U) {
     using namespace dual;
     constexpr int NP = NPG;
     extern __shared__ __align__(128) float smem_raw[];
@@ -248,7 +255,8 @@ int launch_upd_bwd_umma(int64_t E, const float* g_out, const float* h, const flo
     UpdBwdUArgs a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, g_eid, e_eid, gh_out};
     const size_t smem = 8 * dual::RG_T::BYTES + 4 * WT::BYTES + 1024;
     B200MP_CUDA(cudaFuncSetAttribute(edge_update_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    edge_update_bwd_umma_kernel<<<(n_part + 1) / 2, NTB, smem, st>>>(a, n_part);   // two 64-edge pipelines (partial rows) per CTA
+    const uint32_t fl = wgrad_flush_edges() / 64;          // tiles (64 edges) between drains
+    edge_update_bwd_umma_kernel<<<(n_part + 1) / 2, NTB, smem, st>>>(a, n_part, fl < 1 ? 1 : fl);   // two 64-edge pipelines (partial rows) per CTA
     B200MP_LAUNCH_CHECK();
     return 0;
 }
@@ -279,7 +287,7 @@ __device__ __forceinline__ float pna_g(float m, float c0, float c1, float gmn, f
 }
 
 template <int KIND>
-__global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a) {
+__global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a, uint32_t FLUSH_M) {
     constexpr int NTH = NTB, CW = CWB, NP = NPB;
     extern __shared__ __align__(128) float smem_raw[];
     float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;   // keeps the shared address space
@@ -433,7 +441,8 @@ int launch_msg_bwd_umma(int kind, int64_t E, const float* m, const float* e, con
     const size_t smem = 4 * RT::BYTES + 2 * WT::BYTES + 1024;
     auto kern = kind == 0 ? message_bwd_umma_kernel<0> : message_bwd_umma_kernel<1>;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<n_part, NTB, smem, st>>>(a);
+    const uint32_t fl = wgrad_flush_edges() / TE;
+    kern<<<n_part, NTB, smem, st>>>(a, fl < 1 ? 1 : fl);
     B200MP_LAUNCH_CHECK();
     return 0;
 }

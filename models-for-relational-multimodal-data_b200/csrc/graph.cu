@@ -34,31 +34,40 @@ bool use_tensor_cores() {
 }
 
 int persistent_grid(const void* kernel, size_t smem, int64_t work_items, int threads) {
+    // Resident CTAs per SM from the kernel's own resource usage.  cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for every
+    // tcgen05 kernel here, whatever its footprint (B200, CUDA 12.9: even at 48 KB of shared memory), while ncu's launch statistics
+    // give "Block Limit Registers 2 / Shared Mem 2" for the 97 KB kernels and a grid of 2 x SMs does run them side by side
+    // (hi_small: message forward 1.03 -> 0.87 ms, node_linear64 0.140 -> 0.113 ms).
     int per_sm = 1;
-    // Without this the driver picks the SMALLEST shared-memory carve-out that holds one CTA (measured on B200, round 2:
-    // every 97 KB kernel reported -- and ran -- 1 CTA per SM although two fit in the 228 KB of an SM).
-    (void)cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
-    cudaError_t oe = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem);
-    static const bool dbg = [] { const char* v = getenv("B200MP_DEBUG_OCC"); return v && v[0] == '1'; }();
-    if (dbg) {          // diagnostics: resident CTAs per SM of every persistent kernel (stderr)
-        cudaFuncAttributes fa{};
-        cudaFuncGetAttributes(&fa, kernel);
-        int dev = 0, smem_sm = 0, smem_res = 0, regs_sm = 0, blk_sm = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
-        cudaDeviceGetAttribute(&smem_res, cudaDevAttrReservedSharedMemoryPerBlock, dev);
-        cudaDeviceGetAttribute(&regs_sm, cudaDevAttrMaxRegistersPerMultiprocessor, dev);
-        cudaDeviceGetAttribute(&blk_sm, cudaDevAttrMaxBlocksPerMultiprocessor, dev);
-        int probe[4] = {0, 0, 0, 0};
-        const size_t tries[4] = {48 * 1024, 80 * 1024, 96 * 1024, 110 * 1024};
-        for (int i = 0; i < 4; ++i) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&probe[i], kernel, threads, tries[i]);
-        fprintf(stderr, "[b200mp occ] kernel %p: threads %d dyn smem %zu static smem %zu regs %d maxDyn %d carveout %d -> %d CTA/SM (%s); "
-                "SM: smem %d reserved/block %d regs %d blocks %d; occupancy at 48/80/96/110 KB: %d %d %d %d\n", kernel, threads,
-                smem, fa.sharedSizeBytes, fa.numRegs, fa.maxDynamicSharedSizeBytes, fa.preferredShmemCarveout, per_sm, cudaGetErrorString(oe),
-                smem_sm, smem_res, regs_sm, blk_sm, probe[0], probe[1], probe[2], probe[3]);
+    cudaFuncAttributes fa{};
+    cudaError_t oe = cudaFuncGetAttributes(&fa, kernel);
+    int dev = 0, smem_sm = 233472, smem_res = 1024, regs_sm = 65536;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+    cudaDeviceGetAttribute(&smem_res, cudaDevAttrReservedSharedMemoryPerBlock, dev);
+    cudaDeviceGetAttribute(&regs_sm, cudaDevAttrMaxRegistersPerMultiprocessor, dev);
+    if (oe == cudaSuccess) {
+        const int warps = (threads + 31) / 32;
+        const int regs_warp = ((fa.numRegs * 32 + 511) / 512) * 512;                 // allocation unit: 512 registers per warp
+        const size_t smem_blk = ((smem + fa.sharedSizeBytes + (size_t)smem_res + 127) / 128) * 128;
+        const int by_regs = regs_warp > 0 ? regs_sm / (regs_warp * warps) : 32;
+        const int by_smem = smem_blk > 0 ? (int)((size_t)smem_sm / smem_blk) : 32;
+        const int by_warps = 64 / warps;
+        per_sm = by_regs < by_smem ? by_regs : by_smem;
+        if (by_warps < per_sm) per_sm = by_warps;
+        if (per_sm > 2) per_sm = 2;             // tensor-memory columns (512 per SM) and the kernels' design point: at most two
+        if (per_sm < 1) per_sm = 1;
+    } else {
+        (void)cudaGetLastError();
     }
-    if (oe != cudaSuccess || per_sm < 1) { per_sm = 1; (void)cudaGetLastError(); }
-    if (const char* f = getenv("B200MP_FORCE_CTAS_PER_SM")) {      // experiment switch: grid = SMs x this, whatever the occupancy query says
+    static const bool carve = [] { const char* v = getenv("B200MP_CARVEOUT"); return !(v && v[0] == '0'); }();
+    if (carve && per_sm > 1)                    // two CTAs only fit with the largest shared-memory carve-out; one-CTA kernels keep their L1
+        (void)cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+    static const bool dbg = [] { const char* v = getenv("B200MP_DEBUG_OCC"); return v && v[0] == '1'; }();
+    if (dbg)
+        fprintf(stderr, "[b200mp occ] kernel %p: threads %d dyn smem %zu static smem %zu regs %d -> %d CTA/SM\n", kernel, threads, smem,
+                fa.sharedSizeBytes, fa.numRegs, per_sm);
+    if (const char* f = getenv("B200MP_FORCE_CTAS_PER_SM")) {      // experiment switch
         const int v = atoi(f);
         if (v >= 1 && v <= 8) per_sm = v;
     }

@@ -62,7 +62,31 @@ def tab_case(model, env):
         os.environ.pop(k)
 
 
+def wgrad_chain_case():
+    """error of the edge update's W2 gradient (g^T h over E edges) against fp64 as a function of the drain interval"""
+    E, n = 1_000_000, 65114
+    g = torch.Generator(device=dev).manual_seed(3)
+    ei = torch.stack([torch.randint(0, n, (E,), device=dev, generator=g), torch.randint(0, n, (E,), device=dev, generator=g)])
+    st = G.edge_structure(ei, n)
+    gout, e = torch.randn(E, 64, device=dev, generator=g), torch.randn(E, 64, device=dev, generator=g)
+    h = torch.relu(torch.randn(E, 64, device=dev, generator=g))
+    W1, W2 = torch.randn(64, 64, device=dev, generator=g) / 8, torch.randn(64, 64, device=dev, generator=g) / 8
+    ref2 = 0.5 * gout.double().t() @ h.double()
+    for fl in ("0", "8192", "2048", "1024", "512", "256"):
+        os.environ["B200MP_WGRAD_FLUSH"] = fl
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        out = BF._edge_update_bwd(st, gout, h, e, W1, W2, 1.0, 0.5, True, True)
+        t0.record()
+        for _ in range(5):
+            out = BF._edge_update_bwd(st, gout, h, e, W1, W2, 1.0, 0.5, True, True)
+        t1.record()
+        torch.cuda.synchronize()
+        print(f"wgrad drain every {fl:>5s} edges: gW2 relL2 vs fp64 {l2(out[5], ref2):.2e}, {t0.elapsed_time(t1) / 5:.3f} ms per launch (E = 1 M)")
+    os.environ.pop("B200MP_WGRAD_FLUSH")
+
+
 if __name__ == "__main__":
+    wgrad_chain_case()
     for n_w in (1, 2, 3):
         linear_group_case(n_w)
     pair_gather_case()

@@ -61,10 +61,12 @@ def _check(case, name, got, refs32, o64, forward):
     an ulp of their kink, and an fp32 evaluation lands on either side (measured: the CPU fp32 oracle's own gradient moves by 3.7e-3 relative
     L2 / 2.5e-2 max between two thread counts on the interleaved case, through ONE hub node).  A flip changes a sparse set of rows by a lot
     and leaves the bulk untouched, so the MEDIAN element-wise error must still be at the oracle's level and the relative L2 error below
-    2e-2; a systematic error in the smooth region (1e-4, say) moves the median and fails."""
+    2e-2; a systematic error in the smooth region (1e-4, say) moves the median and fails.  "At the oracle's level" = within 4x the
+    oracle's median or 5e-6 (half the 1e-5 tolerance): the 3xTF32 tensor-core products carry ~1e-6 per GEMM against the CPU's 6e-8
+    (measured: node linears 4e-7..1.3e-6 relative L2), so the kernels' bulk noise sits at ~2e-6 of the scale after two layers."""
     k, o, txt = _line(case, name, got, refs32, o64)
     strict = k[2] < max(TOL, 4 * o[2]) and k[1] <= max(1e-4, 4 * o[1]) and (not forward or k[0] < max(TOL, 4 * o[0]))
-    kink = (not forward) and k[2] < 2e-2 and k[3] <= max(2e-7, 4 * o[3])
+    kink = (not forward) and k[2] < 2e-2 and k[3] <= max(5e-6, 4 * o[3])
     _emit(txt + ("" if strict else "   [kink decision: bulk at oracle level]" if kink else "   [FAIL]"))
     assert strict or kink, (case, name, k, o)
 
