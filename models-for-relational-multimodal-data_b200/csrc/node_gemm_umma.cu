@@ -204,6 +204,7 @@ static int launch_node_linear(const NodeLinArgs& a, cudaStream_t st) {
 // MN-major views of row32 panels (umma.cuh), the reduction runs over the node rows of the tile.
 namespace ng {
 constexpr int RW = 32;                    // node rows per tile
+constexpr uint32_t WG_DRAIN_TILES = 32;   // 1024 rows between drains of the weight-gradient accumulator
 using WP = RowFmt<RW, 32>;                // 4 KB panel [32 rows x 32 columns]
 struct NodeWgArgs {
     int64_t N; int ldx; int ldy;
@@ -251,6 +252,26 @@ __global__ void __launch_bounds__(NT2, 2) node_wgrad_umma_kernel(NodeWgArgs a) {
         for (int p = 0; p < YPN; ++p) yr[p] = ldg4(a.Y + rc * a.ldy + p * 32 + piece * 4);
     };
     if ((int64_t)blockIdx.x < ntiles) prefetch(blockIdx.x);
+    // accumulator [128 x NO] -> this CTA's partial (thread (t, ch) = row 128 kb + t, columns 32 ch + 64 q ..): at the end and every
+    // WG_DRAIN_TILES tiles in between -- a sum kept in one tensor-memory accumulator loses accuracy linearly in the number of MMAs
+    // added into it (umma_edge.cuh: WGRAD_FLUSH_EDGES has the measurement); `valid` false writes zeros, `accumulate` adds to the
+    // partial an earlier drain left
+    auto drain = [&](bool valid, bool accumulate) {
+        const int t = tid & (TE - 1), ch = tid >> 7;
+        float* out = a.part + ((int64_t)blockIdx.x * a.K + kb * 128 + t) * NO;
+        const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
+#pragma unroll 1
+        for (int c0 = ch * 16; c0 < NO; c0 += 32) {
+            float v[16];
+            if (valid) tmem_ld16(tm + lane_off + c0, v);
+#pragma unroll
+            for (int c = 0; c < 16; c += 4) {
+                float4 w = valid ? f4(v[c], v[c + 1], v[c + 2], v[c + 3]) : f4(0.f, 0.f, 0.f, 0.f);
+                if (accumulate) w = w + lds4(out + c0 + c);
+                st4(out + c0 + c, w);
+            }
+        }
+    };
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         const int o = WP::off(row, piece);
@@ -275,28 +296,16 @@ __global__ void __launch_bounds__(NT2, 2) node_wgrad_umma_kernel(NodeWgArgs a) {
         __syncthreads();
         fence_after();
         if (tid == 0) {
-            issue_wgrad_gemm_row32<RW, 128, NO>(tm, smem_u32(X_lo), smem_u32(Y_hi), it > 0);
+            issue_wgrad_gemm_row32<RW, 128, NO>(tm, smem_u32(X_lo), smem_u32(Y_hi), (it % WG_DRAIN_TILES) != 0);
             issue_wgrad_gemm_row32<RW, 128, NO>(tm, smem_u32(X_hi), smem_u32(Y_lo), 1);
             issue_wgrad_gemm_row32<RW, 128, NO>(tm, smem_u32(X_hi), smem_u32(Y_hi), 1);
             mma_commit(&bar_m);
         }
         mbar_wait(&bar_m, it & 1);
         fence_after();
+        if ((it % WG_DRAIN_TILES) == WG_DRAIN_TILES - 1) drain(true, it >= WG_DRAIN_TILES);
     }
-    // ---- partial [128 x NO] of this CTA: thread (t, ch) = row 128 kb + t, columns 32 ch + 64 q ..
-    {
-        const int t = tid & (TE - 1), ch = tid >> 7;
-        float* out = a.part + ((int64_t)blockIdx.x * a.K + kb * 128 + t) * NO;
-        const uint32_t lane_off = (uint32_t)((warp & 3) * 32) << 16;
-#pragma unroll 1
-        for (int c0 = ch * 16; c0 < NO; c0 += 32) {
-            float v[16];
-            if (it > 0) tmem_ld16(tm + lane_off + c0, v);
-#pragma unroll
-            for (int c = 0; c < 16; c += 4)
-                st4(out + c0 + c, it > 0 ? f4(v[c], v[c + 1], v[c + 2], v[c + 3]) : f4(0.f, 0.f, 0.f, 0.f));
-        }
-    }
+    if ((it % WG_DRAIN_TILES) != 0 || it < WG_DRAIN_TILES) drain((it % WG_DRAIN_TILES) != 0, it >= WG_DRAIN_TILES);
     fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tm, 256);

@@ -202,10 +202,12 @@ __device__ __forceinline__ float column_total(const float* bsum, int c) {
 
 // The M = 64 accumulator (weight gradient [64 x 64]) -> this CTA's partial in global memory.
 // Row m sits in tensor-memory lane (m % 16) + 32 (m / 16): warp w, lanes 0..15 own rows 16w..16w+15.
-// accumulate: add to what an earlier flush left in `part` (the accumulators are drained every WGRAD_FLUSH_EDGES edges: a
-// tensor-memory accumulator that runs over all ~2e5 edges of a CTA is an fp32 chain of ~3e4 partial sums and loses ~2e-5 of a
-// well-conditioned weight gradient -- measured against the fp64 oracle on the 1 M-edge bench sample; two levels keep it < 3e-6).
-constexpr int WGRAD_FLUSH_EDGES = 8192;
+// accumulate: add to what an earlier drain left in `part`.  The weight-gradient accumulators are drained every WGRAD_FLUSH_EDGES
+// edges: the error of a sum kept in ONE tensor-memory accumulator grows linearly with the number of MMAs added into it (the
+// tensor core's fp32 accumulation does not round to nearest).  Measured on B200 against fp64, edge update's gW2 = g^T h over 1 M
+// edges, relative L2: 2.3e-5 with 3 400 edges per accumulator chain, 1.2e-5 at 2 048, 6.4e-6 at 1 024, 3.1e-6 at 512, 1.5e-6 at
+// 256 (kernel time +0 / +1 / +3 / +6 / +14 %).  1 024 keeps the gradient inside the 1e-5 tolerance for +3 %.
+constexpr int WGRAD_FLUSH_EDGES = 1024;
 __device__ __forceinline__ void store_wgrad_partial(uint32_t tmem_cols, float* part, float scale, bool valid, int tid,
                                                     bool accumulate = false) {
     const int warp = tid >> 5, lane = tid & 31;
