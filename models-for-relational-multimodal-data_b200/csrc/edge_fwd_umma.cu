@@ -361,9 +361,10 @@ int launch_edge_fwd_umma(int mode, int64_t E, const float* e, const int32_t* eid
         case 0: return launch_fwd_umma_mode<0>(a, st);
         case 1: return launch_fwd_umma_mode<1>(a, st);
         case 2: {
-            // B200MP_UPD_PIPE=0: the one-tile-at-a-time kernel (A/B runs)
+            // B200MP_UPD_PIPE=1: the software-pipelined kernel.  Opt-in: same-box A/B on B200 -- hi_small 1.63 -> 1.54 ms, but
+            // hi_medium 9.80 -> 9.94 ms (the residual rows re-read behind the MMAs stop hitting L2 once 148 SMs stream 8 GB tensors)
             const char* v = getenv("B200MP_UPD_PIPE");
-            const bool pipe = !(v && v[0] == '0');
+            const bool pipe = v && v[0] == '1';
             return pipe ? launch_update_fwd_pipe(a, st) : launch_fwd_umma_mode<2>(a, st);
         }
     }

@@ -267,8 +267,7 @@ __global__ void __launch_bounds__(NT2, 2) node_wgrad_umma_kernel(NodeWgArgs a) {
 #pragma unroll
             for (int c = 0; c < 16; c += 4) {
                 float4 w = valid ? f4(v[c], v[c + 1], v[c + 2], v[c + 3]) : f4(0.f, 0.f, 0.f, 0.f);
-                if (accumulate) w = w + lds4(out + c0 + c);
-                st4(out + c0 + c, w);
+                if (accumulate) red_add4(out + c0 + c, w); else st4(out + c0 + c, w);     // single writer per address: deterministic
             }
         }
     };

@@ -223,8 +223,10 @@ __device__ __forceinline__ void store_wgrad_partial(uint32_t tmem_cols, float* p
             for (int c = 0; c < 16; c += 4) {
                 float4 w = valid ? make_float4(scale * v[c], scale * v[c + 1], scale * v[c + 2], scale * v[c + 3])
                                  : make_float4(0.f, 0.f, 0.f, 0.f);
-                if (accumulate) w = w + lds4(o + c);      // plain 16-byte load (same thread wrote it)
-                st4(o + c, w);
+                // later drains add with a vector RED: fire and forget (a load-add-store chain costs an L2 round trip per step while
+                // the other warps wait at the next barrier: measured +9..13 % kernel time at a 1024-edge interval); every address
+                // has ONE writer thread and its REDs arrive in program order, so the sum is still run-to-run identical
+                if (accumulate) red_add4(o + c, w); else st4(o + c, w);
             }
         }
     }
