@@ -94,6 +94,15 @@ KERNEL_BYTES = {
 }
 
 
+# bf16 storage: the [E,H] rows are 2 H bytes, the gathered / scattered node rows stay fp32
+KERNEL_BYTES_BF16 = {
+    "pna_message_fwd": 2 * 2 * H + 4 * H + 8, "gine_message_fwd": 2 * 2 * H + 4 * H + 4,
+    "segment_reduce_pna": 2 * H, "segment_reduce_sum": 2 * H,
+    "edge_update_fwd": 3 * 2 * H + 4 * H + 8, "edge_update_bwd": 4 * 2 * H + 4 * H + 8,
+    "pna_message_bwd": 3 * 2 * H + 4 * H + 8, "gine_message_bwd": 3 * 2 * H + 4 * H + 8,
+}
+
+
 class ClockSampler:
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -378,6 +387,9 @@ def run_b200(args, rank, world, local_rank):
         _, deg_hist = b200mp.degree_histogram(st.fwd.ptr)
         n_loc, e_loc = n, e
     model = make_model(args.model, deg_hist.cpu(), dev)
+    bf16 = args.dtype == "bf16"
+    if bf16:
+        model.set_edge_storage(torch.bfloat16)
     # inputs are a function of the GLOBAL row id (every rank draws the full tensor from the same seed and keeps its
     # shard), so the N = 1 / 2 / 4 / 8 runs compute the same function and their checksums are comparable
     g = torch.Generator(device=dev).manual_seed(seed)
@@ -397,6 +409,10 @@ def run_b200(args, rank, world, local_rank):
     ea = draw(e, lambda t: part.shard_edges(t), (K_COLS, H) if tab else (H,)).requires_grad_(True)
     gx = draw(n, lambda t: part.shard_nodes(t))
     ge = draw(e, lambda t: part.shard_edges(t))
+    if bf16:
+        ge = ge.to(torch.bfloat16)
+        if not tab:                           # the embedded edge features arrive in storage precision (the cast belongs to edge_emb)
+            ea = ea.detach().to(torch.bfloat16).requires_grad_(True)
     torch.cuda.empty_cache()
 
     def step(keep=False):
@@ -459,20 +475,24 @@ def run_b200(args, rank, world, local_rank):
     summ = stats.summary()
     peak, peak_src = measured_peak_gbs()
     kern = {}
+    KB = KERNEL_BYTES_BF16 if bf16 else KERNEL_BYTES
     for name, (calls, total_ms) in summ.items():
         per = total_ms / calls
         kern[name] = {"calls_per_step": calls / args.steps, "ms_per_call": round(per, 4),
                       "share_of_step": round(total_ms / ms, 4),
-                      "achieved_gbs": round(KERNEL_BYTES[name] * e_loc / (per * 1e-3) / 1e9, 1) if name in KERNEL_BYTES else None}
-    top = max(((k, v) for k, v in summ.items() if k in KERNEL_BYTES), key=lambda kv: kv[1][1])[0]
+                      "achieved_gbs": round(KB[name] * e_loc / (per * 1e-3) / 1e9, 1) if name in KB else None}
+    top = max(((k, v) for k, v in summ.items() if k in KB), key=lambda kv: kv[1][1])[0]
     achieved = kern[top]["achieved_gbs"]
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": ncu_traffic(top, args.workload, world),
                 "traffic_source": "profiles/traffic.json: ncu --set full dram__bytes_read+write per launch, captured on the build named in that file (not this run)",
                 "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": KERNEL_BYTES[top] * e_loc}
+                "algorithmic_bytes_per_launch": KB[top] * e_loc}
     step_bytes = LAYERS * (e_loc * algorithmic_bytes_per_edge(args.model) + n_loc * 12 * 4 * H)
     formula = "L*(E*(22*s*H+64) + N*12*s*H), SURVEY.md 8(d)"
+    if bf16:      # SURVEY's bf16 figure: s = 2 for the 22 [E,H] touches (it also halves the node-table gathers, which stay fp32 here)
+        step_bytes = LAYERS * (e_loc * (22 * 2 * H + 64) + n_loc * 12 * 4 * H)
+        formula = "L*(E*(22*2*H+64) + N*12*4*H): SURVEY.md 8(d) with s = 2 for the edge terms"
     if tab:      # + L column-attention layers over the (K+1)-token edge rows and the 2-token node rows, + edge_emb / node_emb
         step_bytes += LAYERS * (e_loc * tab_bytes_per_row(K_COLS + 1) + n_loc * tab_bytes_per_row(2))
         step_bytes += 2 * 4 * (e_loc * ((K_COLS + 1) * H + H) + n_loc * (2 * H + H))
@@ -563,7 +583,8 @@ def run_b200(args, rank, world, local_rank):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "ms_per_step_median": ms_median,
         "value_median": e / (ms_median * 1e-3), "higher_is_better": True,
         "scaling": "weak" if world == 1 else "strong", "checksum": checksum,
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
+        "vs_baseline": None, "dtype": "bf16 storage of the [E,H] tensors, fp32 arithmetic (extra line)" if bf16 else "f32", "data": "synthetic",
+        "config": workload_config(args, world),
         "clocks": clk, "e2e": e2e, "gpu_launches": stats.launches, "roofline": roofline, "step_roofline": step_roofline,
         "kernels": kern, "cpu_baseline": cpu,
     }
@@ -580,6 +601,8 @@ def main():
                          "token tensors (49 GB each) only fit partitioned over 8 GPUs, which is how config 5 is worded")
     ap.add_argument("--model", default="pna", choices=["pna", "gine", "tabgnn"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"],
+                    help="bf16: EXTRA line (BASELINE.json config 3) -- every [E,H] edge tensor stored as bf16, fp32 arithmetic; the f32 line is the headline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer arm")
     args = ap.parse_args()

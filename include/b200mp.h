@@ -306,6 +306,27 @@ int b200mp_edge_update_bwd_rows(int64_t E, const float* g_out, const float* h, c
                                 float* gb1_part, float* gW2_part, float* gb2_part, int n_part, const int32_t* g_eid,
                                 const int32_t* e_eid, const int32_t* src, const int32_t* dst, void* stream);
 
+/* ------------------------------------------------------------------ bf16 storage (BASELINE.json config 3)
+ * The per-edge kernels and the segmented reduction with every [E,64] tensor (e, m, h, e', the gradients) STORED as bf16 -- half
+ * the bytes of the streams that dominate the step -- while node tables, weights, partials and all arithmetic stay fp32 (bf16
+ * values are split exactly into the tf32 operands, accumulation in fp32 tensor memory).  Same contracts as the fp32 entry
+ * points (H = 64, tensor-core path); `void*` arguments are bf16 device arrays. */
+int b200mp_edge_linear_fwd_bf16(int mode, int64_t E, const void* e, const int32_t* eid, const float* W1, const float* b1,
+                                const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
+                                const float* W2, const float* b2, float alpha, float beta, void* out1, void* out2,
+                                const int32_t* out_eid, void* stream);
+int b200mp_segment_reduce_fwd_bf16(int kind, int64_t N, const int64_t* ptr, const void* m, float* agg, float* tie,
+                                   int64_t light_max, int64_t chunk, int64_t n_heavy, const int32_t* heavy_node,
+                                   const int32_t* heavy_chunk_ptr, int64_t n_chunks, const int32_t* chunk_heavy,
+                                   const int64_t* chunk_begin, float* partial, void* stream);
+int b200mp_message_bwd_bf16(int kind, int64_t E, const void* m, const void* e, const int32_t* eid, const float* node_in,
+                            const int32_t* seg, const int32_t* nbr, const float* W, void* g_e, int accumulate, float* gT1,
+                            float* gW_part, float* gb_part, int n_part, const void* g_acc, void* stream);
+int b200mp_edge_update_bwd_bf16(int64_t E, const void* g_out, const void* h, const void* e, const int32_t* src,
+                                const int32_t* dst, const float* W1, const float* W2, float alpha, float beta, void* g_e,
+                                float* gP, float* gQ, float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part,
+                                int n_part, const int32_t* g_eid, const int32_t* e_eid, void* stream);
+
 /* ------------------------------------------------------------------ read-out heads, ranking metric, pooled write-back
  * (kernels in csrc/readout.cu)
  *

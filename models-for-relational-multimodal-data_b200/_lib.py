@@ -61,6 +61,10 @@ _SIGS = {
     "b200mp_col_encode_bwd": [_p, _i, _i, _l, _i, _p, _p, _p, _p, _p],
     "b200mp_message_bwd_rows": [_i, _l, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p, _p],
     "b200mp_edge_update_bwd_rows": [_l, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _p, _p],
+    "b200mp_edge_linear_fwd_bf16": [_i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p],
+    "b200mp_segment_reduce_fwd_bf16": [_i, _l, _p, _p, _p, _p, _l, _l, _l, _p, _p, _l, _p, _p, _p, _p],
+    "b200mp_message_bwd_bf16": [_i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p, _i, _p, _p],
+    "b200mp_edge_update_bwd_bf16": [_l, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p],
     "b200mp_pair_gather_act": [_p, _p, _p, _p, _p, _l, _i, _i, _p, _p],
     "b200mp_rank_positive": [_p, _p, _l, _i, _p, _p],
     "b200mp_segment_mean_blend_fwd": [_p, _p, _p, _p, _l, _i, _p, _p],

@@ -16,12 +16,13 @@ using namespace ue;
 //   g_e = alpha g + Gh W1                  ACC2 = alpha g + Gh W1 (data GEMM, tmem cols  64..127)
 //   gW2 = beta g^T h                       GW2                    (wgrad,     tmem cols 128..191)
 //   gW1 = Gh^T e                           GW1                    (wgrad,     tmem cols 192..255)
+template <typename T>                   // T: storage type of the [E,H] tensors (float | bf16)
 struct UpdBwdUArgs {
     int64_t E;
-    const float* g_out; const float* h; const float* e;
+    const T* g_out; const T* h; const T* e;
     const int32_t* src; const int32_t* dst;
     const float* W1; const float* W2; float alpha, beta;
-    float* g_e; float* gP; float* gQ;
+    T* g_e; float* gP; float* gQ;
     float* gW1_part; float* gb1_part; float* gW2_part; float* gb2_part;
     const int32_t* g_eid; const int32_t* e_eid;       // storage rows of g_out / e for segment position k (null = k)
     float* gh_out;                                    // optional [E,H] (segment order): Gh rows, for the atomic-free node gradients
@@ -89,7 +90,8 @@ __device__ __forceinline__ void cta_column_sums(float* red, float4 acc, float* _
 
 // (namespace dual -- the two-pipelines-per-CTA helpers -- lives in umma_edge.cuh: the update forward uses it too)
 
-__global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArgs a, int n_virtual, uint32_t FLUSH_U) {
+template <typename T>
+__global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArgs<T> a, int n_virtual, uint32_t FLUSH_U) {
     using namespace dual;
     constexpr int NP = NPG;
     extern __shared__ __align__(128) float smem_raw[];
@@ -220,7 +222,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
         for (int i = 0; i < NP; ++i) {
             const int r = g * NP + i;
             const float4 v = a.alpha * Rg.v[i] + lds4(stage + stage_off(r, j));
-            if (r < nrows) st4(a.g_e + (row0 + r) * HH + j * 4, v);
+            if (r < nrows) st_e4(a.g_e + (row0 + r) * HH + j * 4, v);
         }
 #pragma unroll
         for (int i = 0; i < NP; ++i) Rg.v[i] = Re.v[i];
@@ -248,30 +250,41 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
     if (warp == 0) tmem_dealloc(tmem_base_s, 512);
 }
 
+template <typename T>
+static int launch_upd_bwd_umma_t(int64_t E, const T* g_out, const T* h, const T* e, const int32_t* src, const int32_t* dst,
+                                 const float* W1, const float* W2, float alpha, float beta, T* g_e, float* gP, float* gQ,
+                                 float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part,
+                                 const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st, float* gh_out) {
+    UpdBwdUArgs<T> a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, g_eid, e_eid, gh_out};
+    const size_t smem = 8 * dual::RG_T::BYTES + 4 * WT::BYTES + 1024;
+    auto kern = edge_update_bwd_umma_kernel<T>;
+    B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const uint32_t fl = wgrad_flush_edges() / 64;          // tiles (64 edges) between drains
+    kern<<<(n_part + 1) / 2, NTB, smem, st>>>(a, n_part, fl < 1 ? 1 : fl);   // two 64-edge pipelines (partial rows) per CTA
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}
+
 int launch_upd_bwd_umma(int64_t E, const float* g_out, const float* h, const float* e, const int32_t* src, const int32_t* dst,
                         const float* W1, const float* W2, float alpha, float beta, float* g_e, float* gP, float* gQ,
                         float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part,
                         const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st, float* gh_out) {
-    UpdBwdUArgs a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, g_eid, e_eid, gh_out};
-    const size_t smem = 8 * dual::RG_T::BYTES + 4 * WT::BYTES + 1024;
-    B200MP_CUDA(cudaFuncSetAttribute(edge_update_bwd_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const uint32_t fl = wgrad_flush_edges() / 64;          // tiles (64 edges) between drains
-    edge_update_bwd_umma_kernel<<<(n_part + 1) / 2, NTB, smem, st>>>(a, n_part, fl < 1 ? 1 : fl);   // two 64-edge pipelines (partial rows) per CTA
-    B200MP_LAUNCH_CHECK();
-    return 0;
+    return launch_upd_bwd_umma_t<float>(E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part,
+                                        n_part, g_eid, e_eid, st, gh_out);
 }
 
 // ------------------------------------------------------------------ message backward
 //   G (per edge, from the saved message m and per-node coefficient rows; edge_bwd.cu has the rules)
 //   g_e = G W        ACC (data GEMM, tmem cols  0.. 63)        gT1[nbr] += G   (vector REDs)
 //   gW  = G^T e      GW  (wgrad,     tmem cols 64..127)        gb = sum_k G
+template <typename T>
 struct MsgBwdUArgs {
     int64_t E;
-    const float* m; const float* e; const int32_t* eid;
+    const T* m; const T* e; const int32_t* eid;
     const float* node_in; const int32_t* seg; const int32_t* nbr;
-    const float* W; float* g_e; int accumulate; float* gT1;
+    const float* W; T* g_e; int accumulate; float* gT1;
     float* gW_part; float* gb_part;
-    const float* g_acc;                               // optional [E,H] in segment order added to g_e
+    const T* g_acc;                                   // optional [E,H] in segment order added to g_e
     float* G_out;                                     // optional [E,H] (segment order): per-edge gradient rows G
 };
 
@@ -286,8 +299,8 @@ __device__ __forceinline__ float pna_g(float m, float c0, float c1, float gmn, f
     return fmaf(c1, m - mu, c0) + (m == mn ? gmn : 0.f) + (m == mx ? gmx : 0.f);
 }
 
-template <int KIND>
-__global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a, uint32_t FLUSH_M) {
+template <int KIND, typename T>
+__global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs<T> a, uint32_t FLUSH_M) {
     constexpr int NTH = NTB, CW = CWB, NP = NPB;
     extern __shared__ __align__(128) float smem_raw[];
     float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;   // keeps the shared address space
@@ -398,12 +411,12 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a,
         if (a.accumulate) {
 #pragma unroll
             for (int i = 0; i < NP; ++i)
-                if (g * NP + i < nrows) prev[i] = *reinterpret_cast<const float4*>(a.g_e + orow[i] * HH + j * 4);
+                if (g * NP + i < nrows) prev[i] = ld_e4(a.g_e + orow[i] * HH + j * 4);
         }
         if (a.g_acc) {
 #pragma unroll
             for (int i = 0; i < NP; ++i)
-                if (g * NP + i < nrows) prev[i] = prev[i] + ldg4(a.g_acc + (row0 + g * NP + i) * HH + j * 4);
+                if (g * NP + i < nrows) prev[i] = prev[i] + ldg_e4(a.g_acc + (row0 + g * NP + i) * HH + j * 4);
         }
         if (tile + gridDim.x < ntiles) prefetch(tile + gridDim.x);    // next tile's m, e and ids in flight
         mbar_wait(&sync.bar[0], it & 1);
@@ -417,7 +430,7 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a,
             const int r = g * NP + i;
             float4 v = lds4(stage + stage_off(r, j));
             v = v + prev[i];
-            if (r < nrows) st4(a.g_e + orow[i] * HH + j * 4, v);
+            if (r < nrows) st_e4(a.g_e + orow[i] * HH + j * 4, v);
         }
         if ((it % FLUSH_M) == FLUSH_M - 1)                // drain the weight-gradient accumulator
             store_wgrad_partial(T_GW, a.gW_part + (int64_t)blockIdx.x * HH * HH, 1.f, true, tid, it >= FLUSH_M);
@@ -434,12 +447,13 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs a,
     if (warp == 0) tmem_dealloc(tm, 128);
 }
 
-int launch_msg_bwd_umma(int kind, int64_t E, const float* m, const float* e, const int32_t* eid, const float* node_in,
-                        const int32_t* seg, const int32_t* nbr, const float* W, float* g_e, int accumulate, float* gT1,
-                        float* gW_part, float* gb_part, int n_part, const float* g_acc, cudaStream_t st, float* G_out) {
-    MsgBwdUArgs a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, g_acc, G_out};
+template <typename T>
+static int launch_msg_bwd_umma_t(int kind, int64_t E, const T* m, const T* e, const int32_t* eid, const float* node_in,
+                                 const int32_t* seg, const int32_t* nbr, const float* W, T* g_e, int accumulate, float* gT1,
+                                 float* gW_part, float* gb_part, int n_part, const T* g_acc, cudaStream_t st, float* G_out) {
+    MsgBwdUArgs<T> a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, g_acc, G_out};
     const size_t smem = 4 * RT::BYTES + 2 * WT::BYTES + 1024;
-    auto kern = kind == 0 ? message_bwd_umma_kernel<0> : message_bwd_umma_kernel<1>;
+    auto kern = kind == 0 ? message_bwd_umma_kernel<0, T> : message_bwd_umma_kernel<1, T>;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const uint32_t fl = wgrad_flush_edges() / TE;
     kern<<<n_part, NTB, smem, st>>>(a, fl < 1 ? 1 : fl);
@@ -447,4 +461,33 @@ int launch_msg_bwd_umma(int kind, int64_t E, const float* m, const float* e, con
     return 0;
 }
 
+int launch_msg_bwd_umma(int kind, int64_t E, const float* m, const float* e, const int32_t* eid, const float* node_in,
+                        const int32_t* seg, const int32_t* nbr, const float* W, float* g_e, int accumulate, float* gT1,
+                        float* gW_part, float* gb_part, int n_part, const float* g_acc, cudaStream_t st, float* G_out) {
+    return launch_msg_bwd_umma_t<float>(kind, E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, n_part, g_acc, st, G_out);
+}
+
 }  // namespace b200mp
+
+/* bf16 STORAGE of the [E,64] tensors (m, e, g_e, g_acc / g_out, h), fp32 node tables / weights / partials; tensor-core path only */
+extern "C" int b200mp_message_bwd_bf16(int kind, int64_t E, const void* m, const void* e, const int32_t* eid, const float* node_in,
+                                       const int32_t* seg, const int32_t* nbr, const float* W, void* g_e, int accumulate, float* gT1,
+                                       float* gW_part, float* gb_part, int n_part, const void* g_acc, void* stream) {
+    using namespace b200mp;
+    if (E < 0 || n_part <= 0 || !W || !gW_part || !gb_part || (kind != 0 && kind != 1)) return B200MP_EINVAL;
+    if (E > 0 && (!g_e || !m || !e || !node_in || !seg || (gT1 && !nbr))) return B200MP_EINVAL;
+    return launch_msg_bwd_umma_t<ue::bf16>(kind, E, (const ue::bf16*)m, (const ue::bf16*)e, eid, node_in, seg, nbr, W, (ue::bf16*)g_e, accumulate,
+                                           gT1, gW_part, gb_part, n_part, (const ue::bf16*)g_acc, (cudaStream_t)stream, nullptr);
+}
+
+extern "C" int b200mp_edge_update_bwd_bf16(int64_t E, const void* g_out, const void* h, const void* e, const int32_t* src,
+                                           const int32_t* dst, const float* W1, const float* W2, float alpha, float beta, void* g_e,
+                                           float* gP, float* gQ, float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part,
+                                           int n_part, const int32_t* g_eid, const int32_t* e_eid, void* stream) {
+    using namespace b200mp;
+    if (E < 0 || n_part <= 0 || !W1 || !W2 || !gW1_part || !gb1_part || !gW2_part || !gb2_part) return B200MP_EINVAL;
+    if (E > 0 && (!g_e || !g_out || !h || !e || !dst || (gP && !src))) return B200MP_EINVAL;
+    return launch_upd_bwd_umma_t<ue::bf16>(E, (const ue::bf16*)g_out, (const ue::bf16*)h, (const ue::bf16*)e, src, dst, W1, W2, alpha, beta,
+                                           (ue::bf16*)g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, n_part, g_eid, e_eid,
+                                           (cudaStream_t)stream, nullptr);
+}

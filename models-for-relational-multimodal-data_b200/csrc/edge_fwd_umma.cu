@@ -12,15 +12,16 @@
 namespace b200mp {
 using namespace ue;
 
+template <typename T>                   // T: storage type of the [E,H] tensors (float | bf16)
 struct EdgeFwdUArgs {
     int64_t E;
-    const float* e; const int32_t* eid;
+    const T* e; const int32_t* eid;
     const float* W1; const float* b1;
     const float* T1; const int32_t* idx1;
     const float* T2; const int32_t* idx2;
     const float* W2; const float* b2;
     float alpha, beta;
-    float* out1; float* out2; const int32_t* out_eid;
+    T* out1; T* out2; const int32_t* out_eid;
 };
 
 // threads per CTA: the message modes fit two CTAs of 256 per SM; the update's tiles fill shared
@@ -32,8 +33,8 @@ template <int MODE> struct FwdCfg { static constexpr int NTH = MODE == 2 ? 512 :
 // everything that touches global memory -- e rows, gathered node rows, h / e' / m rows -- runs in
 // the coalesced mapping (thread (g, j): 16-byte chunk j of NP adjacent rows), with the gathered
 // rows and the residual e rows kept in registers instead of shared memory.
-template <int MODE>
-__global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_kernel(EdgeFwdUArgs a) {
+template <int MODE, typename T>
+__global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_kernel(EdgeFwdUArgs<T> a) {
     constexpr int NTH = FwdCfg<MODE>::NTH;
     constexpr int CW = HH / (NTH / TE);       // accumulator columns per tensor-memory thread
     constexpr int NP = RowRegs<NTH>::NP;
@@ -129,7 +130,7 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
             const int r = g * NP + i;
             float4 v = lds4(stage + stage_off(r, j)) + bias1 + G.v[i];
             if (MODE >= 1) v = relu4(v);
-            if (r < nrows) st4(a.out1 + (row0 + r) * HH + j * 4, v);
+            if (r < nrows) st_e4(a.out1 + (row0 + r) * HH + j * 4, v);
             if (MODE == 2) {                 // h -> MMA operand (the e tile is dead: its MMAs are done)
                 float4 hh, hl;
                 split4(r < nrows ? v : f4(0.f, 0.f, 0.f, 0.f), hh, hl);
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
             for (int i = 0; i < NP; ++i) {
                 const int r = g * NP + i;
                 const float4 v = a.alpha * R.v[i] + a.beta * (lds4(stage + stage_off(r, j)) + bias2);
-                if (r < nrows) st4(a.out2 + orow[i] * HH + j * 4, v);
+                if (r < nrows) st_e4(a.out2 + orow[i] * HH + j * 4, v);
             }
 #pragma unroll
             for (int i = 0; i < NP; ++i) R.v[i] = Rn.v[i];
@@ -190,7 +191,8 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
 // Shared memory: two e / h operand sets (4 x 32 KB), staging tile (32 KB), weights (64 KB) = 224 KB, one CTA per SM.
 // The residual rows e[row(k)] are re-read (L2) behind MMA2 instead of being held in registers for a whole iteration:
 // the register budget (512 threads x 128) has room for four row sets -- prefetch, residual, two gathered tables.
-__global__ void __launch_bounds__(512, 1) edge_update_fwd_pipe_kernel(EdgeFwdUArgs a) {
+template <typename T>
+__global__ void __launch_bounds__(512, 1) edge_update_fwd_pipe_kernel(EdgeFwdUArgs<T> a) {
     constexpr int NTH = 512;
     constexpr int CW = HH / (NTH / TE);
     constexpr int NP = RowRegs<NTH>::NP;
@@ -271,7 +273,7 @@ __global__ void __launch_bounds__(512, 1) edge_update_fwd_pipe_kernel(EdgeFwdUAr
         for (int i = 0; i < NP; ++i) {
             const int r = g * NP + i;
             float4 v = relu4(lds4(ST + stage_off(r, j)) + bias1 + (G.v[i] + G2.v[i]));
-            if (r < nrows) st4(a.out1 + (row0 + r) * HH + j * 4, v);
+            if (r < nrows) st_e4(a.out1 + (row0 + r) * HH + j * 4, v);
             float4 hh, hl;
             split4(r < nrows ? v : f4(0.f, 0.f, 0.f, 0.f), hh, hl);
             const int o = RT::off(r, j);
@@ -320,7 +322,7 @@ __global__ void __launch_bounds__(512, 1) edge_update_fwd_pipe_kernel(EdgeFwdUAr
         for (int i = 0; i < NP; ++i) {
             const int r = g * NP + i;
             const float4 v = a.alpha * Rr.v[i] + a.beta * (lds4(ST + stage_off(r, j)) + bias2);
-            if (r < nrows) st4(a.out2 + orow[i] * HH + j * 4, v);
+            if (r < nrows) st_e4(a.out2 + orow[i] * HH + j * 4, v);
         }
         __syncthreads();                      // the staging tile is free for the next iteration's Z rows
     }
@@ -329,20 +331,22 @@ __global__ void __launch_bounds__(512, 1) edge_update_fwd_pipe_kernel(EdgeFwdUAr
     if (warp == 0) tmem_dealloc(tm, 128);
 }
 
-static int launch_update_fwd_pipe(const EdgeFwdUArgs& a, cudaStream_t st) {
+template <typename T>
+static int launch_update_fwd_pipe(const EdgeFwdUArgs<T>& a, cudaStream_t st) {
     const size_t smem = 5 * RT::BYTES + 4 * WT::BYTES + 1024;
-    B200MP_CUDA(cudaFuncSetAttribute(edge_update_fwd_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    auto kern = edge_update_fwd_pipe_kernel<T>;
+    B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ntiles = (a.E + TE - 1) / TE;
-    int grid = persistent_grid((const void*)edge_update_fwd_pipe_kernel, smem, ntiles, 512);
-    edge_update_fwd_pipe_kernel<<<grid, 512, smem, st>>>(a);
+    int grid = persistent_grid((const void*)kern, smem, ntiles, 512);
+    kern<<<grid, 512, smem, st>>>(a);
     B200MP_LAUNCH_CHECK();
     return 0;
 }
 
-template <int MODE>
-static int launch_fwd_umma_mode(const EdgeFwdUArgs& a, cudaStream_t st) {
+template <int MODE, typename T>
+static int launch_fwd_umma_mode(const EdgeFwdUArgs<T>& a, cudaStream_t st) {
     const size_t smem = (MODE == 2 ? 3 * RT::BYTES + 4 * WT::BYTES : 2 * RT::BYTES + 2 * WT::BYTES) + 1024;
-    auto kern = edge_linear_fwd_umma_kernel<MODE>;
+    auto kern = edge_linear_fwd_umma_kernel<MODE, T>;
     constexpr int NTH = FwdCfg<MODE>::NTH;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ntiles = (a.E + TE - 1) / TE;
@@ -352,23 +356,44 @@ static int launch_fwd_umma_mode(const EdgeFwdUArgs& a, cudaStream_t st) {
     return 0;
 }
 
-int launch_edge_fwd_umma(int mode, int64_t E, const float* e, const int32_t* eid, const float* W1, const float* b1,
-                         const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
-                         const float* W2, const float* b2, float alpha, float beta, float* out1, float* out2,
-                         const int32_t* out_eid, cudaStream_t st) {
-    EdgeFwdUArgs a{E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2, out_eid};
+template <typename T>
+static int launch_edge_fwd_umma_t(int mode, int64_t E, const T* e, const int32_t* eid, const float* W1, const float* b1,
+                                  const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
+                                  const float* W2, const float* b2, float alpha, float beta, T* out1, T* out2,
+                                  const int32_t* out_eid, cudaStream_t st) {
+    EdgeFwdUArgs<T> a{E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2, out_eid};
     switch (mode) {
-        case 0: return launch_fwd_umma_mode<0>(a, st);
-        case 1: return launch_fwd_umma_mode<1>(a, st);
+        case 0: return launch_fwd_umma_mode<0, T>(a, st);
+        case 1: return launch_fwd_umma_mode<1, T>(a, st);
         case 2: {
             // B200MP_UPD_PIPE=1: the software-pipelined kernel.  Opt-in: same-box A/B on B200 -- hi_small 1.63 -> 1.54 ms, but
             // hi_medium 9.80 -> 9.94 ms (the residual rows re-read behind the MMAs stop hitting L2 once 148 SMs stream 8 GB tensors)
             const char* v = getenv("B200MP_UPD_PIPE");
             const bool pipe = v && v[0] == '1';
-            return pipe ? launch_update_fwd_pipe(a, st) : launch_fwd_umma_mode<2>(a, st);
+            return pipe ? launch_update_fwd_pipe<T>(a, st) : launch_fwd_umma_mode<2, T>(a, st);
         }
     }
     return B200MP_EINVAL;
 }
 
+int launch_edge_fwd_umma(int mode, int64_t E, const float* e, const int32_t* eid, const float* W1, const float* b1,
+                         const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
+                         const float* W2, const float* b2, float alpha, float beta, float* out1, float* out2,
+                         const int32_t* out_eid, cudaStream_t st) {
+    return launch_edge_fwd_umma_t<float>(mode, E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2, out_eid, st);
+}
+
 }  // namespace b200mp
+
+/* bf16 STORAGE of the [E,64] tensors (e, out1, out2), fp32 node tables / weights / arithmetic; tensor-core path only */
+extern "C" int b200mp_edge_linear_fwd_bf16(int mode, int64_t E, const void* e, const int32_t* eid, const float* W1, const float* b1,
+                                           const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
+                                           const float* W2, const float* b2, float alpha, float beta, void* out1, void* out2,
+                                           const int32_t* out_eid, void* stream) {
+    using namespace b200mp;
+    if (E < 0 || mode < 0 || mode > 2) return B200MP_EINVAL;
+    if (E == 0) return 0;
+    if (!W1 || !b1 || !out1 || !e || (T1 && !idx1) || (T2 && !idx2) || (mode == 2 && (!W2 || !b2 || !out2))) return B200MP_EINVAL;
+    return launch_edge_fwd_umma_t<ue::bf16>(mode, E, (const ue::bf16*)e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta,
+                                            (ue::bf16*)out1, (ue::bf16*)out2, out_eid, (cudaStream_t)stream);
+}

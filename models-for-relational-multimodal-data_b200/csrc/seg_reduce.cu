@@ -8,10 +8,12 @@
 //   empty segments;  std = sqrt(clamp(E[m^2]-E[m]^2, 1e-5)) masked to 0 at <= sqrt(1e-5).
 // and GINEConv's 'add' aggregation.  Called for /root/reference/src/nn/gnn/pna.py:71-74,96 and
 // gine.py:66-70,87.
-#include "common.cuh"
+#include "umma_edge.cuh"      // ldg_e4: float | bf16 message rows
 #include <math_constants.h>
 
 namespace b200mp {
+using ue::bf16;
+using ue::ldg_e4;
 
 #ifndef SEG_MINB
 #define SEG_MINB 4
@@ -85,18 +87,18 @@ __device__ __forceinline__ void warp_merge(Acc<STATS>& a) {
 }
 
 // rows [begin, end) of m, this lane's 4 columns starting at c; rows are strided by `stride`
-template <bool STATS, int H>
-__device__ __forceinline__ void accumulate_rows(Acc<STATS>& a, const float* __restrict__ m, int64_t first, int64_t end,
+template <bool STATS, int H, typename T>
+__device__ __forceinline__ void accumulate_rows(Acc<STATS>& a, const T* __restrict__ m, int64_t first, int64_t end,
                                                 int stride, int c) {
     int64_t r = first;
     for (; r + 3 * (int64_t)stride < end; r += 4 * (int64_t)stride) {      // 4 independent loads in flight
-        float4 v0 = ldg4(m + r * H + c);
-        float4 v1 = ldg4(m + (r + stride) * H + c);
-        float4 v2 = ldg4(m + (r + 2 * (int64_t)stride) * H + c);
-        float4 v3 = ldg4(m + (r + 3 * (int64_t)stride) * H + c);
+        float4 v0 = ldg_e4(m + r * H + c);
+        float4 v1 = ldg_e4(m + (r + stride) * H + c);
+        float4 v2 = ldg_e4(m + (r + 2 * (int64_t)stride) * H + c);
+        float4 v3 = ldg_e4(m + (r + 3 * (int64_t)stride) * H + c);
         a.add(v0); a.add(v1); a.add(v2); a.add(v3);
     }
-    for (; r < end; r += stride) a.add(ldg4(m + r * H + c));
+    for (; r < end; r += stride) a.add(ldg_e4(m + r * H + c));
 }
 
 template <bool STATS, int H>
@@ -130,8 +132,8 @@ __device__ __forceinline__ void finalize_store(const Acc<STATS>& a, int64_t deg,
 }
 
 // ---- light segments: one warp per node
-template <bool STATS, int H>
-__global__ void __launch_bounds__(NT, SEG_MINB) seg_light_kernel(int64_t N, const int64_t* __restrict__ ptr, const float* __restrict__ m,
+template <bool STATS, int H, typename T>
+__global__ void __launch_bounds__(NT, SEG_MINB) seg_light_kernel(int64_t N, const int64_t* __restrict__ ptr, const T* __restrict__ m,
                                                        float* __restrict__ agg, float* __restrict__ tie, int64_t light_max) {
     constexpr int LPR = H / 4, RPW = 32 / LPR;
     const int lane = threadIdx.x & 31;
@@ -153,8 +155,8 @@ __global__ void __launch_bounds__(NT, SEG_MINB) seg_light_kernel(int64_t N, cons
 }
 
 // ---- heavy segments: one CTA per chunk -> partial [6][H] (sum, sumsq, min, cmin, max, cmax)
-template <bool STATS, int H>
-__global__ void __launch_bounds__(NT) seg_heavy_partial_kernel(const int64_t* __restrict__ ptr, const float* __restrict__ m,
+template <bool STATS, int H, typename T>
+__global__ void __launch_bounds__(NT) seg_heavy_partial_kernel(const int64_t* __restrict__ ptr, const T* __restrict__ m,
                                                                const int32_t* __restrict__ heavy_node,
                                                                const int32_t* __restrict__ chunk_heavy,
                                                                const int64_t* __restrict__ chunk_begin, int64_t chunk,
@@ -211,19 +213,19 @@ __global__ void seg_heavy_combine_kernel(const int64_t* __restrict__ ptr, const 
     finalize_store<STATS, H>(t, __ldg(ptr + node + 1) - __ldg(ptr + node), node, c, agg, tie);
 }
 
-template <bool STATS, int H>
-static int launch_reduce(int64_t N, const int64_t* ptr, const float* m, float* agg, float* tie, int64_t light_max,
+template <bool STATS, int H, typename T = float>
+static int launch_reduce(int64_t N, const int64_t* ptr, const T* m, float* agg, float* tie, int64_t light_max,
                          int64_t chunk, int64_t n_heavy, const int32_t* heavy_node, const int32_t* heavy_chunk_ptr,
                          int64_t n_chunks, const int32_t* chunk_heavy, const int64_t* chunk_begin, float* partial,
                          cudaStream_t st) {
     if (N == 0) return 0;
     const int64_t want = (N + NT / 32 - 1) / (NT / 32);
     const int grid = (int)min64(want, (int64_t)device_info().sms * 32);
-    seg_light_kernel<STATS, H><<<grid, NT, 0, st>>>(N, ptr, m, agg, tie, light_max);
+    seg_light_kernel<STATS, H, T><<<grid, NT, 0, st>>>(N, ptr, m, agg, tie, light_max);
     B200MP_LAUNCH_CHECK();
     if (n_heavy > 0) {
         if (!heavy_node || !heavy_chunk_ptr || !chunk_heavy || !chunk_begin || !partial || n_chunks <= 0) return B200MP_EINVAL;
-        seg_heavy_partial_kernel<STATS, H><<<(unsigned)n_chunks, NT, 0, st>>>(ptr, m, heavy_node, chunk_heavy, chunk_begin, chunk, partial);
+        seg_heavy_partial_kernel<STATS, H, T><<<(unsigned)n_chunks, NT, 0, st>>>(ptr, m, heavy_node, chunk_heavy, chunk_begin, chunk, partial);
         B200MP_LAUNCH_CHECK();
         seg_heavy_combine_kernel<STATS, H><<<(unsigned)n_heavy, 32, 0, st>>>(ptr, heavy_node, heavy_chunk_ptr, partial, agg, tie);
         B200MP_LAUNCH_CHECK();
@@ -250,4 +252,20 @@ extern "C" int b200mp_segment_reduce_fwd(int kind, int H, int64_t N, const int64
     }
 #undef B200MP_RED
     return B200MP_EINVAL;
+}
+
+/* the same reductions over bf16-stored messages m [E,64] (fp32 statistics and outputs) */
+extern "C" int b200mp_segment_reduce_fwd_bf16(int kind, int64_t N, const int64_t* ptr, const void* m, float* agg, float* tie,
+                                              int64_t light_max, int64_t chunk, int64_t n_heavy, const int32_t* heavy_node,
+                                              const int32_t* heavy_chunk_ptr, int64_t n_chunks, const int32_t* chunk_heavy,
+                                              const int64_t* chunk_begin, float* partial, void* stream) {
+    using namespace b200mp;
+    if (N < 0 || !ptr || !agg || (kind == 0 && !tie) || light_max < 0 || chunk <= 0 || (kind != 0 && kind != 1)) return B200MP_EINVAL;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bf16* mb = (const bf16*)m;
+    if (kind == 0)
+        return launch_reduce<true, 64, bf16>(N, ptr, mb, agg, tie, light_max, chunk, n_heavy, heavy_node, heavy_chunk_ptr, n_chunks, chunk_heavy,
+                                             chunk_begin, partial, st);
+    return launch_reduce<false, 64, bf16>(N, ptr, mb, agg, tie, light_max, chunk, n_heavy, heavy_node, heavy_chunk_ptr, n_chunks, chunk_heavy,
+                                          chunk_begin, partial, st);
 }

@@ -13,12 +13,37 @@
 // twice as much of it as 8.
 // Weights sit in shared memory for the CTA's lifetime as interleaved K-major [N x K] tiles.
 #pragma once
+#include <cuda_bf16.h>
 #include "common.cuh"
 #include "umma.cuh"
 
 namespace b200mp {
 namespace ue {
 using namespace umma;
+
+// ---- edge-tensor storage type: float, or __nv_bfloat16 (bf16 STORAGE of every [E,H] tensor, fp32 arithmetic inside the kernels:
+// BASELINE.json config 3).  Four consecutive elements <-> float4.
+using bf16 = __nv_bfloat16;
+__device__ __forceinline__ float4 ldg_e4(const float* p) { return ldg4(p); }
+__device__ __forceinline__ float4 ldg_e4(const bf16* p) {
+    const uint2 r = __ldg(reinterpret_cast<const uint2*>(p));
+    return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u), __uint_as_float(r.y << 16),
+                       __uint_as_float(r.y & 0xffff0000u));
+}
+__device__ __forceinline__ float4 ld_e4(const float* p) { return *reinterpret_cast<const float4*>(p); }      // plain (read-modify-write paths)
+__device__ __forceinline__ float4 ld_e4(const bf16* p) {
+    const uint2 r = *reinterpret_cast<const uint2*>(p);
+    return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u), __uint_as_float(r.y << 16),
+                       __uint_as_float(r.y & 0xffff0000u));
+}
+__device__ __forceinline__ void st_e4(float* p, float4 v) { st4(p, v); }
+__device__ __forceinline__ void st_e4(bf16* p, float4 v) {
+    const __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+    uint2 r;
+    r.x = *reinterpret_cast<const uint32_t*>(&a);
+    r.y = *reinterpret_cast<const uint32_t*>(&b);
+    *reinterpret_cast<uint2*>(p) = r;
+}
 
 constexpr int TE = 128;          // edges per tile = MMA M
 constexpr int HH = 64;           // hidden width these kernels are written for
@@ -68,8 +93,8 @@ struct RowRegs {
     static constexpr int NP = TE * 16 / NTH;
     float4 v[NP];
 };
-template <int NTH>
-__device__ __forceinline__ void load_rows(RowRegs<NTH>& R, const float* __restrict__ src, const int32_t* __restrict__ rowmap,
+template <int NTH, typename T>
+__device__ __forceinline__ void load_rows(RowRegs<NTH>& R, const T* __restrict__ src, const int32_t* __restrict__ rowmap,
                                           int64_t row0, int nrows, int tid) {
     constexpr int NP = RowRegs<NTH>::NP;
     const int j = tid & 15, r0 = tid >> 4;
@@ -80,7 +105,7 @@ __device__ __forceinline__ void load_rows(RowRegs<NTH>& R, const float* __restri
         rows[i] = rowmap ? (int64_t)__ldg(rowmap + row0 + rc) : row0 + rc;
     }
 #pragma unroll
-    for (int i = 0; i < NP; ++i) R.v[i] = ldg4(src + rows[i] * HH + j * 4);
+    for (int i = 0; i < NP; ++i) R.v[i] = ldg_e4(src + rows[i] * HH + j * 4);
 }
 // R = T1[i1[row]] + T2[i2[row]] (either table nullable), same thread mapping as load_rows.  The
 // row indices come from SHARED memory (staged one tile ahead): with the index loads in global
@@ -123,12 +148,12 @@ __device__ __forceinline__ void load_row_ids(RowIds<NTH>& I, const int32_t* __re
 #pragma unroll
     for (int i = 0; i < NP; ++i) I.v[i] = __ldg(rowmap + row0 + min(r0 * NP + i, nrows - 1));
 }
-template <int NTH>
-__device__ __forceinline__ void load_rows_by_id(RowRegs<NTH>& R, const float* __restrict__ src, const RowIds<NTH>& I, int tid) {
+template <int NTH, typename T>
+__device__ __forceinline__ void load_rows_by_id(RowRegs<NTH>& R, const T* __restrict__ src, const RowIds<NTH>& I, int tid) {
     constexpr int NP = RowRegs<NTH>::NP;
     const int j = tid & 15;
 #pragma unroll
-    for (int i = 0; i < NP; ++i) R.v[i] = ldg4(src + (int64_t)I.v[i] * HH + j * 4);
+    for (int i = 0; i < NP; ++i) R.v[i] = ldg_e4(src + (int64_t)I.v[i] * HH + j * 4);
 }
 template <int NTH>
 __device__ __forceinline__ void store_rows_split(const RowRegs<NTH>& R, float* hi, float* lo, int nrows, int tid) {
@@ -246,7 +271,8 @@ using RG_T = RowFmt<RG, HH>;              // 16 KB operand tile
 
 struct Rows { float4 v[NPG]; };
 __device__ __forceinline__ void group_sync(int grp) { asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "r"(NTG) : "memory"); }
-__device__ __forceinline__ void load_rows(Rows& R, const float* __restrict__ src, const int32_t* __restrict__ rowmap,
+template <typename T>
+__device__ __forceinline__ void load_rows(Rows& R, const T* __restrict__ src, const int32_t* __restrict__ rowmap,
                                           int64_t row0, int nrows, int lt) {
     const int j = lt & 15, g = lt >> 4;
     int64_t rows[NPG];
@@ -256,7 +282,7 @@ __device__ __forceinline__ void load_rows(Rows& R, const float* __restrict__ src
         rows[i] = rowmap ? (int64_t)__ldg(rowmap + row0 + rc) : row0 + rc;
     }
 #pragma unroll
-    for (int i = 0; i < NPG; ++i) R.v[i] = ldg4(src + rows[i] * HH + j * 4);
+    for (int i = 0; i < NPG; ++i) R.v[i] = ldg_e4(src + rows[i] * HH + j * 4);
 }
 __device__ __forceinline__ void store_rows_split(const Rows& R, float* hi, float* lo, int nrows, int lt) {
     const int j = lt & 15, g = lt >> 4;

@@ -66,6 +66,21 @@ def _f32c(t: torch.Tensor) -> torch.Tensor:
     return t.contiguous()
 
 
+_EDGE_DTYPES = (torch.float32, torch.bfloat16)
+
+
+def _edge_c(t: torch.Tensor) -> torch.Tensor:
+    """an [E,H] edge tensor: fp32, or bf16 STORAGE (config 3: half the bytes of the streams; arithmetic stays fp32 in the kernels)"""
+    if t.dtype not in _EDGE_DTYPES:
+        raise TypeError(f"b200mp edge tensors are stored as fp32 or bf16; got {t.dtype}")
+    return t.contiguous()
+
+
+def _bf16_ok(t: torch.Tensor):
+    if t.shape[-1] != 64 or not row_maps_available():
+        raise L.B200MPError("bf16 storage runs on the H = 64 tensor-core kernels only")
+
+
 def _H(t: torch.Tensor) -> int:
     H = t.shape[-1]
     L.tile_edges(H)      # raises for unsupported widths
@@ -89,6 +104,8 @@ class _PermuteRows(torch.autograd.Function):
 
 
 def _permute(x, idx, scatter):
+    if x.dtype != torch.float32:
+        raise TypeError("row permutation passes are fp32 only (bf16 storage uses the row-map kernels, H = 64)")
     n, H = x.shape
     if H % 4:
         raise L.B200MPError("row width must be a multiple of 4")
@@ -340,8 +357,15 @@ def linear3x(x, W, b=None):
 # ----------------------------------------------------------------------------- raw launches
 def _edge_linear_fwd(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2=None, b2=None, alpha=0.0, beta=0.0, out_eid=None):
     E, H = e.shape
-    out1 = torch.empty((E, H), dtype=torch.float32, device=e.device)
-    out2 = torch.empty((E, H), dtype=torch.float32, device=e.device) if mode == 2 else None
+    out1 = torch.empty((E, H), dtype=e.dtype, device=e.device)
+    out2 = torch.empty((E, H), dtype=e.dtype, device=e.device) if mode == 2 else None
+    if e.dtype == torch.bfloat16:
+        _bf16_ok(e)
+        with torch.cuda.device(e.device), _track(("pna_message_fwd", "gine_message_fwd", "edge_update_fwd")[mode]):
+            L.check(L.lib().b200mp_edge_linear_fwd_bf16(mode, E, L.ptr(e), L.ptr(eid), L.ptr(W1), L.ptr(b1), L.ptr(T1), L.ptr(idx1),
+                                                        L.ptr(T2), L.ptr(idx2), L.ptr(W2), L.ptr(b2), alpha, beta, L.ptr(out1),
+                                                        L.ptr(out2), L.ptr(out_eid), L.stream()), "b200mp_edge_linear_fwd_bf16")
+        return out1, out2
     with torch.cuda.device(e.device), _track(("pna_message_fwd", "gine_message_fwd", "edge_update_fwd")[mode]):
         L.check(L.lib().b200mp_edge_linear_fwd(mode, H, E, L.ptr(e), L.ptr(eid), L.ptr(W1), L.ptr(b1),
                                                L.ptr(T1), L.ptr(idx1), L.ptr(T2), L.ptr(idx2),
@@ -357,6 +381,13 @@ def _segment_reduce(kind, seg: SegmentIndex, m, H):
     tie = torch.empty((N, 2 * H), dtype=torch.float32, device=dev) if kind == 0 else None
     nh, hnode, hcptr, nc, chv, cbeg = seg.heavy()
     partial = torch.empty((nc, 6 * H), dtype=torch.float32, device=dev) if nh else None
+    if m.dtype == torch.bfloat16:
+        _bf16_ok(m)
+        with torch.cuda.device(dev), _track("segment_reduce_pna" if kind == 0 else "segment_reduce_sum", 3 if nh else 1):
+            L.check(L.lib().b200mp_segment_reduce_fwd_bf16(kind, N, L.ptr(seg.ptr), L.ptr(m), L.ptr(agg), L.ptr(tie), LIGHT_MAX, CHUNK,
+                                                           nh, L.ptr(hnode), L.ptr(hcptr), nc, L.ptr(chv), L.ptr(cbeg), L.ptr(partial),
+                                                           L.stream()), "b200mp_segment_reduce_fwd_bf16")
+        return agg, tie
     with torch.cuda.device(dev), _track("segment_reduce_pna" if kind == 0 else "segment_reduce_sum", 3 if nh else 1):
         L.check(L.lib().b200mp_segment_reduce_fwd(kind, H, N, L.ptr(seg.ptr), L.ptr(m), L.ptr(agg), L.ptr(tie),
                                                   LIGHT_MAX, CHUNK, nh, L.ptr(hnode), L.ptr(hcptr), nc, L.ptr(chv),
@@ -377,7 +408,7 @@ def _message_fwd_reduce(kind, seg: SegmentIndex, e, eid, W, b, T1, T2):
     """messages + their aggregation over the segments of ``seg``: kind 0 (PNA) m = e W^T + b + T1[nbr] + T2[seg] ->
     (m, agg [N,4H] = mean|min|max|std, tie [N,2H]); kind 1 (GINE) m = relu(e W^T + b + T1[nbr]) -> (m, agg [N,H], None)."""
     E, H = e.shape
-    if not fused_reduce_available(H):
+    if not fused_reduce_available(H) or e.dtype != torch.float32:
         m, _ = _edge_linear_fwd(kind, e, eid, W, b, T1, seg.nbr32, T2, seg.seg32 if T2 is not None else None)
         agg, tie = _segment_reduce(kind, seg, m, H)
         return m, agg, tie
@@ -461,8 +492,18 @@ def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N, g_e=None
     elif g_e is not None:
         accumulate = 1
     if g_e is None:
-        g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
+        g_e = torch.empty((E, H), dtype=m.dtype, device=dev)
     npart = L.n_part(E, H)
+    if m.dtype == torch.bfloat16:
+        _bf16_ok(m)
+        gT1 = torch.zeros((N, H), dtype=torch.float32, device=dev) if need_T1 else None
+        gW = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
+        gb = torch.empty((npart, H), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev), _track("pna_message_bwd" if kind == 0 else "gine_message_bwd"):
+            L.check(L.lib().b200mp_message_bwd_bf16(kind, E, L.ptr(m), L.ptr(e), L.ptr(eid), L.ptr(node_in), L.ptr(seg.seg32),
+                                                    L.ptr(seg.nbr32), L.ptr(W), L.ptr(g_e), accumulate, L.ptr(gT1), L.ptr(gW), L.ptr(gb),
+                                                    npart, L.ptr(g_acc), L.stream()), "b200mp_message_bwd_bf16")
+        return g_e, gT1, gW.sum(0), gb.sum(0)
     if need_T1 and E > 0 and H == 64 and row_maps_available() and deterministic_backward():
         G, gW, gb = _message_bwd_rows(kind, seg, m, e, node_in, W, g_e, accumulate, g_acc, eid, npart)
         return g_e, _sum_rows_by_neighbour(seg, G, N), gW.sum(0), gb.sum(0)
@@ -481,12 +522,22 @@ def _edge_update_bwd(st: EdgeStructure, g_out, h, e, W1, W2, alpha, beta, need_P
                      g_eid=None, e_eid=None):
     E, H = e.shape
     dev = e.device
-    g_e = torch.empty((E, H), dtype=torch.float32, device=dev)
+    g_e = torch.empty((E, H), dtype=e.dtype, device=dev)
     npart = L.n_part(E, H)
     gW1 = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
     gW2 = torch.empty((npart, H, H), dtype=torch.float32, device=dev)
     gb1 = torch.empty((npart, H), dtype=torch.float32, device=dev)
     gb2 = torch.empty((npart, H), dtype=torch.float32, device=dev)
+    if e.dtype == torch.bfloat16:
+        _bf16_ok(e)
+        gP = torch.zeros((nP or st.num_nodes, H), dtype=torch.float32, device=dev) if need_P else None
+        gQ = torch.zeros((nQ or st.num_nodes, H), dtype=torch.float32, device=dev) if need_Q else None
+        with torch.cuda.device(dev), _track("edge_update_bwd"):
+            L.check(L.lib().b200mp_edge_update_bwd_bf16(E, L.ptr(g_out), L.ptr(h), L.ptr(e), L.ptr(st.src32), L.ptr(st.dst32), L.ptr(W1),
+                                                        L.ptr(W2), alpha, beta, L.ptr(g_e), L.ptr(gP), L.ptr(gQ), L.ptr(gW1), L.ptr(gb1),
+                                                        L.ptr(gW2), L.ptr(gb2), npart, L.ptr(g_eid), L.ptr(e_eid), L.stream()),
+                    "b200mp_edge_update_bwd_bf16")
+        return g_e, gP, gQ, gW1.sum(0), gb1.sum(0), gW2.sum(0), gb2.sum(0)
     if (need_P or need_Q) and E > 0 and H == 64 and row_maps_available() and deterministic_backward():
         Gh = torch.empty((E, H), dtype=torch.float32, device=dev)
         with torch.cuda.device(dev), _track("edge_update_bwd"):
@@ -572,7 +623,8 @@ class _PNAAggregate(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, A, B, e, W, b, seg: SegmentIndex, sink=None, e_eid=None):
-        A, B, e, W, b = map(_f32c, (A, B, e, W, b))
+        A, B, W, b = map(_f32c, (A, B, W, b))
+        e = _edge_c(e)
         L.require_cuda(A, B, e, W, b)
         H = _H(e)
         m, agg, tie = _message_fwd_reduce(0, seg, e, seg.eid32 if e_eid is None else e_eid, W, b, B, A)
@@ -606,7 +658,8 @@ class _GINEAggregate(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, e, W, b, seg: SegmentIndex, sink=None, e_eid=None):
-        x, e, W, b = map(_f32c, (x, e, W, b))
+        x, W, b = map(_f32c, (x, W, b))
+        e = _edge_c(e)
         L.require_cuda(x, e, W, b)
         H = _H(e)
         m, agg, _ = _message_fwd_reduce(1, seg, e, seg.eid32 if e_eid is None else e_eid, W, b, x, None)
@@ -633,7 +686,8 @@ class _EdgeUpdate(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, P, Q, e, W1, b1, W2, b2, st: EdgeStructure, alpha, beta, sink=None, e_eid=None, out_eid=None):
-        P, Q, e, W1, b1, W2, b2 = map(_f32c, (P, Q, e, W1, b1, W2, b2))
+        P, Q, W1, b1, W2, b2 = map(_f32c, (P, Q, W1, b1, W2, b2))
+        e = _edge_c(e)
         L.require_cuda(P, Q, e, W1, b1, W2, b2)
         _H(e)
         h, out = _edge_linear_fwd(2, e, e_eid, W1, b1, P, st.src32, Q, st.dst32, W2, b2, float(alpha), float(beta), out_eid)
@@ -645,7 +699,7 @@ class _EdgeUpdate(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_out):
         h, e, W1, W2 = ctx.saved_tensors
-        g_e, gP, gQ, gW1, gb1, gW2, gb2 = _edge_update_bwd(ctx.st, _f32c(g_out), h, e, W1, W2, ctx.alpha, ctx.beta,
+        g_e, gP, gQ, gW1, gb1, gW2, gb2 = _edge_update_bwd(ctx.st, _edge_c(g_out).to(e.dtype), h, e, W1, W2, ctx.alpha, ctx.beta,
                                                            ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.nP, ctx.nQ,
                                                            ctx.out_eid, ctx.e_eid)
         if ctx.sink is not None and ctx.needs_input_grad[2]:

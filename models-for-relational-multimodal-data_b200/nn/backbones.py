@@ -68,12 +68,30 @@ def _conv_sorted(conv, x, st: EdgeStructure, e, sink=None):
     return conv.forward_sorted(x, st.fwd, e, sink=sink)
 
 
-class _Backbone(nn.Module):
+class _EdgeStorage:
+    """bf16 STORAGE of the [E,H] edge tensors inside the layer loop (BASELINE.json config 3): ``model.set_edge_storage(torch.bfloat16)``.
+    Node tensors, parameters and all arithmetic stay fp32; the embedded edge features are rounded to bf16 once, every edge tensor
+    produced inside (messages, hidden rows, updated features, their gradients) is stored as bf16, and the model returns the updated
+    edge features in that dtype.  H = 64 (tensor-core kernels) only."""
+    edge_dtype = torch.float32
+
+    def set_edge_storage(self, dtype):
+        if dtype not in (torch.float32, torch.bfloat16):
+            raise ValueError("edge storage is torch.float32 or torch.bfloat16")
+        self.edge_dtype = dtype
+        return self
+
+    def _store(self, e):
+        return e if e.dtype == self.edge_dtype else e.to(self.edge_dtype)
+
+
+class _Backbone(_EdgeStorage, nn.Module):
     """Shared layer loop of gine.py:86-89 / pna.py:95-99."""
 
     def _layers(self, x, edge_index, e):
         st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
         H = x.shape[1]
+        e = self._store(e)
         if self.reverse_mp or H != 64 or not BF.row_maps_available():
             return self._layers_permuted(x, st, e)
         # e stays in the caller's edge order at both ends: the first layer's kernels read it through
@@ -106,7 +124,7 @@ class _Backbone(nn.Module):
         from .. import parallel as PL
         if self.reverse_mp:
             raise NotImplementedError("reverse_mp is not supported on a partitioned graph")
-        st, x, e = part.st, x_local, e_local
+        st, x, e = part.st, x_local, self._store(e_local)
         gather = lambda t: PL.all_gather_rows(t, part)
         for i in range(self.num_gnn_layers):
             sink = BF.EdgeGradSink() if (self.edge_updates and e.requires_grad and torch.is_grad_enabled()) else None

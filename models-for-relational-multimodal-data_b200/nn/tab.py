@@ -21,7 +21,7 @@ from torch import Tensor, nn
 
 from .. import functional as BF
 from ..graph import EdgeStructure, edge_structure
-from .backbones import PNAConvHetero
+from .backbones import PNAConvHetero, _EdgeStorage
 from .conv import BatchNorm, PNAConv, edge_update_sorted
 
 _AGGR = ['mean', 'max', 'min', 'std']
@@ -141,7 +141,7 @@ class PNALayer(_GraphStep):
         return x, BF.scatter_rows(e, st.fwd.perm)
 
 
-class TABGNN(_SharedParams, nn.Module):
+class TABGNN(_EdgeStorage, _SharedParams, nn.Module):
     def __init__(self, channels: int, num_layers: int, deg=None, node_dim: int = 1, nhidden: int = 128,
                  edge_dim: int = None, reverse_mp: bool = False, feedforward_channels: Optional[int] = None,
                  nhead: int = 8, dropout: float = 0.5, activation: str = 'relu') -> None:
@@ -178,7 +178,7 @@ class TABGNN(_SharedParams, nn.Module):
         for layer in self.tabular_backbone:          # the same layer serves node and edge tokens
             tx, te = layer(tx), layer(te)
         x = self.node_emb(((x + tx) / 2).reshape(x.shape[0], -1))
-        e = self.edge_emb(((e + te) / 2).reshape(e.shape[0], -1))
+        e = self._store(self.edge_emb(((e + te) / 2).reshape(e.shape[0], -1)))
         st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
         if not self.reverse_mp and x.shape[1] == 64 and BF.row_maps_available():
             # e stays in the caller's order at both ends: first layer reads / last layer writes through the CSC permutation
@@ -201,7 +201,7 @@ class TABGNN(_SharedParams, nn.Module):
         for layer in self.tabular_backbone:
             tx, te = layer(tx), layer(te)
         x = self.node_emb(((x + tx) / 2).reshape(x.shape[0], -1))
-        e = self.edge_emb(((e + te) / 2).reshape(e.shape[0], -1))
+        e = self._store(self.edge_emb(((e + te) / 2).reshape(e.shape[0], -1)))
         for layer in self.gnn_backbone:
             x, e = layer.forward_sorted(x, None, e, part)
         return x, e

@@ -331,7 +331,34 @@ def node_wgrad(x, y):
     return x.t() @ y
 
 
+def _with_storage(fn, edge_args, edge_outs):
+    """bf16-stored edge tensors: compute in fp32, round the edge-shaped results to the storage dtype (what the kernels do)"""
+    def wrapped(*args, **kw):
+        args, dt = list(args), None
+        for i in edge_args:
+            if i < len(args) and torch.is_tensor(args[i]) and args[i].dtype == torch.bfloat16:
+                dt, args[i] = torch.bfloat16, args[i].float()
+        for k in ("g_e",):
+            if torch.is_tensor(kw.get(k)) and kw[k].dtype == torch.bfloat16:
+                dt, kw[k] = torch.bfloat16, kw[k].float()
+        out = fn(*args, **kw)
+        if dt is None:
+            return out
+        out = list(out)
+        for i in edge_outs:
+            if out[i] is not None:
+                out[i] = out[i].to(dt)
+        return tuple(out)
+    return wrapped
+
+
+edge_linear_fwd = _with_storage(edge_linear_fwd, (1,), (0, 1))
+segment_reduce = _with_storage(segment_reduce, (2,), ())
+message_bwd = _with_storage(message_bwd, (2, 3, 8), (0,))
+edge_update_bwd = _with_storage(edge_update_bwd, (1, 2, 3), (0,))
+
 _PATCHES = [
+    (BF, "_bf16_ok", lambda t: None),
     (BF, "fused_reduce_available", lambda H: False),          # the fused kernel's two halves are emulated separately
     (BF, "_node_linear64", node_linear64),
     (BF, "_node_pair_wgrad", node_pair_wgrad),
