@@ -90,7 +90,7 @@ __device__ __forceinline__ void cta_column_sums(float* red, float4 acc, float* _
 
 // (namespace dual -- the two-pipelines-per-CTA helpers -- lives in umma_edge.cuh: the update forward uses it too)
 
-template <typename T>
+template <typename T, bool ROWS>          // ROWS: write the Gh rows (atomic-free node gradients) instead of scattering them
 __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArgs<T> a, int n_virtual, uint32_t FLUSH_U) {
     using namespace dual;
     constexpr int NP = NPG;
@@ -182,15 +182,15 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
                            valid && hv.z > 0.f ? a.beta * u.z : 0.f, valid && hv.w > 0.f ? a.beta * u.w : 0.f);
                 accb1 = accb1 + Gh[i];
                 if (valid) accb2 = accb2 + Rg.v[i];
-                if (valid && a.gP) red_add4(a.gP + (int64_t)srow[i] * HH + j * 4, Gh[i]);
-                if (valid && a.gh_out) st4(a.gh_out + (row0 + r) * HH + j * 4, Gh[i]);
+                if (!ROWS && valid && a.gP) red_add4(a.gP + (int64_t)srow[i] * HH + j * 4, Gh[i]);
+                if (ROWS && valid) st4(a.gh_out + (row0 + r) * HH + j * 4, Gh[i]);
                 float4 gh, gl;
                 split4(Gh[i], gh, gl);
                 const int o = RG_T::off(r, j);
                 st4(H_hi + o, gh);
                 st4(H_lo + o, gl);
             }
-            if (a.gQ) red_runs(a.gQ, drow, Gh, j, lane);
+            if (!ROWS && a.gQ) red_runs(a.gQ, drow, Gh, j, lane);
         }
         group_sync(grp);                                 // every thread is done reading the staged U rows
         store_rows_split(Re, G_hi, G_lo, nrows, lt);     // e tile replaces them
@@ -257,7 +257,7 @@ static int launch_upd_bwd_umma_t(int64_t E, const T* g_out, const T* h, const T*
                                  const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st, float* gh_out) {
     UpdBwdUArgs<T> a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, g_eid, e_eid, gh_out};
     const size_t smem = 8 * dual::RG_T::BYTES + 4 * WT::BYTES + 1024;
-    auto kern = edge_update_bwd_umma_kernel<T>;
+    auto kern = gh_out ? edge_update_bwd_umma_kernel<T, true> : edge_update_bwd_umma_kernel<T, false>;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const uint32_t fl = wgrad_flush_edges() / 64;          // tiles (64 edges) between drains
     kern<<<(n_part + 1) / 2, NTB, smem, st>>>(a, n_part, fl < 1 ? 1 : fl);   // two 64-edge pipelines (partial rows) per CTA
@@ -299,7 +299,7 @@ __device__ __forceinline__ float pna_g(float m, float c0, float c1, float gmn, f
     return fmaf(c1, m - mu, c0) + (m == mn ? gmn : 0.f) + (m == mx ? gmx : 0.f);
 }
 
-template <int KIND, typename T>
+template <int KIND, typename T, bool ROWS>
 __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs<T> a, uint32_t FLUSH_M) {
     constexpr int NTH = NTB, CW = CWB, NP = NPB;
     extern __shared__ __align__(128) float smem_raw[];
@@ -376,8 +376,8 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs<T>
                     G = f4(mv.x > 0.f ? ga.x : 0.f, mv.y > 0.f ? ga.y : 0.f, mv.z > 0.f ? ga.z : 0.f, mv.w > 0.f ? ga.w : 0.f);
                 }
                 if (r >= nrows) G = f4(0.f, 0.f, 0.f, 0.f);
-                if (r < nrows && a.gT1) red_add4(a.gT1 + (int64_t)nbr_pf[i] * HH + j * 4, G);
-                if (r < nrows && a.G_out) st4(a.G_out + (row0 + r) * HH + j * 4, G);
+                if (!ROWS && r < nrows && a.gT1) red_add4(a.gT1 + (int64_t)nbr_pf[i] * HH + j * 4, G);
+                if (ROWS && r < nrows) st4(a.G_out + (row0 + r) * HH + j * 4, G);
                 accb = accb + G;
                 Gv[i] = G;
             }
@@ -453,7 +453,8 @@ static int launch_msg_bwd_umma_t(int kind, int64_t E, const T* m, const T* e, co
                                  float* gW_part, float* gb_part, int n_part, const T* g_acc, cudaStream_t st, float* G_out) {
     MsgBwdUArgs<T> a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, g_acc, G_out};
     const size_t smem = 4 * RT::BYTES + 2 * WT::BYTES + 1024;
-    auto kern = kind == 0 ? message_bwd_umma_kernel<0, T> : message_bwd_umma_kernel<1, T>;
+    auto kern = G_out ? (kind == 0 ? message_bwd_umma_kernel<0, T, true> : message_bwd_umma_kernel<1, T, true>)
+                      : (kind == 0 ? message_bwd_umma_kernel<0, T, false> : message_bwd_umma_kernel<1, T, false>);
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const uint32_t fl = wgrad_flush_edges() / TE;
     kern<<<n_part, NTB, smem, st>>>(a, fl < 1 ? 1 : fl);
