@@ -31,7 +31,7 @@ def _case(kind, n, e, seed):
 def _run(m, ei, x, ea, wx, we, dtype, device):
     m.set_edge_storage(dtype)
     m.zero_grad(set_to_none=True)
-    xi, ei2 = x.to(device).requires_grad_(True), ea.to(device).requires_grad_(True)
+    xi, ei2 = x.detach().clone().to(device).requires_grad_(True), ea.detach().clone().to(device).requires_grad_(True)
     ox, oe = m.message_passing(xi, ei.to(device), ei2)
     assert oe.dtype == dtype and ox.dtype == torch.float32
     ((ox * wx.to(device)).sum() + (oe.float() * we.to(device)).sum()).backward()
