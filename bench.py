@@ -471,6 +471,35 @@ def run_b200(args, rank, world, local_rank):
     checksum = step(keep=True)
     torch.cuda.synchronize()
 
+    # whole model ("report whole-model numbers separately"): node_emb / edge_emb included, N = 1, f32 line only
+    whole = None
+    if part is None and not tab and not bf16 and not args.no_e2e:
+        try:
+            xw = x.detach().clone().requires_grad_(True)
+            ew = ea.detach().clone().requires_grad_(True)
+
+            def full_step():
+                ox, oe = model(xw, ei, ew.view(e, 1, H))
+                torch.autograd.backward([ox, oe], [gx, ge])
+                xw.grad = None
+                ew.grad = None
+                model.zero_grad(set_to_none=True)
+
+            full_step()
+            w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            nw = max(1, min(args.steps, 3))
+            w0.record()
+            for _ in range(nw):
+                full_step()
+            w1.record()
+            torch.cuda.synchronize()
+            wms = w0.elapsed_time(w1) / nw
+            whole = {"ms_per_step": wms, "value": e / (wms * 1e-3), "unit": "edges/s",
+                     "includes": "node_emb and edge_emb (64 -> 64 linears over the N / E rows, fwd + bwd) around the timed layer loop"}
+            del xw, ew
+        except Exception as ex:
+            whole = {"error": f"{type(ex).__name__}: {ex}"[:200]}
+
     # per-kernel accounting -> roofline of the dominant kernel
     summ = stats.summary()
     peak, peak_src = measured_peak_gbs()
@@ -586,7 +615,7 @@ def run_b200(args, rank, world, local_rank):
         "vs_baseline": None, "dtype": "bf16 storage of the [E,H] tensors, fp32 arithmetic (extra line)" if bf16 else "f32", "data": "synthetic",
         "config": workload_config(args, world),
         "clocks": clk, "e2e": e2e, "gpu_launches": stats.launches, "roofline": roofline, "step_roofline": step_roofline,
-        "kernels": kern, "cpu_baseline": cpu,
+        "kernels": kern, "cpu_baseline": cpu, "whole_model": whole,
     }
     print(json.dumps(line), flush=True)
 
