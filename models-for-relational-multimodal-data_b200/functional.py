@@ -1227,12 +1227,15 @@ class _RowChunked(torch.autograd.Function):
         ctx.fn, ctx.chunk_rows = fn, int(chunk_rows)
         ctx.save_for_backward(x, *params)
         ctx.rng = []
-        outs = []
+        out = None
         with torch.no_grad():
             for r0 in range(0, x.shape[0], ctx.chunk_rows):
                 ctx.rng.append(torch.get_rng_state())
-                outs.append(fn(x[r0:r0 + ctx.chunk_rows]))
-        return torch.cat(outs, dim=0) if len(outs) != 1 else outs[0]
+                yc = fn(x[r0:r0 + ctx.chunk_rows])
+                if out is None:                        # chunks land in place: no concatenation pass over the whole tensor
+                    out = torch.empty((x.shape[0], *yc.shape[1:]), dtype=yc.dtype, device=yc.device)
+                out[r0:r0 + yc.shape[0]] = yc
+        return out
 
     @staticmethod
     def backward(ctx, g):
