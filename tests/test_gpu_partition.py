@@ -23,7 +23,7 @@ def _worker(rank, world, port, kind):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("kind", ["pna", "gine"])
+@pytest.mark.parametrize("kind", ["pna", "gine", "tabgnn"])
 def test_partition_nccl(kind):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
