@@ -348,6 +348,52 @@ def linear_group(x, weights, biases):
     return _LinearGroup.apply(x, len(weights), *weights, *biases)
 
 
+class _LinearCat(torch.autograd.Function):
+    """y = [x_0 | x_1 | x_2] W^T + b for [N,64] blocks WITHOUT building the concatenation (the `lin` of the reverse-message-passing
+    convs over [x, a_in, a_out]: gine.py:35, pna.py:46): one pass of the tcgen05 node kernel with the blocks as K segments; backward =
+    the split-output form of the same kernel for the data gradients, pair weight-gradient kernels for g^T x_i."""
+
+    @staticmethod
+    def forward(ctx, W, b, *xs):
+        xs = tuple(_f32c(x) for x in xs)
+        W = _f32c(W)
+        L.require_cuda(W, *xs)
+        ctx.n = len(xs)
+        ctx.has_bias = b is not None
+        ctx.save_for_backward(W, *xs)
+        return _node_linear64(list(xs), W, None if b is None else _f32c(b), False)
+
+    @staticmethod
+    def backward(ctx, g):
+        W, *xs = ctx.saved_tensors
+        g = _f32c(g)
+        n = ctx.n
+        gxs = [None] * n
+        if any(ctx.needs_input_grad[2:]):
+            Wt = torch.cat([W[:, 64 * i:64 * (i + 1)].t() for i in range(n)], 0)          # y_i = g W_i
+            gxs = _node_linear64([g], Wt, None, True)
+        gW = None
+        if ctx.needs_input_grad[0]:
+            parts = []
+            for k in range(0, n, 2):
+                a, bb = _node_pair_wgrad(xs[k], xs[min(k + 1, n - 1)], g)                  # (x_k^T g, x_k+1^T g)
+                parts.append(a.t())
+                if k + 1 < n:
+                    parts.append(bb.t())
+            gW = torch.cat(parts, 1)
+        gb = g.sum(0) if (ctx.has_bias and ctx.needs_input_grad[1]) else None
+        return (gW, gb, *[gx if need else None for gx, need in zip(gxs, ctx.needs_input_grad[2:])])
+
+
+def linear_cat(xs, W, b=None):
+    """``F.linear(torch.cat(xs, 1), W, b)`` for up to three [N,64] blocks; N >= 4096 runs on the node kernel without the concatenation"""
+    xs = list(xs)
+    if 1 <= len(xs) <= 3 and all(x.dim() == 2 and x.shape[1] == 64 and x.dtype == torch.float32 for x in xs) and xs[0].shape[0] >= 4096 \
+            and tuple(W.shape) == (64, 64 * len(xs)):
+        return _LinearCat.apply(W, b, *xs)
+    return torch.nn.functional.linear(torch.cat(xs, dim=1), W, b)
+
+
 def linear3x(x, W, b=None):
     """torch.nn.functional.linear(x, W, b) for node-level [N, K] inputs, fp32-accurate on the
     tensor cores (three TF32 library GEMMs)."""

@@ -31,10 +31,11 @@ class GINEConvHetero(_HeteroMixin, nn.Module):
         self.conv_back = GINEConv(network, edge_dim=n_hidden)      # same `network` object, as in the reference
         self.lin = Linear(n_hidden * 3, n_hidden)
 
-    def forward_sorted(self, x, st: EdgeStructure, e, sink=None):
-        a_in = self.conv_forw.forward_sorted((x, None), st.fwd, e, sink=sink)
-        a_out = self.conv_back.forward_sorted((x, None), st.rev, e)
-        return self.lin(torch.cat([x, a_in, a_out], dim=1))
+    def forward_sorted(self, x, st: EdgeStructure, e, sink=None, e_eid=None, rev_eid=None):
+        """e_eid / rev_eid: row maps of the two convs when e is in the caller's edge order (first layer of the backbones)"""
+        a_in = self.conv_forw.forward_sorted((x, None), st.fwd, e, sink=sink, e_eid=e_eid)
+        a_out = self.conv_back.forward_sorted((x, None), st.rev, e, e_eid=rev_eid)
+        return BF.linear_cat([x, a_in, a_out], self.lin.weight, self.lin.bias)
 
     def forward(self, x, edge_index, edge_attr):
         st = edge_structure(edge_index, x.shape[0], reverse=True)
@@ -52,10 +53,10 @@ class PNAConvHetero(_HeteroMixin, nn.Module):
         self.conv_back = PNAConv(**kw)
         self.lin = Linear(n_hidden * 3, n_hidden)
 
-    def forward_sorted(self, x, st: EdgeStructure, e, sink=None):
-        a_in = self.conv_forw.forward_sorted(x, st.fwd, e, sink=sink)
-        a_out = self.conv_back.forward_sorted(x, st.rev, e)
-        return self.lin(torch.cat([x, a_in, a_out], dim=1))
+    def forward_sorted(self, x, st: EdgeStructure, e, sink=None, e_eid=None, rev_eid=None):
+        a_in = self.conv_forw.forward_sorted(x, st.fwd, e, sink=sink, e_eid=e_eid)
+        a_out = self.conv_back.forward_sorted(x, st.rev, e, e_eid=rev_eid)
+        return BF.linear_cat([x, a_in, a_out], self.lin.weight, self.lin.bias)
 
     def forward(self, x, edge_index, edge_attr):
         st = edge_structure(edge_index, x.shape[0], reverse=True)
@@ -98,18 +99,23 @@ class _Backbone(_EdgeStorage, nn.Module):
         st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
         H = x.shape[1]
         e = self._store(e)
-        if self.reverse_mp or H != 64 or not BF.row_maps_available():
+        if H != 64 or not BF.row_maps_available():
             return self._layers_permuted(x, st, e)
         # e stays in the caller's edge order at both ends: the first layer's kernels read it through
         # the CSC permutation, the last edge update writes through it -- no permutation passes
         perm32 = st.fwd.perm32()
+        rperm32 = st.rev.perm32() if self.reverse_mp else None          # reverse convs: CSR position -> caller row
         L = self.num_gnn_layers
         e_in = e
         for i in range(L):
             e_eid = perm32 if (i == 0 or not self.edge_updates) else None
             out_eid = perm32 if i == L - 1 else None
             sink = BF.EdgeGradSink() if (self.edge_updates and e.requires_grad and torch.is_grad_enabled()) else None
-            x = BF.bn_relu_residual(self.batch_norms[i].module, self.convs[i].forward_sorted(x, st.fwd, e, sink=sink, e_eid=e_eid), x)
+            if self.reverse_mp:
+                c = self.convs[i].forward_sorted(x, st, e, sink=sink, e_eid=e_eid, rev_eid=rperm32 if e_eid is not None else None)
+            else:
+                c = self.convs[i].forward_sorted(x, st.fwd, e, sink=sink, e_eid=e_eid)
+            x = BF.bn_relu_residual(self.batch_norms[i].module, c, x)
             if self.edge_updates:
                 e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, sink=sink, e_eid=e_eid, out_eid=out_eid)
         return x, (e if self.edge_updates else e_in)

@@ -70,3 +70,24 @@ def test_linear_group_matches_fp64(N):
         err = rel_err(a, t)
         print(f"linear_group N={N} {name}: rel err {err:.2e}")
         assert err < 1e-5
+
+
+@pytest.mark.parametrize("N,n", [(4096, 3), (7001, 2), (5000, 1)])
+def test_linear_cat_matches_fp64(N, n):
+    """y = [x_0 | x_1 | x_2] W^T + b without the concatenation (reverse-message-passing `lin`): values and every gradient vs fp64"""
+    g = torch.Generator(device="cuda").manual_seed(N + n)
+    xs = [torch.randn(N, 64, device="cuda", generator=g, requires_grad=True) for _ in range(n)]
+    W = (torch.randn(64, 64 * n, device="cuda", generator=g) / 8).requires_grad_(True)
+    b = torch.randn(64, device="cuda", generator=g, requires_grad=True)
+    gy = torch.randn(N, 64, device="cuda", generator=g)
+    y = BF.linear_cat(xs, W, b)
+    y.backward(gy)
+    xd = [x.detach().double().requires_grad_(True) for x in xs]
+    Wd, bd = W.detach().double().requires_grad_(True), b.detach().double().requires_grad_(True)
+    yd = torch.cat(xd, 1) @ Wd.t() + bd
+    yd.backward(gy.double())
+    pairs = [("y", y, yd), ("gW", W.grad, Wd.grad), ("gb", b.grad, bd.grad)] + [(f"gx{i}", a.grad, c.grad) for i, (a, c) in enumerate(zip(xs, xd))]
+    for name, a, t in pairs:
+        err = rel_err(a, t)
+        print(f"linear_cat N={N} n={n} {name}: rel err {err:.2e}")
+        assert err < 1e-5

@@ -130,12 +130,12 @@ def _run_case(case, model, oracle_fn, dropin_fn, ins, gin, seed):
             _check(case, f"grad.{k}", gp[k], [r[2][k] for r in r32], o64[2][k], False, flipped)
 
 
-def _backbone(kind, n, ei, H, seed):
+def _backbone(kind, n, ei, H, seed, rev=False):
     deg = torch.bincount(torch.bincount(ei[1], minlength=n))
     torch.manual_seed(seed)
     if kind == "pna":
-        return b200mp.PNAS(num_features=H, num_gnn_layers=2, n_hidden=H, edge_updates=True, edge_dim=H, deg=deg)
-    return b200mp.GINe(num_features=H, num_gnn_layers=2, n_hidden=H, edge_updates=True, edge_dim=H)
+        return b200mp.PNAS(num_features=H, num_gnn_layers=2, n_hidden=H, edge_updates=True, edge_dim=H, deg=deg, reverse_mp=rev)
+    return b200mp.GINe(num_features=H, num_gnn_layers=2, n_hidden=H, edge_updates=True, edge_dim=H, reverse_mp=rev)
 
 
 @pytest.mark.parametrize("kind", ["pna", "gine"])
@@ -149,6 +149,20 @@ def test_backbone_vs_oracle_node_kernels_active(kind):
     fn = OM.pnas if kind == "pna" else OM.gine
     _run_case(f"{kind} N=8192 E=120k H=64", m, lambda p, i: fn(p, i["x"], i["edge_index"], i["edge_attr"], 2, True, False),
               lambda mod, i: mod(i["x"], i["edge_index"], i["edge_attr"]), ins, ("x", "edge_attr"), 3)
+
+
+@pytest.mark.parametrize("kind", ["pna", "gine"])
+def test_reverse_mp_vs_oracle_node_kernels_active(kind):
+    """reverse message passing (gine.py:28-35, pna.py:37-46) at N = 8192, E = 120 k: both convs through the row maps (no permutation
+    passes), `lin` over [x, a_in, a_out] on the node kernel without the concatenation"""
+    n, e, H = 8192, 120_000, 64
+    ei = hub_graph(n, e, 12, 3000)
+    g = torch.Generator().manual_seed(6)
+    m = _backbone(kind, n, ei, H, 22, rev=True)
+    ins = {"x": torch.randn(n, H, generator=g), "edge_index": ei, "edge_attr": torch.randn(e, 1, H, generator=g)}
+    fn = OM.pnas if kind == "pna" else OM.gine
+    _run_case(f"{kind} reverse_mp N=8192 E=120k", m, lambda p, i: fn(p, i["x"], i["edge_index"], i["edge_attr"], 2, True, True),
+              lambda mod, i: mod(i["x"], i["edge_index"], i["edge_attr"]), ins, ("x", "edge_attr"), 5)
 
 
 @pytest.mark.parametrize("kind", ["pna", "gine"])
