@@ -138,16 +138,28 @@ class _Backbone(_EdgeStorage, nn.Module):
             raise NotImplementedError("reverse_mp is not supported on a partitioned graph")
         st, x, e = part.st, x_local, self._store(e_local)
         gather = lambda t: PL.all_gather_rows(t, part)
-        for i in range(self.num_gnn_layers):
+        gather_async = lambda t: PL.all_gather_rows_async(t, part)
+        pre = None
+        L = self.num_gnn_layers
+        for i in range(L):
             sink = BF.EdgeGradSink() if (self.edge_updates and e.requires_grad and torch.is_grad_enabled()) else None
-            c = self.convs[i].forward_sorted(x, st.fwd, e, gather=gather, sink=sink)
+            c = self.convs[i].forward_sorted(x, st.fwd, e, gather=gather, sink=sink, hoisted=pre)
+            pre = None
             bn = self.batch_norms[i].module
             if bn.training:
                 x = BF.bn_relu_residual(bn, c, x, group=part.group, n_total=part.num_nodes)
             else:
                 x = (x + F.relu(PL.sync_batch_norm(bn, c, part))) / 2
             if self.edge_updates:
-                e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, gather=gather, sink=sink)
+                # the update needs ITS source table now; the next conv's table is requested right behind it, so that its all-gather
+                # runs on the communication stream while the edge-update kernel computes
+                l1 = self.emlps[i][0]
+                H = x.shape[1]
+                P, Q = BF.linear_group(x, (l1.weight[:, :H], l1.weight[:, H:2 * H]), (None, None))
+                P = gather(P)
+                if i + 1 < L:
+                    pre = self.convs[i + 1].hoist(x, gather_async)
+                e = edge_update_sorted(self.emlps[i], x, st, e, 1.0, 0.5, sink=sink, hoisted=(P, Q))
         return x, e
 
     def message_passing(self, x, edge_index, e):

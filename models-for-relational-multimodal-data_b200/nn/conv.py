@@ -71,7 +71,12 @@ class GINEConv(nn.Module):
         self.eps.data.fill_(self.initial_eps)
         self.lin.reset_parameters()
 
-    def forward_sorted(self, x: Union[Tensor, tuple], seg: SegmentIndex, e: Tensor, gather=None, sink=None, e_eid=None) -> Tensor:
+    def hoist(self, x: Tensor, gather):
+        """the source-side node table of this conv on every rank's rows (multi-GPU): may be requested one step early, so that its
+        all-gather runs behind the previous layer's edge update (parallel.AsyncRows)"""
+        return gather(x)
+
+    def forward_sorted(self, x: Union[Tensor, tuple], seg: SegmentIndex, e: Tensor, gather=None, sink=None, e_eid=None, hoisted=None) -> Tensor:
         """`gather` (multi-GPU, parallel.py): maps the owned rows of the source-side node table to
         the table of all ranks; the self term and the output stay on the owned rows.  `sink`:
         functional.EdgeGradSink shared with the layer's edge update.  `e_eid`: int32 row map when e
@@ -82,7 +87,10 @@ class GINEConv(nn.Module):
             self_term = x_dst is not None
         if self.lin.weight.shape[0] != self.lin.weight.shape[1] or x.shape[1] != self.lin.weight.shape[0]:
             raise ValueError("b200mp GINEConv kernels need edge_dim == in_channels")
-        out = BF.gine_aggregate(gather(x) if gather is not None else x, e, self.lin.weight, self.lin.bias, seg, sink, e_eid)
+        xs = hoisted if hoisted is not None else (gather(x) if gather is not None else x)
+        if hasattr(xs, "ready"):
+            xs = xs.ready()                   # an all-gather issued earlier: the consumer stream waits for it here
+        out = BF.gine_aggregate(xs, e, self.lin.weight, self.lin.bias, seg, sink, e_eid)
         if self_term:
             out = torch.addcmul(out, x, 1 + self.eps)
         return self._apply_nn(out)
@@ -151,16 +159,28 @@ class PNAConv(nn.Module):
         self.post_nns[0][0].reset_parameters()
         self.lin.reset_parameters()
 
-    def forward_sorted(self, x: Tensor, seg: SegmentIndex, e: Tensor, gather=None, sink=None, e_eid=None) -> Tensor:
+    def hoist(self, x: Tensor, gather=None):
+        """(A, B, out0): the node halves of pre_nn and the self term of post_nn on the N rows (SURVEY.md section 7 "hoisting"); with
+        `gather` (multi-GPU) B covers every rank's rows -- requested one step early, its all-gather runs behind the previous layer's
+        edge update (parallel.AsyncRows)"""
         Fi = self.F_in
-        pre = self.pre_nns[0][0]
-        Wi, Wj, Wc = pre.weight[:, :Fi], pre.weight[:, Fi:2 * Fi], pre.weight[:, 2 * Fi:]
-        # pre_nn is one Linear without activation: hoist the node halves to N rows and fold the
-        # edge encoder into a single H x H matrix (SURVEY.md section 7 "hoisting")
-        post = self.post_nns[0][0]
+        pre, post = self.pre_nns[0][0], self.post_nns[0][0]
+        Wi, Wj = pre.weight[:, :Fi], pre.weight[:, Fi:2 * Fi]
         A, B, out = BF.linear_group(x, (Wi, Wj, post.weight[:, :Fi]), (None, None, post.bias))
         if gather is not None:            # multi-GPU: source rows of every rank (parallel.py)
             B = gather(B)
+        return A, B, out
+
+    def forward_sorted(self, x: Tensor, seg: SegmentIndex, e: Tensor, gather=None, sink=None, e_eid=None, hoisted=None) -> Tensor:
+        Fi = self.F_in
+        pre = self.pre_nns[0][0]
+        Wc = pre.weight[:, 2 * Fi:]
+        # pre_nn is one Linear without activation: hoist the node halves to N rows and fold the
+        # edge encoder into a single H x H matrix (SURVEY.md section 7 "hoisting")
+        post = self.post_nns[0][0]
+        A, B, out = hoisted if hoisted is not None else self.hoist(x, gather)
+        if hasattr(B, "ready"):
+            B = B.ready()                     # an all-gather issued earlier: the consumer stream waits for it here
         Wp = Wc @ self.edge_encoder.weight
         bp = Wc @ self.edge_encoder.bias + pre.bias
         agg4, _ = BF.pna_aggregate(A, B, e, Wp, bp, seg, sink, e_eid)
@@ -182,13 +202,16 @@ class PNAConv(nn.Module):
 
 
 def edge_update_sorted(emlp: nn.Sequential, x: Tensor, st: EdgeStructure, e: Tensor, alpha: float, beta: float,
-                       gather=None, sink=None, e_eid=None, out_eid=None) -> Tensor:
+                       gather=None, sink=None, e_eid=None, out_eid=None, hoisted=None) -> Tensor:
     """e' = alpha e + beta emlp([x[src], x[dst], e]) with emlp = Sequential(Linear(3H,H), ReLU,
     Linear(H,H)) (gine.py:71-75,88-89; pna.py:80-84,97-99; models/fused.py:215-219,254)."""
     l1, l2 = emlp[0], emlp[2]
     H = x.shape[1]
     Ws, Wd, We = l1.weight[:, :H], l1.weight[:, H:2 * H], l1.weight[:, 2 * H:]
-    P, Q = BF.linear_group(x, (Ws, Wd), (None, None))
-    if gather is not None:
-        P = gather(P)
+    if hoisted is not None:               # (P on every rank's rows, Q): computed and gathered by the caller
+        P, Q = hoisted
+    else:
+        P, Q = BF.linear_group(x, (Ws, Wd), (None, None))
+        if gather is not None:
+            P = gather(P)
     return BF.edge_update(P, Q, e, We, l1.bias, l2.weight, l2.bias, st, alpha, beta, sink, e_eid, out_eid)

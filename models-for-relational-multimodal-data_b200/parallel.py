@@ -117,6 +117,45 @@ def all_gather_rows(x, part: Partition):
     return _AllGatherRows.apply(x, part)
 
 
+class AsyncRows:
+    """An all-gather of node rows in flight on the communication stream.  ``ready()`` makes the current stream wait for it and
+    returns the gathered table (autograd-connected: its backward is the reduce-scatter of ``_AllGatherRows``)."""
+
+    def __init__(self, table, work, keep=None):
+        self.table, self.work, self.keep = table, work, keep          # keep: the send buffer, alive until the collective is done
+
+    def ready(self):
+        if self.work is not None:
+            self.work.wait()
+            self.work = self.keep = None
+        return self.table
+
+
+class _AllGatherRowsAsync(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, part: Partition, box):
+        ctx.part = part
+        H = x.shape[1]
+        mine = x.new_zeros((part.n_max, H))
+        mine[: x.shape[0]] = x
+        out = x.new_empty((part.world * part.n_max, H))
+        box.append(dist.all_gather_into_tensor(out, mine, group=part.group, async_op=True))
+        box.append(mine)                       # keep the send buffer alive until the collective is done
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        return _AllGatherRows.backward(ctx, g) + (None,)
+
+
+def all_gather_rows_async(x, part: Partition) -> AsyncRows:
+    """start the all-gather now, use it later: between the two the current stream keeps computing (the gather of layer l + 1's
+    source table runs behind layer l's edge-update kernel)"""
+    box = []
+    table = _AllGatherRowsAsync.apply(x, part, box)
+    return AsyncRows(table, box[0], box[1])
+
+
 class _SyncBatchNorm(torch.autograd.Function):
     """BatchNorm1d training forward over the rows of ALL ranks (sums all-reduced)."""
 
