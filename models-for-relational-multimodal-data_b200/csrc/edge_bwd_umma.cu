@@ -447,11 +447,175 @@ __global__ void __launch_bounds__(NTB, 1) message_bwd_umma_kernel(MsgBwdUArgs<T>
     if (warp == 0) tmem_dealloc(tm, 128);
 }
 
+// ---- message backward on 64-edge tiles, two CTAs per SM ---------------------------------------------------------------
+// Round 2 measured that two resident CTAs are what hides the per-tile phase chain (message forward: -16 %); the 128-edge
+// kernel above needs 160 KB of shared memory, so it runs alone on its SM.  This variant is the same computation on 64-edge
+// tiles with 256 threads: 96 KB (G and e hi / lo tiles of 16 KB, the hi / lo weight tile), two CTAs per SM, each with its own
+// tensor-memory columns and weight-gradient partial.  The data product runs at M = 64 (half the tensor-pipe efficiency of
+// M = 128, as in the two-pipeline edge-update backward); the weight-gradient product is M = 64 in both.
+template <int KIND, typename T, bool ROWS>
+__global__ void __launch_bounds__(256, 2) message_bwd_umma64_kernel(MsgBwdUArgs<T> a, uint32_t FLUSH_T) {
+    using namespace dual;
+    constexpr int NP = NPG;
+    extern __shared__ __align__(128) float smem_raw[];
+    float* smem = smem_raw + (((smem_u32(smem_raw) + 1023u) & ~1023u) - smem_u32(smem_raw)) / 4;
+    float* G_hi = smem;
+    float* G_lo = G_hi + RG_T::FLOATS;
+    float* E_hi = G_lo + RG_T::FLOATS;        // e tile; staging tile once the MMAs are done
+    float* E_lo = E_hi + RG_T::FLOATS;
+    float* W_hi = E_lo + RG_T::FLOATS;
+    float* W_lo = W_hi + WT::FLOATS;
+    __shared__ TileSync sync;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int j = tid & 15, g = tid >> 4;                  // global-memory side: chunk j of rows 4 g .. 4 g + 3
+    if (warp == 0) tmem_alloc(&sync.tmem_base, 128);
+    if (tid == 0) { mbar_init(&sync.bar[0], 1); mbar_fence_init(); }
+    load_weight_tiles<true, NTG>(W_hi, W_lo, a.W, tid);
+    fence_async_smem();
+    fence_before();
+    __syncthreads();
+    fence_after();
+    const uint32_t tm = sync.tmem_base;
+    const uint32_t T_ACC = tm, T_GW = tm + 64;
+    float* stage = E_hi;
+
+    float4 accb = f4(0.f, 0.f, 0.f, 0.f);
+    const int64_t ntiles = (a.E + RG - 1) / RG;
+    uint32_t it = 0;
+    Rows Rm, Re;
+    int nrows_pf = 0, seg_pf[NP], nbr_pf[NP];
+#pragma unroll
+    for (int i = 0; i < NP; ++i) { seg_pf[i] = 0; nbr_pf[i] = 0; }
+    auto prefetch = [&](int64_t tile_) {
+        const int64_t r0_ = tile_ * RG;
+        nrows_pf = (int)min64(RG, a.E - r0_);
+        load_rows(Rm, a.m, nullptr, r0_, nrows_pf, tid);
+        load_rows(Re, a.e, a.eid, r0_, nrows_pf, tid);
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            const int rc = min(g * NP + i, nrows_pf - 1);
+            seg_pf[i] = __ldg(a.seg + r0_ + rc);
+            if (a.gT1) nbr_pf[i] = __ldg(a.nbr + r0_ + rc);
+        }
+    };
+    if ((int64_t)blockIdx.x < ntiles) prefetch(blockIdx.x);
+
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int64_t row0 = tile * RG;
+        const int nrows = nrows_pf;
+
+        store_rows_split(Re, E_hi, E_lo, nrows, tid);
+        {
+            float4 Gv[NP];
+            PnaCoef cf;
+            float4 ga = f4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
+                const int r = g * NP + i;
+                const float4 mv = Rm.v[i];
+                const int64_t d = seg_pf[i];
+                const bool fresh = i == 0 || seg_pf[i] != seg_pf[i - 1];
+                float4 G;
+                if (KIND == 0) {
+                    if (fresh) load_coef(cf, a.node_in + d * 7 * HH + j * 4);
+                    G.x = pna_g(mv.x, cf.c0.x, cf.c1.x, cf.gmn.x, cf.mn.x, cf.gmx.x, cf.mx.x, cf.mu.x);
+                    G.y = pna_g(mv.y, cf.c0.y, cf.c1.y, cf.gmn.y, cf.mn.y, cf.gmx.y, cf.mx.y, cf.mu.y);
+                    G.z = pna_g(mv.z, cf.c0.z, cf.c1.z, cf.gmn.z, cf.mn.z, cf.gmx.z, cf.mx.z, cf.mu.z);
+                    G.w = pna_g(mv.w, cf.c0.w, cf.c1.w, cf.gmn.w, cf.mn.w, cf.gmx.w, cf.mx.w, cf.mu.w);
+                } else {
+                    if (fresh) ga = ldg4(a.node_in + d * HH + j * 4);
+                    G = f4(mv.x > 0.f ? ga.x : 0.f, mv.y > 0.f ? ga.y : 0.f, mv.z > 0.f ? ga.z : 0.f, mv.w > 0.f ? ga.w : 0.f);
+                }
+                if (r >= nrows) G = f4(0.f, 0.f, 0.f, 0.f);
+                if (!ROWS && r < nrows && a.gT1) red_add4(a.gT1 + (int64_t)nbr_pf[i] * HH + j * 4, G);
+                if (ROWS && r < nrows) st4(a.G_out + (row0 + r) * HH + j * 4, G);
+                accb = accb + G;
+                Gv[i] = G;
+            }
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
+                float4 gh, gl;
+                split4(Gv[i], gh, gl);
+                const int o = RG_T::off(g * NP + i, j);
+                st4(G_hi + o, gh);
+                st4(G_lo + o, gl);
+            }
+        }
+        fence_async_smem();
+        fence_before();
+        __syncthreads();
+        fence_after();
+        if (tid == 0) {
+            gemm3_data64(T_ACC, G_hi, G_lo, W_hi, W_lo, 0);
+            gemm3_wgrad64(T_GW, G_hi, G_lo, E_hi, E_lo, (it % FLUSH_T) != 0);
+            mma_commit(&sync.bar[0]);
+        }
+        int64_t orow[NP];
+        float4 prev[NP];
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            const int r = g * NP + i;
+            orow[i] = (a.eid && r < nrows) ? (int64_t)__ldg(a.eid + row0 + r) : row0 + r;
+        }
+#pragma unroll
+        for (int i = 0; i < NP; ++i) prev[i] = f4(0.f, 0.f, 0.f, 0.f);
+        if (a.accumulate) {
+#pragma unroll
+            for (int i = 0; i < NP; ++i)
+                if (g * NP + i < nrows) prev[i] = ld_e4(a.g_e + orow[i] * HH + j * 4);
+        }
+        if (a.g_acc) {
+#pragma unroll
+            for (int i = 0; i < NP; ++i)
+                if (g * NP + i < nrows) prev[i] = prev[i] + ldg_e4(a.g_acc + (row0 + g * NP + i) * HH + j * 4);
+        }
+        if (tile + gridDim.x < ntiles) prefetch(tile + gridDim.x);
+        mbar_wait(&sync.bar[0], it & 1);
+        fence_after();
+        stage_from_tmem64(T_ACC, stage, warp, lane);      // the e tile is dead: g_e rows take its place
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            const int r = g * NP + i;
+            float4 v = lds4(stage + stage_off(r, j));
+            v = v + prev[i];
+            if (r < nrows) st_e4(a.g_e + orow[i] * HH + j * 4, v);
+        }
+        if ((it % FLUSH_T) == FLUSH_T - 1)
+            store_wgrad_partial(T_GW, a.gW_part + (int64_t)blockIdx.x * HH * HH, 1.f, true, tid, it >= FLUSH_T);
+        fence_before();
+        __syncthreads();
+        fence_after();
+    }
+
+    if ((it % FLUSH_T) != 0 || it < FLUSH_T)
+        store_wgrad_partial(T_GW, a.gW_part + (int64_t)blockIdx.x * HH * HH, 1.f, (it % FLUSH_T) != 0, tid, it >= FLUSH_T);
+    group_column_sums(G_hi, accb, a.gb_part + (int64_t)blockIdx.x * HH, 1.f, tid, 0);
+    fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tm, 128);
+}
+
 template <typename T>
 static int launch_msg_bwd_umma_t(int kind, int64_t E, const T* m, const T* e, const int32_t* eid, const float* node_in,
                                  const int32_t* seg, const int32_t* nbr, const float* W, T* g_e, int accumulate, float* gT1,
                                  float* gW_part, float* gb_part, int n_part, const T* g_acc, cudaStream_t st, float* G_out) {
     MsgBwdUArgs<T> a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, g_acc, G_out};
+    {   // B200MP_MSG_BWD64=1: the 64-edge / two-CTAs-per-SM variant (A/B switch)
+        const char* v = getenv("B200MP_MSG_BWD64");
+        if (v && v[0] == '1') {
+            const size_t smem64 = 4 * dual::RG_T::BYTES + 2 * WT::BYTES + 1024;
+            auto k64 = G_out ? (kind == 0 ? message_bwd_umma64_kernel<0, T, true> : message_bwd_umma64_kernel<1, T, true>)
+                             : (kind == 0 ? message_bwd_umma64_kernel<0, T, false> : message_bwd_umma64_kernel<1, T, false>);
+            B200MP_CUDA(cudaFuncSetAttribute(k64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem64));
+            (void)cudaFuncSetAttribute(k64, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+            const uint32_t fl64 = wgrad_flush_edges() / 64;
+            k64<<<n_part, 256, smem64, st>>>(a, fl64 < 1 ? 1 : fl64);
+            B200MP_LAUNCH_CHECK();
+            return 0;
+        }
+    }
     const size_t smem = 4 * RT::BYTES + 2 * WT::BYTES + 1024;
     auto kern = G_out ? (kind == 0 ? message_bwd_umma_kernel<0, T, true> : message_bwd_umma_kernel<1, T, true>)
                       : (kind == 0 ? message_bwd_umma_kernel<0, T, false> : message_bwd_umma_kernel<1, T, false>);

@@ -94,3 +94,26 @@ def test_update_forward_pipelined_equals_serial(e, n, maps):
         outs.append(BF._edge_linear_fwd(2, ea, eid, W1, b1, P, st.src32, Q, st.dst32, W2, b2, 0.5, 0.5, eid))
     os.environ.pop("B200MP_UPD_PIPE")
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize("kind_id", [0, 1])
+@pytest.mark.parametrize("e,n", [(37, 50), (64, 10), (100_001, 9000), (2_000_000, 150_000)])
+def test_message_backward_64_edge_tiles_equals_128(kind_id, e, n):
+    """B200MP_MSG_BWD64=1 (64-edge tiles, 256 threads, two CTAs per SM) computes what the 128-edge kernel computes: g_e row by row with
+    the same MMA order (bit for bit), node / weight / bias gradients to re-association"""
+    g = torch.Generator(device="cuda").manual_seed(e + kind_id)
+    ei = torch.stack([torch.randint(0, n, (e,), device="cuda", generator=g), (torch.rand(e, device="cuda", generator=g) ** 3 * n).long().clamp_(max=n - 1)])
+    seg = G.edge_structure(ei, n).fwd
+    m = torch.randn(e, H, device="cuda", generator=g)
+    ea = torch.randn(e, H, device="cuda", generator=g)
+    W = torch.randn(H, H, device="cuda", generator=g) / 8
+    node_in = torch.randn(n, 7 * H if kind_id == 0 else H, device="cuda", generator=g)
+    acc = torch.randn(e, H, device="cuda", generator=g)
+    outs = []
+    for flag in ("0", "1"):
+        os.environ["B200MP_MSG_BWD64"] = flag
+        outs.append(BF._message_bwd(kind_id, seg, m, ea, node_in, W, True, n, acc.clone(), seg.perm32()))
+    os.environ.pop("B200MP_MSG_BWD64")
+    (ge0, gT0, gW0, gb0), (ge1, gT1, gW1, gb1) = outs
+    assert torch.equal(ge0, ge1)
+    assert rel_err(gT1, gT0) < 1e-5 and rel_err(gW1, gW0) < 1e-5 and rel_err(gb1, gb0) < 1e-5
