@@ -602,9 +602,10 @@ static int launch_msg_bwd_umma_t(int kind, int64_t E, const T* m, const T* e, co
                                  const int32_t* seg, const int32_t* nbr, const float* W, T* g_e, int accumulate, float* gT1,
                                  float* gW_part, float* gb_part, int n_part, const T* g_acc, cudaStream_t st, float* G_out) {
     MsgBwdUArgs<T> a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, g_acc, G_out};
-    {   // B200MP_MSG_BWD64=1: the 64-edge / two-CTAs-per-SM variant (A/B switch)
+    {   // the 64-edge / two-CTAs-per-SM variant is the default (same-box A/B on hi_medium: PNA 11.77 -> 11.36 ms, GINE 10.85 -> 10.61 ms);
+        // B200MP_MSG_BWD64=0 selects the 128-edge kernel
         const char* v = getenv("B200MP_MSG_BWD64");
-        if (v && v[0] == '1') {
+        if (!(v && v[0] == '0')) {
             const size_t smem64 = 4 * dual::RG_T::BYTES + 2 * WT::BYTES + 1024;
             auto k64 = G_out ? (kind == 0 ? message_bwd_umma64_kernel<0, T, true> : message_bwd_umma64_kernel<1, T, true>)
                              : (kind == 0 ? message_bwd_umma64_kernel<0, T, false> : message_bwd_umma64_kernel<1, T, false>);
