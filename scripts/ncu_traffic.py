@@ -3,7 +3,8 @@
 kernel, averaged over the captured launches).  usage: ncu_traffic.py raw.csv workload out.json"""
 import csv, json, sys
 NAMES = {"edge_update_bwd_umma_kernel": "edge_update_bwd", "message_bwd_umma_kernel<0": "pna_message_bwd",
-         "message_bwd_umma_kernel<1": "gine_message_bwd", "edge_linear_fwd_umma_kernel<0": "pna_message_fwd",
+         "message_bwd_umma_kernel<1": "gine_message_bwd", "message_bwd_umma64_kernel<0": "pna_message_bwd",
+         "message_bwd_umma64_kernel<1": "gine_message_bwd", "edge_linear_fwd_umma_kernel<0": "pna_message_fwd",
          "edge_linear_fwd_umma_kernel<1": "gine_message_fwd", "edge_linear_fwd_umma_kernel<2": "edge_update_fwd",
          "seg_light_kernel<1": "segment_reduce_pna"}
 rows = list(csv.reader(open(sys.argv[1])))
