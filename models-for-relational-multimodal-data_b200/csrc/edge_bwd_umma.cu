@@ -90,7 +90,11 @@ __device__ __forceinline__ void cta_column_sums(float* red, float4 acc, float* _
 
 // (namespace dual -- the two-pipelines-per-CTA helpers -- lives in umma_edge.cuh: the update forward uses it too)
 
-template <typename T, bool ROWS>          // ROWS: write the Gh rows (atomic-free node gradients) instead of scattering them
+// SPLIT: the data product and the weight-gradient product of a phase are committed to separate mbarriers and the
+// accumulator rows are staged in a tile of their own (2 x 16 KB more shared memory), so that the epilogue of a phase only waits
+// for the product it reads: the weight-gradient MMAs (half of the tensor-pipe time of this kernel, 42 % active under ncu) run
+// behind the epilogue instead of in front of it, and are only awaited where their operand tiles are overwritten.
+template <typename T, bool ROWS, bool SPLIT>   // ROWS: write the Gh rows (atomic-free node gradients) instead of scattering them
 __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArgs<T> a, int n_virtual, uint32_t FLUSH_U) {
     using namespace dual;
     constexpr int NP = NPG;
@@ -100,7 +104,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
     float* W2_lo = W2_hi + WT::FLOATS;
     float* W1_hi = W2_lo + WT::FLOATS;        // B[n=k][K=j] = W1[j][k]   (g_e = Gh W1)
     float* W1_lo = W1_hi + WT::FLOATS;
-    __shared__ uint64_t bars[2][2];
+    __shared__ uint64_t bars[2][4];           // [group][U | ACC2 | GW2 | GW1] (the last two only with SPLIT)
     __shared__ uint32_t tmem_base_s;
     __shared__ int sidx_s[2][2][RG];          // [group][src / dst][row]
 
@@ -114,7 +118,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
     uint64_t* bar = bars[grp];
     int (*sidx)[RG] = sidx_s[grp];
     if (warp == 0) tmem_alloc(&tmem_base_s, 512);
-    if (lt == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
+    if (lt == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_init(&bar[2], 1); mbar_init(&bar[3], 1); mbar_fence_init(); }
     load_weight_tiles<true, NTB>(W2_hi, W2_lo, a.W2, tid);
     load_weight_tiles<true, NTB>(W1_hi, W1_lo, a.W1, tid);
     fence_async_smem();
@@ -123,7 +127,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
     fence_after();
     const uint32_t tm = tmem_base_s + grp * 256;
     const uint32_t T_U = tm, T_ACC2 = tm + 64, T_GW2 = tm + 128, T_GW1 = tm + 192;
-    float* stage = G_hi;
+    float* stage = SPLIT ? W1_lo + WT::FLOATS + (8 + grp) * RG_T::FLOATS : G_hi;
 
     float4 accb1 = f4(0.f, 0.f, 0.f, 0.f), accb2 = f4(0.f, 0.f, 0.f, 0.f);   // columns 4 j .. 4 j + 3 over this thread's rows
     const int64_t ntiles = (a.E + RG - 1) / RG;
@@ -157,8 +161,9 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
         fence_after();
         if (lt == 0) {
             gemm3_data64(T_U, G_hi, G_lo, W2_hi, W2_lo, 0);
+            if (SPLIT) mma_commit(&bar[0]);
             gemm3_wgrad64(T_GW2, G_hi, G_lo, H_hi, H_lo, (it % FLUSH_U) != 0);
-            mma_commit(&bar[0]);
+            mma_commit(&bar[SPLIT ? 2 : 0]);
         }
         load_rows(Re, a.e, a.e_eid, row0, nrows, lt);                 // e tile in flight during the MMAs
         int srow[NP], drow[NP];
@@ -184,16 +189,20 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
                 if (valid) accb2 = accb2 + Rg.v[i];
                 if (!ROWS && valid && a.gP) red_add4(a.gP + (int64_t)srow[i] * HH + j * 4, Gh[i]);
                 if (ROWS && valid) st4(a.gh_out + (row0 + r) * HH + j * 4, Gh[i]);
+            }
+            if (!ROWS && a.gQ) red_runs(a.gQ, drow, Gh, j, lane);
+            if (SPLIT) { mbar_wait(&bar[2], par); fence_after(); }    // GW2 has read the g and h tiles: both may be overwritten
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
                 float4 gh, gl;
                 split4(Gh[i], gh, gl);
-                const int o = RG_T::off(r, j);
+                const int o = RG_T::off(g * NP + i, j);
                 st4(H_hi + o, gh);
                 st4(H_lo + o, gl);
             }
-            if (!ROWS && a.gQ) red_runs(a.gQ, drow, Gh, j, lane);
         }
-        group_sync(grp);                                 // every thread is done reading the staged U rows
-        store_rows_split(Re, G_hi, G_lo, nrows, lt);     // e tile replaces them
+        if (!SPLIT) group_sync(grp);                     // every thread is done reading the staged U rows
+        store_rows_split(Re, G_hi, G_lo, nrows, lt);     // e tile replaces them (SPLIT: replaces the g tile; the stage is separate)
         fence_async_smem();
         fence_before();
         group_sync(grp);
@@ -202,8 +211,9 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
         // ---- phase B: ACC2 = Gh W1; GW1 += Gh^T e
         if (lt == 0) {
             gemm3_data64(T_ACC2, H_hi, H_lo, W1_hi, W1_lo, 0);
+            if (SPLIT) mma_commit(&bar[1]);
             gemm3_wgrad64(T_GW1, H_hi, H_lo, G_hi, G_lo, (it % FLUSH_U) != 0);
-            mma_commit(&bar[1]);
+            mma_commit(&bar[SPLIT ? 3 : 1]);
         }
         int nrows_next = 0;
         if (tile + stride < ntiles) {                    // next tile's h and g in flight
@@ -227,6 +237,7 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
 #pragma unroll
         for (int i = 0; i < NP; ++i) Rg.v[i] = Re.v[i];
         nrows_pf = nrows_next;
+        if (SPLIT) { mbar_wait(&bar[3], par); fence_after(); }    // GW1 done: its operand tiles are free for the next tile, and the drain may read it
         if ((it % FLUSH_U) == FLUSH_U - 1) {             // drain the two weight-gradient accumulators (both products are complete)
             store_wgrad_partial(T_GW1, a.gW1_part + v0 * HH * HH, 1.f, true, lt, it >= FLUSH_U);
             store_wgrad_partial(T_GW2, a.gW2_part + v0 * HH * HH, a.beta, true, lt, it >= FLUSH_U);
@@ -256,8 +267,12 @@ static int launch_upd_bwd_umma_t(int64_t E, const T* g_out, const T* h, const T*
                                  float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part,
                                  const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st, float* gh_out) {
     UpdBwdUArgs<T> a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, g_eid, e_eid, gh_out};
-    const size_t smem = 8 * dual::RG_T::BYTES + 4 * WT::BYTES + 1024;
-    auto kern = gh_out ? edge_update_bwd_umma_kernel<T, true> : edge_update_bwd_umma_kernel<T, false>;
+    // B200MP_UPD_BWD_SPLIT=0 selects the single-barrier phases (round-2 baseline) for the same-box A/B
+    const char* sv = getenv("B200MP_UPD_BWD_SPLIT");
+    const bool split = !(sv && sv[0] == '0');
+    const size_t smem = (split ? 10 : 8) * dual::RG_T::BYTES + 4 * WT::BYTES + 1024;
+    auto kern = split ? (gh_out ? edge_update_bwd_umma_kernel<T, true, true> : edge_update_bwd_umma_kernel<T, false, true>)
+                      : (gh_out ? edge_update_bwd_umma_kernel<T, true, false> : edge_update_bwd_umma_kernel<T, false, false>);
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const uint32_t fl = wgrad_flush_edges() / 64;          // tiles (64 edges) between drains
     kern<<<(n_part + 1) / 2, NTB, smem, st>>>(a, n_part, fl < 1 ? 1 : fl);   // two 64-edge pipelines (partial rows) per CTA

@@ -18,7 +18,7 @@ ncu -i gpurun_out/prof_small.ncu-rep --page raw --csv > gpurun_out/prof_small_ra
 ncu -i gpurun_out/prof_small.ncu-rep --page source --csv --print-source sass > gpurun_out/prof_small_src.csv 2>/dev/null
 rm -f gpurun_out/prof_small.ncu-rep
 # DRAM traffic of the per-edge kernels at the bench workload itself (one timed step: launches after the 3 warm-ups)
-timeout 900 ncu --set full --clock-control none -k regex:'umma_kernel|seg_light' -s ${TSKIP:-108} -c 36 -f -o gpurun_out/prof_medium $CMD > gpurun_out/ncu_medium.log 2>&1
+timeout 900 ncu --set full --clock-control none -k regex:'umma|seg_light' -s ${TSKIP:-108} -c 36 -f -o gpurun_out/prof_medium $CMD > gpurun_out/ncu_medium.log 2>&1
 echo "ncu medium rc=$?"; tail -2 gpurun_out/ncu_medium.log
 ncu -i gpurun_out/prof_medium.ncu-rep --page raw --csv > gpurun_out/prof_medium_raw.csv 2>/dev/null
 rm -f gpurun_out/prof_medium.ncu-rep

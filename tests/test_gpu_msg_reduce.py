@@ -117,3 +117,27 @@ def test_message_backward_64_edge_tiles_equals_128(kind_id, e, n):
     (ge0, gT0, gW0, gb0), (ge1, gT1, gW1, gb1) = outs
     assert torch.equal(ge0, ge1)
     assert rel_err(gT1, gT0) < 1e-5 and rel_err(gW1, gW0) < 1e-5 and rel_err(gb1, gb0) < 1e-5
+
+
+@pytest.mark.parametrize("e,n", [(37, 50), (64, 10), (129, 40), (100_001, 9000), (2_000_000, 150_000)])
+def test_edge_update_backward_split_barriers_equals_single(e, n):
+    """B200MP_UPD_BWD_SPLIT=1 (data / weight-gradient products on separate mbarriers, accumulator rows staged in their own tile) runs the
+    same MMAs in the same order as the single-barrier phases: g_e bit for bit, the scattered node gradients and the per-CTA partial sums
+    to re-association"""
+    g = torch.Generator(device="cuda").manual_seed(e)
+    ei = torch.stack([torch.randint(0, n, (e,), device="cuda", generator=g), (torch.rand(e, device="cuda", generator=g) ** 3 * n).long().clamp_(max=n - 1)])
+    st = G.edge_structure(ei, n)
+    g_out = torch.randn(e, H, device="cuda", generator=g)
+    h = torch.randn(e, H, device="cuda", generator=g).relu_()
+    ea = torch.randn(e, H, device="cuda", generator=g)
+    W1 = torch.randn(H, H, device="cuda", generator=g) / 8
+    W2 = torch.randn(H, H, device="cuda", generator=g) / 8
+    outs = []
+    for flag in ("0", "1"):
+        os.environ["B200MP_UPD_BWD_SPLIT"] = flag
+        outs.append(BF._edge_update_bwd(st, g_out, h, ea, W1, W2, 0.5, 0.5, True, True, g_eid=st.fwd.perm32(), e_eid=None))
+    os.environ.pop("B200MP_UPD_BWD_SPLIT")
+    a, b = outs
+    assert torch.equal(a[0], b[0])
+    for x, y in zip(a[1:], b[1:]):
+        assert rel_err(y, x) < 1e-5
