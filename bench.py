@@ -34,7 +34,17 @@ WORKLOADS = {   # name: (nodes, edges, seed)  -- SURVEY.md section 8(d)
     "hi_small": (515_080, 5_078_345, 20240719),
     "tiny": (8_989, 5_198 * 16, 20240718),
 }
-H, LAYERS = 64, 2
+def _hidden_from_argv(default=64):
+    """--hidden is read before the per-kernel byte tables below are built (they are functions of H); 64 = the headline width"""
+    for i, a in enumerate(sys.argv):
+        if a == "--hidden" and i + 1 < len(sys.argv):
+            return int(sys.argv[i + 1])
+        if a.startswith("--hidden="):
+            return int(a.split("=", 1)[1])
+    return default
+
+
+H, LAYERS = _hidden_from_argv(), 2
 K_COLS = 5                     # edge columns of the AML table (3 categorical + 1 numerical + 1 timestamp, SURVEY.md 8)
 CPU_SAMPLE_EDGES = 1_000_000
 
@@ -633,6 +643,8 @@ def main():
     ap.add_argument("--dtype", default="f32", choices=["f32", "bf16"],
                     help="bf16: EXTRA line (BASELINE.json config 3) -- every [E,H] edge tensor stored as bf16, fp32 arithmetic; the f32 line is the headline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--hidden", type=int, default=64, choices=(64, 128),
+                    help="hidden width H (extra lines; 64 is the headline configuration, 128 the reference's PNAS default: pna.py:50)")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer arm")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))

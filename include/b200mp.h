@@ -351,6 +351,31 @@ int b200mp_segment_mean_blend_fwd(const float* x, const float* emb, const int64_
 int b200mp_segment_mean_blend_bwd(const float* g, const int64_t* ptr, const int64_t* index, int64_t N, int64_t R, int W,
                                   float* gx, float* gemb, void* stream);
 
+/* ------------------------------------------------------------------ per-edge linears at H = 128 on the tensor cores
+ * `n_hidden = 128` is the reference's PNAS default (src/nn/gnn/pna.py:50) and the only width its notebook timed
+ * (benchmark.ipynb:90,100).  The fused H = 64 kernels keep a whole weight image (and, in the backward, two weight-gradient
+ * accumulators) resident per CTA; at H = 128 that no longer fits next to the operand tiles, so the same products are composed from
+ * the node-level tcgen05 kernels over the E rows:
+ * b200mp_row_linear: for tile row k (N rows, K % 32 == 0, NO in {64,128,192,256}; T1 / T2 / mask / R / R2 / Y rows are NO wide)
+ *     z = X[xrow[k]] W^T + bias + T1[idx1[k]] + T2[idx2[k]];   relu != 0: z = max(z, 0);   mask: z = z * [mask[k] > 0]
+ *     Y[orow[k]] = alpha R[rrow[k]] + beta z + R2[k]
+ *   every pointer after Wimg except Y is nullable (row maps NULL = k).  Wimg as b200mp_node_linear.  R may alias Y when
+ *   rrow == orow.  Covers PNAConv / GINEConv messages (pna.py:71-74, gine.py:66-70: T1 = B[src], T2 = A[dst]), both halves of the
+ *   edge update (pna.py:93, gine.py:90: h = relu(..), e' = alpha e + beta (h W2^T + b2)) and the data products of their backward
+ *   (Gh = beta (g W2) * [h > 0];  g_e = alpha g + Gh W1;  g_e += G W).
+ * b200mp_message_grad_rows: G[k] = d loss / d m_k from the saved message and the per-node coefficient rows (kind 0: PNA, node_in
+ *   [N,7H] of b200mp_pna_coef; kind 1: GINE, node_in [N,H] = gradient at the aggregate), same rules as b200mp_message_bwd;
+ *   gT1 (nullable): gT1[nbr[k]] += G[k] with vector REDs.  H % 4 == 0.
+ * b200mp_scatter_add_rows: out[idx[k]] += rows[k] (vector REDs), H % 4 == 0.
+ * The weight gradients of the composition are b200mp_node_linear_wgrad over the E rows. */
+int b200mp_row_linear(const float* X, const int32_t* xrow, int64_t N, int K, int ldx, const float* Wimg, int NO,
+                      const float* bias, const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
+                      int relu, const float* mask, const float* R, const int32_t* rrow, float alpha, float beta,
+                      const float* R2, float* Y, const int32_t* orow, void* stream);
+int b200mp_message_grad_rows(int kind, int H, int64_t E, const float* m, const float* node_in, const int32_t* seg,
+                             const int32_t* nbr, float* G, float* gT1, void* stream);
+int b200mp_scatter_add_rows(const float* rows, const int32_t* idx, int64_t n, int H, float* out, void* stream);
+
 /* ------------------------------------------------------------------ tensor-core self test
  * One-CTA check of the tcgen05 building blocks (csrc/umma.cuh) used by the per-edge kernels:
  *   mode 0: Y[128,64] = X[128,64] W[64,64]^T     mode 1: Y = X W      (3xTF32)

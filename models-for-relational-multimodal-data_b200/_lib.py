@@ -69,6 +69,9 @@ _SIGS = {
     "b200mp_rank_positive": [_p, _p, _l, _i, _p, _p],
     "b200mp_segment_mean_blend_fwd": [_p, _p, _p, _p, _l, _i, _p, _p],
     "b200mp_segment_mean_blend_bwd": [_p, _p, _p, _l, _l, _i, _p, _p, _p],
+    "b200mp_row_linear": [_p, _p, _l, _i, _i, _p, _i, _p, _p, _p, _p, _p, _i, _p, _p, _p, _f, _f, _p, _p, _p, _p],
+    "b200mp_message_grad_rows": [_i, _i, _l, _p, _p, _p, _p, _p, _p, _p],
+    "b200mp_scatter_add_rows": [_p, _p, _l, _i, _p, _p],
     "b200mp_umma_selftest": [_i, _p, _p, _p, _p],
     "b200mp_umma_probe": [_p, _i, _p, _i, C.c_uint64, C.c_uint64, _i, _i, _i, C.c_uint32, _p, _p],
     "b200mp_edge_update_bwd": [_i, _l, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _p],

@@ -320,3 +320,77 @@ extern "C" int b200mp_edge_update_bwd_rows(int64_t E, const float* g_out, const 
     return launch_upd_bwd_umma(E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, nullptr, nullptr, gW1_part, gb1_part, gW2_part, gb2_part,
                                n_part, g_eid, e_eid, (cudaStream_t)stream, Gh_rows);
 }
+
+// ------------------------------------------------------------------ row passes of the H = 128 tensor-core composition
+// At H = 128 the per-edge products run on the tcgen05 row-linear kernel (node_gemm_umma.cu: b200mp_row_linear) and the weight
+// gradients on b200mp_node_linear_wgrad; what is left of the message backward is the per-edge gradient itself, one pass:
+//   G[k] = rule(m[k], node_in[seg[k]])   (same rules as message_bwd_kernel above),   gT1[nbr[k]] += G[k]  (vector REDs, optional)
+namespace b200mp {
+template <int KIND>
+__global__ void __launch_bounds__(256) message_grad_rows_kernel(const float* __restrict__ m, const float* __restrict__ node_in,
+                                                                const int32_t* __restrict__ seg, const int32_t* __restrict__ nbr,
+                                                                int64_t E, int H, float* __restrict__ G, float* __restrict__ gT1) {
+    const int W4 = H / 4;
+    const int64_t total = E * W4;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t k = i / W4;
+        const int c = (int)(i - k * W4) * 4;
+        const float4 mv = ldg4(m + i * 4);
+        const int64_t d = __ldg(seg + k);
+        float4 g;
+        if (KIND == 0) {
+            const float* q = node_in + d * 7 * H + c;
+            const float4 c0 = ldg4(q), c1 = ldg4(q + H), gmn = ldg4(q + 2 * H), mn = ldg4(q + 3 * H),
+                         gmx = ldg4(q + 4 * H), mx = ldg4(q + 5 * H), mu = ldg4(q + 6 * H);
+            g.x = fmaf(c1.x, mv.x - mu.x, c0.x) + (mv.x == mn.x ? gmn.x : 0.f) + (mv.x == mx.x ? gmx.x : 0.f);
+            g.y = fmaf(c1.y, mv.y - mu.y, c0.y) + (mv.y == mn.y ? gmn.y : 0.f) + (mv.y == mx.y ? gmx.y : 0.f);
+            g.z = fmaf(c1.z, mv.z - mu.z, c0.z) + (mv.z == mn.z ? gmn.z : 0.f) + (mv.z == mx.z ? gmx.z : 0.f);
+            g.w = fmaf(c1.w, mv.w - mu.w, c0.w) + (mv.w == mn.w ? gmn.w : 0.f) + (mv.w == mx.w ? gmx.w : 0.f);
+        } else {
+            const float4 ga = ldg4(node_in + d * H + c);
+            g = f4(mv.x > 0.f ? ga.x : 0.f, mv.y > 0.f ? ga.y : 0.f, mv.z > 0.f ? ga.z : 0.f, mv.w > 0.f ? ga.w : 0.f);
+        }
+        st4(G + i * 4, g);
+        if (gT1) red_add4(gT1 + (int64_t)__ldg(nbr + k) * H + c, g);
+    }
+}
+
+// out[idx[k]] += rows[k]   (vector REDs; the scatter half of the edge-update backward: gP[src] += Gh)
+__global__ void __launch_bounds__(256) scatter_add_rows_kernel(const float* __restrict__ rows, const int32_t* __restrict__ idx,
+                                                               int64_t n, int W4, float* __restrict__ out) {
+    const int64_t total = n * W4;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t k = i / W4;
+        const int c = (int)(i - k * W4);
+        red_add4(out + ((int64_t)__ldg(idx + k) * W4 + c) * 4, ldg4(rows + i * 4));
+    }
+}
+
+static inline int rows_grid(int64_t items) {
+    const int64_t want = (items + 255) / 256, cap = (int64_t)device_info().sms * 16;
+    return (int)(want < 1 ? 1 : (want < cap ? want : cap));
+}
+}  // namespace b200mp
+
+extern "C" int b200mp_message_grad_rows(int kind, int H, int64_t E, const float* m, const float* node_in, const int32_t* seg,
+                                        const int32_t* nbr, float* G, float* gT1, void* stream) {
+    using namespace b200mp;
+    if (E < 0 || H < 4 || (H & 3) || (kind != 0 && kind != 1)) return B200MP_EINVAL;
+    if (E == 0) return 0;
+    if (!m || !node_in || !seg || !G || (gT1 && !nbr)) return B200MP_EINVAL;
+    const int grid = rows_grid(E * (H / 4));
+    if (kind == 0) message_grad_rows_kernel<0><<<grid, 256, 0, (cudaStream_t)stream>>>(m, node_in, seg, nbr, E, H, G, gT1);
+    else message_grad_rows_kernel<1><<<grid, 256, 0, (cudaStream_t)stream>>>(m, node_in, seg, nbr, E, H, G, gT1);
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int b200mp_scatter_add_rows(const float* rows, const int32_t* idx, int64_t n, int H, float* out, void* stream) {
+    using namespace b200mp;
+    if (n < 0 || H < 4 || (H & 3)) return B200MP_EINVAL;
+    if (n == 0) return 0;
+    if (!rows || !idx || !out) return B200MP_EINVAL;
+    scatter_add_rows_kernel<<<rows_grid(n * (H / 4)), 256, 0, (cudaStream_t)stream>>>(rows, idx, n, H / 4, out);
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}

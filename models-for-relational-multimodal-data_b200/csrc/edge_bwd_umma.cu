@@ -189,16 +189,26 @@ __global__ void __launch_bounds__(NTB, 1) edge_update_bwd_umma_kernel(UpdBwdUArg
                 if (valid) accb2 = accb2 + Rg.v[i];
                 if (!ROWS && valid && a.gP) red_add4(a.gP + (int64_t)srow[i] * HH + j * 4, Gh[i]);
                 if (ROWS && valid) st4(a.gh_out + (row0 + r) * HH + j * 4, Gh[i]);
+                if (!SPLIT) {
+                    float4 gh, gl;
+                    split4(Gh[i], gh, gl);
+                    const int o = RG_T::off(r, j);
+                    st4(H_hi + o, gh);
+                    st4(H_lo + o, gl);
+                }
             }
             if (!ROWS && a.gQ) red_runs(a.gQ, drow, Gh, j, lane);
-            if (SPLIT) { mbar_wait(&bar[2], par); fence_after(); }    // GW2 has read the g and h tiles: both may be overwritten
+            if (SPLIT) {
+                mbar_wait(&bar[2], par);                 // GW2 has read the g and h tiles: both may be overwritten
+                fence_after();
 #pragma unroll
-            for (int i = 0; i < NP; ++i) {
-                float4 gh, gl;
-                split4(Gh[i], gh, gl);
-                const int o = RG_T::off(g * NP + i, j);
-                st4(H_hi + o, gh);
-                st4(H_lo + o, gl);
+                for (int i = 0; i < NP; ++i) {
+                    float4 gh, gl;
+                    split4(Gh[i], gh, gl);
+                    const int o = RG_T::off(g * NP + i, j);
+                    st4(H_hi + o, gh);
+                    st4(H_lo + o, gl);
+                }
             }
         }
         if (!SPLIT) group_sync(grp);                     // every thread is done reading the staged U rows
@@ -267,9 +277,11 @@ static int launch_upd_bwd_umma_t(int64_t E, const T* g_out, const T* h, const T*
                                  float* gW1_part, float* gb1_part, float* gW2_part, float* gb2_part, int n_part,
                                  const int32_t* g_eid, const int32_t* e_eid, cudaStream_t st, float* gh_out) {
     UpdBwdUArgs<T> a{E, g_out, h, e, src, dst, W1, W2, alpha, beta, g_e, gP, gQ, gW1_part, gb1_part, gW2_part, gb2_part, g_eid, e_eid, gh_out};
-    // B200MP_UPD_BWD_SPLIT=0 selects the single-barrier phases (round-2 baseline) for the same-box A/B
+    // B200MP_UPD_BWD_SPLIT=1 selects the split-barrier phases.  OPT-IN: same-box A/B on hi_medium 16.2 ms against 13.8 ms -- the
+    // tensor-memory reads of the epilogue queue behind the weight-gradient MMAs they were meant to overlap, and every thread
+    // polls four mbarriers per tile instead of two
     const char* sv = getenv("B200MP_UPD_BWD_SPLIT");
-    const bool split = !(sv && sv[0] == '0');
+    const bool split = sv && sv[0] == '1';
     const size_t smem = (split ? 10 : 8) * dual::RG_T::BYTES + 4 * WT::BYTES + 1024;
     auto kern = split ? (gh_out ? edge_update_bwd_umma_kernel<T, true, true> : edge_update_bwd_umma_kernel<T, false, true>)
                       : (gh_out ? edge_update_bwd_umma_kernel<T, true, false> : edge_update_bwd_umma_kernel<T, false, false>);

@@ -39,6 +39,22 @@ struct NodeLinArgs {
     const float* X1; const float* X2;         // segmented input: columns 64 s .. 64 s + 63 of X come from X<s>, each [N, 64]
     int ysplit;                               // output as NO / 64 separate [N, 64] blocks (Y + g N 64) instead of [N, NO]
 };
+// Row epilogue of b200mp_row_linear (the per-edge linears at H = 128 run on this kernel): for tile row k
+//   z = X[xrow[k]] W^T + bias + T1[idx1[k]] + T2[idx2[k]];  relu: z = max(z, 0);  mask: z = z * [mask[k] > 0]
+//   Y[orow[k]] = alpha R[rrow[k]] + beta z + R2[k]
+// every pointer nullable (row maps null = k); R may alias Y when rrow == orow (each element is read and written by one thread).
+struct RowEpi {
+    const int32_t* xrow;
+    const float* T1; const int32_t* idx1;
+    const float* T2; const int32_t* idx2;
+    const float* mask;
+    const float* R; const int32_t* rrow;
+    const float* R2;
+    const int32_t* orow;
+    float alpha, beta;
+    int relu;
+};
+struct NoEpi {};
 }  // namespace ng
 using namespace ng;
 
@@ -48,8 +64,8 @@ using namespace ng;
 // c - 1's MMAs run, and chunk c's X panel is split and stored while they run too -- the serial version
 // (two CTAs per SM, single buffers) spent ~3.4 us per chunk for 0.6 us of tensor work, mostly waiting for
 // the 48-64 KB weight copy from L2.
-template <int NO>
-__global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a) {
+template <int NO, bool EPI = false>
+__global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a, typename std::conditional<EPI, RowEpi, NoEpi>::type ep) {
     constexpr int W_PART = NO * KCH;                       // floats per hi (or lo) weight chunk
     constexpr int W_BUF = 2 * W_PART;                      // hi + lo
     extern __shared__ __align__(128) float smem_raw[];
@@ -92,8 +108,10 @@ __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a)
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int rc = min(g8 * 4 + i, nr - 1);
-            const float* xb = a.X1 ? (pf_c < 2 ? a.X : pf_c < 4 ? a.X1 : a.X2) + (r0 + rc) * 64 + (pf_c & 1) * KCH
-                                   : a.X + (r0 + rc) * a.ldx + pf_c * KCH;
+            int64_t xr_ = r0 + rc;
+            if constexpr (EPI) { if (ep.xrow) xr_ = __ldg(ep.xrow + xr_); }
+            const float* xb = a.X1 ? (pf_c < 2 ? a.X : pf_c < 4 ? a.X1 : a.X2) + xr_ * 64 + (pf_c & 1) * KCH
+                                   : a.X + xr_ * a.ldx + pf_c * KCH;
             dst[i] = ldg4(xb + j8 * 4);
         }
         if (++pf_c == nchunks) { pf_c = 0; pf_tile += gridDim.x; }
@@ -163,16 +181,48 @@ __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a)
             fence_after();
         }
         float* stage = Xb;
+        int e_i1[8], e_i2[8], e_rr[8], e_or[8];   // EPI: row ids of this thread's 8 output rows (fetched once per tile)
+        if constexpr (EPI) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int64_t k = row0 + min(g * 8 + i, nrows - 1);
+                e_i1[i] = ep.idx1 ? __ldg(ep.idx1 + k) : 0;
+                e_i2[i] = ep.idx2 ? __ldg(ep.idx2 + k) : 0;
+                e_rr[i] = ep.rrow ? __ldg(ep.rrow + k) : (int)k;
+                e_or[i] = ep.orow ? __ldg(ep.orow + k) : (int)k;
+            }
+        }
 #pragma unroll 1
         for (int grp = 0; grp < NO / 64; ++grp) {
             stage_from_tmem<NT2>(tm + lane_off + grp * 64 + ch * 32, stage, t, ch);
             __syncthreads();
             const float4 b4 = a.bias ? ldg4(a.bias + grp * 64 + j * 4) : f4(0.f, 0.f, 0.f, 0.f);
+            if constexpr (EPI) {
+                const int co = grp * 64 + j * 4;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int r = g * 8 + i;
-                float* yo = a.ysplit ? a.Y + ((int64_t)grp * a.N + row0 + r) * 64 : a.Y + (row0 + r) * NO + grp * 64;
-                if (r < nrows) st4(yo + j * 4, lds4(stage + stage_off(r, j)) + b4);
+                for (int i = 0; i < 8; ++i) {
+                    const int r = g * 8 + i;
+                    if (r >= nrows) continue;
+                    float4 v = lds4(stage + stage_off(r, j)) + b4;
+                    if (ep.T1) v = v + ldg4(ep.T1 + (int64_t)e_i1[i] * NO + co);
+                    if (ep.T2) v = v + ldg4(ep.T2 + (int64_t)e_i2[i] * NO + co);
+                    if (ep.relu) v = relu4(v);
+                    if (ep.mask) {
+                        const float4 mk = ldg4(ep.mask + (row0 + r) * NO + co);
+                        v = f4(mk.x > 0.f ? v.x : 0.f, mk.y > 0.f ? v.y : 0.f, mk.z > 0.f ? v.z : 0.f, mk.w > 0.f ? v.w : 0.f);
+                    }
+                    v = ep.beta * v;
+                    if (ep.R) v = v + ep.alpha * ld_e4(ep.R + (int64_t)e_rr[i] * NO + co);      // may alias Y: plain load
+                    if (ep.R2) v = v + ldg4(ep.R2 + (row0 + r) * NO + co);
+                    st4(a.Y + (int64_t)e_or[i] * NO + co, v);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int r = g * 8 + i;
+                    float* yo = a.ysplit ? a.Y + ((int64_t)grp * a.N + row0 + r) * 64 : a.Y + (row0 + r) * NO + grp * 64;
+                    if (r < nrows) st4(yo + j * 4, lds4(stage + stage_off(r, j)) + b4);
+                }
             }
             __syncthreads();
         }
@@ -188,11 +238,22 @@ __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a)
 template <int NO>
 static int launch_node_linear(const NodeLinArgs& a, cudaStream_t st) {
     const size_t smem = 4 * XP::BYTES + 2 * (2 * NO * KCH * 4) + 1024;    // X panels and weight chunks, double buffered
-    auto kern = node_linear_umma_kernel<NO>;
+    auto kern = node_linear_umma_kernel<NO, false>;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ntiles = (a.N + TE - 1) / TE;
     const int grid = persistent_grid((const void*)kern, smem, ntiles, NT2);
-    kern<<<grid, NT2, smem, st>>>(a);
+    kern<<<grid, NT2, smem, st>>>(a, NoEpi{});
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}
+template <int NO>
+static int launch_row_linear(const NodeLinArgs& a, const RowEpi& ep, cudaStream_t st) {
+    const size_t smem = 4 * XP::BYTES + 2 * (2 * NO * KCH * 4) + 1024;
+    auto kern = node_linear_umma_kernel<NO, true>;
+    B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t ntiles = (a.N + TE - 1) / TE;
+    const int grid = persistent_grid((const void*)kern, smem, ntiles, NT2);
+    kern<<<grid, NT2, smem, st>>>(a, ep);
     B200MP_LAUNCH_CHECK();
     return 0;
 }
@@ -377,6 +438,29 @@ extern "C" int b200mp_node_linear64(const float* X0, const float* X1, const floa
         case 128: return launch_node_linear<128>(a, st);
         case 192: return launch_node_linear<192>(a, st);
         case 256: return launch_node_linear<256>(a, st);
+    }
+    return B200MP_EINVAL;
+}
+
+/* Y[orow[k]] = alpha R[rrow[k]] + beta act(X[xrow[k]] W^T + bias + T1[idx1[k]] + T2[idx2[k]]) * [mask[k] > 0] + R2[k] over N rows: the
+ * per-edge linears of the message / edge-update forward and backward at widths the fused H = 64 kernels do not cover (H = 128:
+ * pna.py:50 default).  Same kernel, tiles and operand image as b200mp_node_linear; K % 32 == 0, NO in {64,128,192,256}; T1 / T2 / mask
+ * / R / R2 / Y rows are NO floats wide. */
+extern "C" int b200mp_row_linear(const float* X, const int32_t* xrow, int64_t N, int K, int ldx, const float* Wimg, int NO,
+                                 const float* bias, const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
+                                 int relu, const float* mask, const float* R, const int32_t* rrow, float alpha, float beta,
+                                 const float* R2, float* Y, const int32_t* orow, void* stream) {
+    using namespace b200mp;
+    if (N < 0 || K <= 0 || K % 32 || ldx < K || ldx % 4 || !X || !Wimg || !Y || (T1 && !idx1) || (T2 && !idx2)) return B200MP_EINVAL;
+    if (N == 0) return 0;
+    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0};
+    RowEpi ep{xrow, T1, idx1, T2, idx2, mask, R, rrow, R2, orow, alpha, beta, relu};
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (NO) {
+        case 64: return launch_row_linear<64>(a, ep, st);
+        case 128: return launch_row_linear<128>(a, ep, st);
+        case 192: return launch_row_linear<192>(a, ep, st);
+        case 256: return launch_row_linear<256>(a, ep, st);
     }
     return B200MP_EINVAL;
 }

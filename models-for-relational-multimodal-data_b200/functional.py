@@ -345,6 +345,8 @@ class _LinearGroup(torch.autograd.Function):
 
 def linear_group(x, weights, biases):
     """[x W^T + b for W, b in zip(weights, biases)] (b may be None) as one autograd node."""
+    if x.dim() == 2 and x.shape[1] != 64 and x.is_cuda and all(_node_kernel_ok(x.shape[0], W.shape[1], W.shape[0]) for W in weights):
+        return tuple(linear3x(x, W, b) for W, b in zip(weights, biases))      # H = 128: the general tcgen05 node kernel, one pass each
     return _LinearGroup.apply(x, len(weights), *weights, *biases)
 
 
@@ -391,6 +393,8 @@ def linear_cat(xs, W, b=None):
     if 1 <= len(xs) <= 3 and all(x.dim() == 2 and x.shape[1] == 64 and x.dtype == torch.float32 for x in xs) and xs[0].shape[0] >= 4096 \
             and tuple(W.shape) == (64, 64 * len(xs)):
         return _LinearCat.apply(W, b, *xs)
+    if all(x.dim() == 2 and x.is_cuda and x.dtype == torch.float32 for x in xs) and _node_kernel_ok(xs[0].shape[0], W.shape[1], W.shape[0]):
+        return linear3x(torch.cat(xs, dim=1), W, b)          # H = 128: the general tcgen05 node kernel over the concatenation
     return torch.nn.functional.linear(torch.cat(xs, dim=1), W, b)
 
 
@@ -400,9 +404,96 @@ def linear3x(x, W, b=None):
     return _Linear3x.apply(x, W, b)
 
 
+# ----------------------------------------------------------------------------- H = 128 on the tensor cores
+def wide_tc_available(H: int) -> bool:
+    """H = 128 (pna.py:50 default width): the per-edge products run on the tcgen05 row-linear kernel (b200mp_row_linear: the node
+    GEMM kernel with gathers / activation / mask / residual in its epilogue) and the weight gradients on b200mp_node_linear_wgrad,
+    composed here; B200MP_SIMT=1 or B200MP_TC128=0 selects the fused SIMT kernels of edge_fwd.cu / edge_bwd.cu instead."""
+    import os
+    return H == 128 and row_maps_available() and os.environ.get("B200MP_TC128", "1") != "0"
+
+
+def _row_linear(x, W, b=None, *, xrow=None, T1=None, idx1=None, T2=None, idx2=None, relu=False, mask=None, R=None, rrow=None,
+                alpha=0.0, beta=1.0, R2=None, out=None, orow=None):
+    """out[orow[k]] = alpha R[rrow[k]] + beta act(x[xrow[k]] W^T + b + T1[idx1[k]] + T2[idx2[k]]) * [mask[k] > 0] + R2[k]"""
+    N = x.shape[0] if xrow is None else xrow.numel()
+    K, NO = x.shape[1], W.shape[0]
+    if out is None:
+        out = torch.empty((N, NO), dtype=torch.float32, device=x.device)
+    img = _w_image(W)
+    L.check(L.lib().b200mp_row_linear(L.ptr(x), L.ptr(xrow), N, K, K, L.ptr(img), NO, L.ptr(b), L.ptr(T1), L.ptr(idx1), L.ptr(T2),
+                                      L.ptr(idx2), 1 if relu else 0, L.ptr(mask), L.ptr(R), L.ptr(rrow), float(alpha), float(beta),
+                                      L.ptr(R2), L.ptr(out), L.ptr(orow), L.stream()), "b200mp_row_linear")
+    return out
+
+
+def _rows_wgrad(a, b):
+    """a^T b over the E rows ([E,Ka], [E,Kb] -> [Ka,Kb]) on the tcgen05 weight-gradient kernel; few rows: library GEMM"""
+    if a.shape[0] == 0:
+        return a.new_zeros((a.shape[1], b.shape[1]))
+    npart = torch.cuda.get_device_properties(a.device).multi_processor_count
+    part = torch.empty((npart, a.shape[1], b.shape[1]), dtype=torch.float32, device=a.device)
+    L.check(L.lib().b200mp_node_linear_wgrad(L.ptr(a), a.shape[1], a.shape[1], L.ptr(b), b.shape[1], b.shape[1], a.shape[0],
+                                             L.ptr(part), npart, L.stream()), "b200mp_node_linear_wgrad")
+    return part.sum(0)
+
+
+def _edge_linear_fwd_wide(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out_eid):
+    name = ("pna_message_fwd", "gine_message_fwd", "edge_update_fwd")[mode]
+    with torch.cuda.device(e.device), _track(name, 2 if mode == 2 else 1):
+        out1 = _row_linear(e, W1, b1, xrow=eid, T1=T1, idx1=idx1 if T1 is not None else None, T2=T2,
+                           idx2=idx2 if T2 is not None else None, relu=mode >= 1)
+        out2 = None
+        if mode == 2:                            # e'[out_eid[k]] = alpha e[eid[k]] + beta (h_k W2^T + b2)
+            out2 = _row_linear(out1, W2, b2, R=e, rrow=eid, alpha=alpha, beta=beta, orow=out_eid)
+    return out1, out2
+
+
+def _message_bwd_wide(kind, seg, m, e, node_in, W, need_T1, N, g_e, accumulate, g_acc, eid):
+    E, H = m.shape
+    dev = m.device
+    det = deterministic_backward()
+    with torch.cuda.device(dev), _track("pna_message_bwd" if kind == 0 else "gine_message_bwd", 3):
+        G = torch.empty((E, H), dtype=torch.float32, device=dev)
+        gT1 = torch.zeros((N, H), dtype=torch.float32, device=dev) if (need_T1 and not det) else None
+        L.check(L.lib().b200mp_message_grad_rows(kind, H, E, L.ptr(m), L.ptr(node_in), L.ptr(seg.seg32), L.ptr(seg.nbr32), L.ptr(G),
+                                                 L.ptr(gT1), L.stream()), "b200mp_message_grad_rows")
+        # g_e[eid[k]] (+)= G_k W (+ g_acc[k])
+        _row_linear(G, W.t(), None, R=g_e if accumulate else None, rrow=eid, alpha=1.0, beta=1.0, R2=g_acc, out=g_e, orow=eid)
+        e_rows = e if eid is None else _permute(e, eid.long(), False)
+        gW = _rows_wgrad(G, e_rows)
+    if need_T1 and det:
+        gT1 = _sum_rows_by_neighbour(seg, G, N)
+    return g_e, gT1, gW, G.sum(0)
+
+
+def _edge_update_bwd_wide(st, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q, nP, nQ, g_eid, e_eid):
+    E, H = e.shape
+    dev = e.device
+    det = deterministic_backward()
+    with torch.cuda.device(dev), _track("edge_update_bwd", 4):
+        Gh = _row_linear(g_out, W2.t(), None, xrow=g_eid, mask=h, beta=beta)               # beta (g W2) [h > 0]
+        g_e = _row_linear(Gh, W1.t(), None, R=g_out, rrow=g_eid, alpha=alpha, beta=1.0)     # alpha g + Gh W1
+        g_rows = g_out if g_eid is None else _permute(g_out, g_eid.long(), False)
+        e_rows = e if e_eid is None else _permute(e, e_eid.long(), False)
+        gW2 = _rows_wgrad(g_rows, h) * beta
+        gW1 = _rows_wgrad(Gh, e_rows)
+        gP = gQ = None
+        if need_P and not det:
+            gP = torch.zeros((nP or st.num_nodes, H), dtype=torch.float32, device=dev)
+            L.check(L.lib().b200mp_scatter_add_rows(L.ptr(Gh), L.ptr(st.src32), E, H, L.ptr(gP), L.stream()), "b200mp_scatter_add_rows")
+    if need_Q:                                   # destination-sorted: a segmented sum, no atomics
+        gQ = _segment_sum_rows(st.fwd, Gh)[: (nQ or st.num_nodes)]
+    if need_P and det:
+        gP = _sum_rows_by_neighbour(st.fwd, Gh, nP or st.num_nodes)
+    return g_e, gP, gQ, gW1, Gh.sum(0), gW2, g_rows.sum(0) * beta
+
+
 # ----------------------------------------------------------------------------- raw launches
 def _edge_linear_fwd(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2=None, b2=None, alpha=0.0, beta=0.0, out_eid=None):
     E, H = e.shape
+    if e.dtype == torch.float32 and E > 0 and wide_tc_available(H):
+        return _edge_linear_fwd_wide(mode, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out_eid)
     out1 = torch.empty((E, H), dtype=e.dtype, device=e.device)
     out2 = torch.empty((E, H), dtype=e.dtype, device=e.device) if mode == 2 else None
     if e.dtype == torch.bfloat16:
@@ -539,6 +630,8 @@ def _message_bwd(kind, seg: SegmentIndex, m, e, node_in, W, need_T1, N, g_e=None
         accumulate = 1
     if g_e is None:
         g_e = torch.empty((E, H), dtype=m.dtype, device=dev)
+    if m.dtype == torch.float32 and E > 0 and wide_tc_available(H):
+        return _message_bwd_wide(kind, seg, m, e, node_in, W, need_T1, N, g_e, accumulate, g_acc, eid)
     npart = L.n_part(E, H)
     if m.dtype == torch.bfloat16:
         _bf16_ok(m)
@@ -568,6 +661,8 @@ def _edge_update_bwd(st: EdgeStructure, g_out, h, e, W1, W2, alpha, beta, need_P
                      g_eid=None, e_eid=None):
     E, H = e.shape
     dev = e.device
+    if e.dtype == torch.float32 and E > 0 and wide_tc_available(H):
+        return _edge_update_bwd_wide(st, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q, nP, nQ, g_eid, e_eid)
     g_e = torch.empty((E, H), dtype=e.dtype, device=dev)
     npart = L.n_part(E, H)
     gW1 = torch.empty((npart, H, H), dtype=torch.float32, device=dev)

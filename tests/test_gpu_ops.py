@@ -131,7 +131,7 @@ def test_edge_kernels_vs_emulation(H):
     o1, o2 = BF._edge_linear_fwd(2, d(E_), p32, d(W1), d(b1), d(B), st.src32, d(A), st.dst32, d(W2), d(b2), 1.0, 0.5, p32)
     r1, r2 = EM.edge_linear_fwd(2, E_, p32.cpu(), W1, b1, B, stc.src32, A, stc.dst32, W2, b2, 1.0, 0.5, p32.cpu())
     assert rel_err(o1, r1) < 2e-6 and rel_err(o2, r2) < 2e-6
-    if H == 64:
+    if H in (64, 128):          # row maps in the backward: the tensor-core paths (fused kernels at 64, the row-linear composition at 128)
         got = BF._edge_update_bwd(st, d(gout), h, d(E_), d(W1), d(W2), 1.0, 0.5, True, True, None, None, p32, p32)
         ref = EM.edge_update_bwd(stc, gout, h.cpu(), E_, W1, W2, 1.0, 0.5, True, True, None, None, p32.cpu(), p32.cpu())
         for a, b, nm in zip(got, ref, ("g_e", "gP", "gQ", "gW1", "gb1", "gW2", "gb2")):
@@ -160,3 +160,62 @@ def test_permute_roundtrip_and_empty():
     agg, tie = BF.pna_aggregate(torch.zeros(5, 32, device=DEV), torch.zeros(5, 32, device=DEV), torch.zeros(0, 32, device=DEV),
                                 torch.eye(32, device=DEV), torch.zeros(32, device=DEV), st.fwd)
     assert agg.shape == (5, 128) and float(agg.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("e,n", [(1, 3), (127, 40), (128, 40), (4097, 300), (300_001, 20_000)])
+@pytest.mark.parametrize("det", [False, True])
+def test_wide_tensor_core_path_equals_simt(e, n, det):
+    """H = 128: the tcgen05 composition (b200mp_row_linear + b200mp_message_grad_rows + b200mp_node_linear_wgrad; functional.wide_tc_available)
+    against the fused SIMT kernels it replaces (B200MP_TC128=0) on the same inputs: forward modes 0 / 1 / 2, both message backward kinds with
+    and without an incoming gradient, the edge-update backward; then the row-mapped forms of the composition (the SIMT backward kernels take
+    none) against the unmapped ones on pre-permuted inputs -- 3xTF32 against fp32 FFMA"""
+    import os
+    H = 128
+    g = torch.Generator(device=DEV).manual_seed(e)
+    rnd = lambda *s: torch.randn(*s, device=DEV, generator=g)
+    ei = torch.stack([torch.randint(0, n, (e,), device=DEV, generator=g), (torch.rand(e, device=DEV, generator=g) ** 3 * n).long().clamp_(max=n - 1)])
+    st = b200mp.edge_structure(ei, n)
+    seg = st.fwd
+    p32 = seg.perm32()
+    pl = p32.long()
+    E_, A, B = rnd(e, H), rnd(n, H), rnd(n, H)
+    W1, b1, W2, b2 = rnd(H, H) / H ** 0.5, rnd(H), rnd(H, H) / H ** 0.5, rnd(H)
+    coef = torch.cat([rnd(n, H) for _ in range(7)], 1)
+    acc, gout = rnd(e, H), rnd(e, H)
+
+    def run(ea, go, maps):
+        """every output in segment order; maps: read / write the caller's order through p32 (inputs un-permuted)"""
+        eid = p32 if maps else None
+        out = []
+        for mode in (0, 1, 2):
+            o1, o2 = BF._edge_linear_fwd(mode, ea, eid, W1, b1, B, seg.nbr32, A, seg.seg32, W2 if mode == 2 else None,
+                                         b2 if mode == 2 else None, 0.5, 0.25, eid if mode == 2 else None)
+            out += [o1] + ([o2[pl] if maps else o2] if mode == 2 else [])
+        m, h = out[0], out[2]
+        agg, _ = BF._segment_reduce(0, seg, m, H)          # PNA min / max rows tied to the messages: the equality branches fire
+        cf = coef.clone()
+        cf[:, 3 * H:4 * H] = agg[:, H:2 * H]
+        cf[:, 5 * H:6 * H] = agg[:, 2 * H:3 * H]
+        for kind, node_in in ((0, cf), (1, A)):
+            for g_e in (None, acc):
+                r = list(BF._message_bwd(kind, seg, m, ea, node_in, W1, True, n, None if g_e is None else g_e.clone(), eid))
+                if maps:
+                    r[0] = r[0][pl]
+                out += r
+        out += list(BF._edge_update_bwd(st, go, h, ea, W1, W2, 1.0, 0.5, True, True, None, None, eid, eid))
+        return out
+
+    BF.set_deterministic(det)
+    try:
+        os.environ["B200MP_TC128"] = "0"
+        ref = run(E_[pl].contiguous(), gout[pl].contiguous(), False)
+        os.environ["B200MP_TC128"] = "1"
+        got = run(E_[pl].contiguous(), gout[pl].contiguous(), False)
+        got_mapped = run(E_, gout, True)
+    finally:
+        os.environ.pop("B200MP_TC128", None)
+        BF.set_deterministic(None)
+    assert len(ref) == len(got) == len(got_mapped)
+    for i, (a, b, c) in enumerate(zip(got, ref, got_mapped)):
+        assert a.shape == b.shape and rel_err(a, b) < 1e-5, (i, rel_err(a, b))
+        assert c.shape == b.shape and rel_err(c, b) < 1e-5, ("mapped", i, rel_err(c, b))
