@@ -77,7 +77,7 @@ int b200mp_scatter_rows(const float* in, const int64_t* idx, float* out, int64_t
 int b200mp_split_tf32(const float* x, float* hi, float* lo, int64_t n, void* stream);
 
 /* Node-level linear on the tensor cores (tcgen05, 3xTF32; fp32 accuracy ~1e-7), one pass over HBM:
- *   Y[N, NO] = X[N, K] W^T (+ bias)         X rows at stride ldx floats; K % 32 == 0; NO in {128,192,256}
+ *   Y[N, NO] = X[N, K] W^T (+ bias)         X rows at stride ldx floats; K % 32 == 0; NO in {64,128,192,256}
  * Wimg is the weight pre-split and pre-tiled by the caller (tiny): [K/32][2 (hi, lo)][8][NO][4] floats,
  * Wimg[c][p][q][n][i] = part_p(W[n][32 c + 4 q + i]) with hi = W rounded to tf32, lo = W - hi.
  * Replaces torch addmm at PyG PNAConv.update's post_nn (pna.py:71-79) and, with W^T, its data gradient. */

@@ -391,6 +391,7 @@ extern "C" int b200mp_node_linear(const float* X, int64_t N, int K, int ldx, con
     NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0};
     cudaStream_t st = (cudaStream_t)stream;
     switch (NO) {
+        case 64: return launch_node_linear<64>(a, st);
         case 128: return launch_node_linear<128>(a, st);
         case 192: return launch_node_linear<192>(a, st);
         case 256: return launch_node_linear<256>(a, st);

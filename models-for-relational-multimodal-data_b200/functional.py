@@ -185,7 +185,7 @@ def _w_image(W):
 
 def _node_kernel_ok(rows, K, NO):
     """Y[rows, NO] = X[rows, K] W^T on the tcgen05 node kernel (node_gemm_umma.cu)."""
-    return rows >= 4096 and K % 32 == 0 and K >= 128 and NO in (128, 192, 256)
+    return rows >= 4096 and K % 32 == 0 and K >= 128 and NO in (64, 128, 192, 256)
 
 
 def _node_linear(x, W, b):

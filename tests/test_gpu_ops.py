@@ -108,7 +108,10 @@ def test_edge_kernels_vs_emulation(H):
         assert torch.equal(tie.cpu(), rtie)
         assert torch.equal(agg[:, H:3 * H].cpu(), ragg[:, H:3 * H])            # min / max exact
         assert rel_err(agg[:, :H], ragg[:, :H]) < 2e-6
-        assert rel_err(agg[:, 3 * H:], ragg[:, 3 * H:]) < 1e-4
+        # std = sqrt(relu(E[m^2] - mean^2) + 1e-5): where the variance vanishes (one-edge segments) the square root turns a 1e-7
+        # rounding difference of the variance into ~1e-4 of the std, so the 1e-5 bound is checked on the variance, the std loosely
+        assert rel_err(agg[:, 3 * H:] ** 2, ragg[:, 3 * H:] ** 2) < 1e-5
+        assert rel_err(agg[:, 3 * H:], ragg[:, 3 * H:]) < 1e-3
         s, _ = BF._segment_reduce(1, seg, m, H)
         rs, _ = EM.segment_reduce(1, segc, m.cpu(), H)
         assert rel_err(s, rs) < 2e-6
