@@ -40,18 +40,21 @@ struct NodeLinArgs {
     int ysplit;                               // output as NO / 64 separate [N, 64] blocks (Y + g N 64) instead of [N, NO]
 };
 // Row epilogue of b200mp_row_linear (the per-edge linears at H = 128 run on this kernel): for tile row k
-//   z = X[xrow[k]] W^T + bias + T1[idx1[k]] + T2[idx2[k]];  relu: z = max(z, 0);  mask: z = z * [mask[k] > 0]
-//   Y[orow[k]] = alpha R[rrow[k]] + beta z + R2[k]
-// every pointer nullable (row maps null = k); R may alias Y when rrow == orow (each element is read and written by one thread).
+//   z = X[xrow[k]] W^T + bias + [pre-addend rows];  relu: z = max(z, 0);  [mask rows]: z = z * [mask > 0]
+//   Y[orow[k]] = beta z + [post-addend rows * coef]
+// The addend / mask rows come through two generic slots (pointer, optional row map, role), fetched into registers BEFORE the
+// accumulator is staged, so that their latency overlaps the tensor-memory reads instead of following them.  A post-addend may
+// alias Y when its row map equals orow (each element is read and written by one thread).
+struct EpiSlot {
+    const float* p; const int32_t* idx;       // rows of NO floats; idx null = tile row k
+    int role;                                 // 0 unused | 1 added before the activation | 2 mask | 3 added after, times coef
+    float coef;
+};
 struct RowEpi {
     const int32_t* xrow;
-    const float* T1; const int32_t* idx1;
-    const float* T2; const int32_t* idx2;
-    const float* mask;
-    const float* R; const int32_t* rrow;
-    const float* R2;
+    EpiSlot s0, s1;
     const int32_t* orow;
-    float alpha, beta;
+    float beta;
     int relu;
 };
 struct NoEpi {};
@@ -131,6 +134,16 @@ __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a,
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int64_t row0 = tile * TE;
         const int nrows = (int)min64(TE, a.N - row0);
+        int e_r0[8], e_r1[8], e_or[8];            // EPI: row ids of this thread's 8 output rows (clamped), fetched ahead of the K loop
+        if constexpr (EPI) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int64_t k = row0 + min(g * 8 + i, nrows - 1);
+                e_r0[i] = (ep.s0.role && ep.s0.idx) ? __ldg(ep.s0.idx + k) : (int)k;
+                e_r1[i] = (ep.s1.role && ep.s1.idx) ? __ldg(ep.s1.idx + k) : (int)k;
+                e_or[i] = ep.orow ? __ldg(ep.orow + k) : (int)k;
+            }
+        }
         for (int c = 0; c < nchunks; ++c, ++gc) {
             const int b = (int)(gc & 1);
             const uint32_t ph = (uint32_t)((gc >> 1) & 1);            // phase of buffer b's barriers at their use number gc / 2
@@ -181,19 +194,17 @@ __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a,
             fence_after();
         }
         float* stage = Xb;
-        int e_i1[8], e_i2[8], e_rr[8], e_or[8];   // EPI: row ids of this thread's 8 output rows (fetched once per tile)
-        if constexpr (EPI) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int64_t k = row0 + min(g * 8 + i, nrows - 1);
-                e_i1[i] = ep.idx1 ? __ldg(ep.idx1 + k) : 0;
-                e_i2[i] = ep.idx2 ? __ldg(ep.idx2 + k) : 0;
-                e_rr[i] = ep.rrow ? __ldg(ep.rrow + k) : (int)k;
-                e_or[i] = ep.orow ? __ldg(ep.orow + k) : (int)k;
-            }
-        }
 #pragma unroll 1
         for (int grp = 0; grp < NO / 64; ++grp) {
+            float4 e_a0[8], e_a1[8];             // EPI: the slots' rows of this column group, in flight while the accumulator is staged
+            if constexpr (EPI) {
+                const int co = grp * 64 + j * 4;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    if (ep.s0.role) e_a0[i] = ld_e4(ep.s0.p + (int64_t)e_r0[i] * NO + co);
+                    if (ep.s1.role) e_a1[i] = ld_e4(ep.s1.p + (int64_t)e_r1[i] * NO + co);
+                }
+            }
             stage_from_tmem<NT2>(tm + lane_off + grp * 64 + ch * 32, stage, t, ch);
             __syncthreads();
             const float4 b4 = a.bias ? ldg4(a.bias + grp * 64 + j * 4) : f4(0.f, 0.f, 0.f, 0.f);
@@ -202,19 +213,16 @@ __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a,
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int r = g * 8 + i;
-                    if (r >= nrows) continue;
                     float4 v = lds4(stage + stage_off(r, j)) + b4;
-                    if (ep.T1) v = v + ldg4(ep.T1 + (int64_t)e_i1[i] * NO + co);
-                    if (ep.T2) v = v + ldg4(ep.T2 + (int64_t)e_i2[i] * NO + co);
+                    if (ep.s0.role == 1) v = v + e_a0[i];
+                    if (ep.s1.role == 1) v = v + e_a1[i];
                     if (ep.relu) v = relu4(v);
-                    if (ep.mask) {
-                        const float4 mk = ldg4(ep.mask + (row0 + r) * NO + co);
-                        v = f4(mk.x > 0.f ? v.x : 0.f, mk.y > 0.f ? v.y : 0.f, mk.z > 0.f ? v.z : 0.f, mk.w > 0.f ? v.w : 0.f);
-                    }
+                    if (ep.s0.role == 2) v = f4(e_a0[i].x > 0.f ? v.x : 0.f, e_a0[i].y > 0.f ? v.y : 0.f, e_a0[i].z > 0.f ? v.z : 0.f, e_a0[i].w > 0.f ? v.w : 0.f);
+                    if (ep.s1.role == 2) v = f4(e_a1[i].x > 0.f ? v.x : 0.f, e_a1[i].y > 0.f ? v.y : 0.f, e_a1[i].z > 0.f ? v.z : 0.f, e_a1[i].w > 0.f ? v.w : 0.f);
                     v = ep.beta * v;
-                    if (ep.R) v = v + ep.alpha * ld_e4(ep.R + (int64_t)e_rr[i] * NO + co);      // may alias Y: plain load
-                    if (ep.R2) v = v + ldg4(ep.R2 + (row0 + r) * NO + co);
-                    st4(a.Y + (int64_t)e_or[i] * NO + co, v);
+                    if (ep.s0.role == 3) v = v + ep.s0.coef * e_a0[i];
+                    if (ep.s1.role == 3) v = v + ep.s1.coef * e_a1[i];
+                    if (r < nrows) st4(a.Y + (int64_t)e_or[i] * NO + co, v);
                 }
             } else {
 #pragma unroll
@@ -455,7 +463,17 @@ extern "C" int b200mp_row_linear(const float* X, const int32_t* xrow, int64_t N,
     if (N < 0 || K <= 0 || K % 32 || ldx < K || ldx % 4 || !X || !Wimg || !Y || (T1 && !idx1) || (T2 && !idx2)) return B200MP_EINVAL;
     if (N == 0) return 0;
     NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0};
-    RowEpi ep{xrow, T1, idx1, T2, idx2, mask, R, rrow, R2, orow, alpha, beta, relu};
+    EpiSlot slots[2] = {{nullptr, nullptr, 0, 0.f}, {nullptr, nullptr, 0, 0.f}};
+    int ns = 0;
+    auto add = [&](const float* p, const int32_t* idx, int role, float coef) {
+        if (!p) return true;
+        if (ns == 2) return false;
+        slots[ns++] = EpiSlot{p, idx, role, coef};
+        return true;
+    };
+    if (!add(T1, idx1, 1, 1.f) || !add(T2, idx2, 1, 1.f) || !add(mask, nullptr, 2, 1.f) || !add(R, rrow, 3, alpha) || !add(R2, nullptr, 3, 1.f))
+        return B200MP_EINVAL;                 // at most two of T1 / T2 / mask / R / R2 per call
+    RowEpi ep{xrow, slots[0], slots[1], orow, beta, relu};
     cudaStream_t st = (cudaStream_t)stream;
     switch (NO) {
         case 64: return launch_row_linear<64>(a, ep, st);

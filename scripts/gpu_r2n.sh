@@ -1,0 +1,5 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_ops.py -m gpu -q > gpurun_out/pytest_n.log 2>&1; grep -E "^FAILED|passed|failed|Error" gpurun_out/pytest_n.log | tail -12
+timeout 300 python scripts/kbench_row_linear.py > gpurun_out/kbench_row_linear.txt 2>&1; cat gpurun_out/kbench_row_linear.txt | tail -12
+B200MP_TC128=1 timeout 600 python bench.py --steps 5 --warmup 3 --no-e2e --no-cpu-baseline --workload hi_small --hidden 128 > gpurun_out/h128_1.json 2> gpurun_out/h128_1.err; echo "== hi_small H=128, tc128=1"; python scripts/benchsum.py gpurun_out/h128_1.json > gpurun_out/h128_1.txt; grep -E "ms/step|message|edge_update" gpurun_out/h128_1.txt
