@@ -186,15 +186,18 @@ def test_wide_tensor_core_path_equals_simt(e, n, det):
     coef = torch.cat([rnd(n, H) for _ in range(7)], 1)
     acc, gout = rnd(e, H), rnd(e, H)
 
-    def run(ea, go, maps):
-        """every output in segment order; maps: read / write the caller's order through p32 (inputs un-permuted)"""
+    def run(ea, go, maps, saved=None):
+        """every output in segment order; maps: read / write the caller's order through p32 (inputs un-permuted).  saved: the (m, h) the
+        backward kernels are given -- shared between the runs, because the backward rules branch on m == min / max and h > 0, and at
+        300 k edges x 128 columns a last-bit difference of the forward flips a handful of those (a whole gradient term moves to
+        another edge: 2e-2 of the tensor's scale, measured; tests/test_gpu_parity_scale.py has the kink-aware statistics)"""
         eid = p32 if maps else None
         out = []
         for mode in (0, 1, 2):
             o1, o2 = BF._edge_linear_fwd(mode, ea, eid, W1, b1, B, seg.nbr32, A, seg.seg32, W2 if mode == 2 else None,
                                          b2 if mode == 2 else None, 0.5, 0.25, eid if mode == 2 else None)
             out += [o1] + ([o2[pl] if maps else o2] if mode == 2 else [])
-        m, h = out[0], out[2]
+        m, h = (out[0], out[2]) if saved is None else saved
         agg, _ = BF._segment_reduce(0, seg, m, H)          # PNA min / max rows tied to the messages: the equality branches fire
         cf = coef.clone()
         cf[:, 3 * H:4 * H] = agg[:, H:2 * H]
@@ -213,14 +216,14 @@ def test_wide_tensor_core_path_equals_simt(e, n, det):
         os.environ["B200MP_TC128"] = "0"
         ref = run(E_[pl].contiguous(), gout[pl].contiguous(), False)
         os.environ["B200MP_TC128"] = "1"
-        got = run(E_[pl].contiguous(), gout[pl].contiguous(), False)
-        got_mapped = run(E_, gout, True)
+        got = run(E_[pl].contiguous(), gout[pl].contiguous(), False, (ref[0], ref[2]))
+        got_mapped = run(E_, gout, True, (ref[0], ref[2]))
     finally:
         os.environ.pop("B200MP_TC128", None)
         BF.set_deterministic(None)
     assert len(ref) == len(got) == len(got_mapped)
     # arbiter for the first message backward (PNA, no incoming gradient): the rule in fp64 torch on the composition's own m
-    m = got[0]
+    m = ref[0]
     cf = coef.clone()
     agg, _ = BF._segment_reduce(0, seg, m, H)
     cf[:, 3 * H:4 * H] = agg[:, H:2 * H]

@@ -138,30 +138,34 @@ def _backbone(kind, n, ei, H, seed, rev=False):
     return b200mp.GINe(num_features=H, num_gnn_layers=2, n_hidden=H, edge_updates=True, edge_dim=H, reverse_mp=rev)
 
 
+@pytest.mark.parametrize("H", [64, 128])
 @pytest.mark.parametrize("kind", ["pna", "gine"])
-def test_backbone_vs_oracle_node_kernels_active(kind):
-    """full forward (node_emb / edge_emb included) at N = 8192, E = 120 k: every node linear runs on the tcgen05 kernels"""
-    n, e, H = 8192, 120_000, 64
+def test_backbone_vs_oracle_node_kernels_active(kind, H):
+    """full forward (node_emb / edge_emb included) at N = 8192, E = 120 k: every node linear runs on the tcgen05 kernels; H = 128
+    (pna.py:50 default width) takes the row-linear composition for the per-edge products (functional.wide_tc_available)"""
+    n, e = 8192, 120_000
     ei = hub_graph(n, e, 11, 3000)
     g = torch.Generator().manual_seed(5)
     m = _backbone(kind, n, ei, H, 21)
     ins = {"x": torch.randn(n, H, generator=g), "edge_index": ei, "edge_attr": torch.randn(e, 1, H, generator=g)}
     fn = OM.pnas if kind == "pna" else OM.gine
-    _run_case(f"{kind} N=8192 E=120k H=64", m, lambda p, i: fn(p, i["x"], i["edge_index"], i["edge_attr"], 2, True, False),
+    _run_case(f"{kind} N=8192 E=120k H={H}", m, lambda p, i: fn(p, i["x"], i["edge_index"], i["edge_attr"], 2, True, False),
               lambda mod, i: mod(i["x"], i["edge_index"], i["edge_attr"]), ins, ("x", "edge_attr"), 3)
 
 
+@pytest.mark.parametrize("H", [64, 128])
 @pytest.mark.parametrize("kind", ["pna", "gine"])
-def test_reverse_mp_vs_oracle_node_kernels_active(kind):
+def test_reverse_mp_vs_oracle_node_kernels_active(kind, H):
     """reverse message passing (gine.py:28-35, pna.py:37-46) at N = 8192, E = 120 k: both convs through the row maps (no permutation
-    passes), `lin` over [x, a_in, a_out] on the node kernel without the concatenation"""
-    n, e, H = 8192, 120_000, 64
+    passes), `lin` over [x, a_in, a_out] on the node kernel without the concatenation (H = 64); H = 128: permuted storage, the
+    row-linear composition, `lin` over the concatenation on the general node kernel"""
+    n, e = 8192, 120_000
     ei = hub_graph(n, e, 12, 3000)
     g = torch.Generator().manual_seed(6)
     m = _backbone(kind, n, ei, H, 22, rev=True)
     ins = {"x": torch.randn(n, H, generator=g), "edge_index": ei, "edge_attr": torch.randn(e, 1, H, generator=g)}
     fn = OM.pnas if kind == "pna" else OM.gine
-    _run_case(f"{kind} reverse_mp N=8192 E=120k", m, lambda p, i: fn(p, i["x"], i["edge_index"], i["edge_attr"], 2, True, True),
+    _run_case(f"{kind} reverse_mp N=8192 E=120k H={H}", m, lambda p, i: fn(p, i["x"], i["edge_index"], i["edge_attr"], 2, True, True),
               lambda mod, i: mod(i["x"], i["edge_index"], i["edge_attr"]), ins, ("x", "edge_attr"), 5)
 
 
