@@ -83,6 +83,10 @@ int b200mp_split_tf32(const float* x, float* hi, float* lo, int64_t n, void* str
  * Replaces torch addmm at PyG PNAConv.update's post_nn (pna.py:71-79) and, with W^T, its data gradient. */
 int b200mp_node_linear(const float* X, int64_t N, int K, int ldx, const float* Wimg, int NO, const float* bias,
                        float* Y, void* stream);
+/* The same with the rows of Y at stride ldy >= NO floats: a call fills a column block of a wider output, so linears with more than
+ * 256 outputs (PNAConv post_nn at H = 128: 3 scalers x 128 = 384, its data gradient 512) are column blocks of <= 256. */
+int b200mp_node_linear_ld(const float* X, int64_t N, int K, int ldx, const float* Wimg, int NO, const float* bias,
+                          float* Y, int ldy, void* stream);
 /* Weight gradient of the above: part[p][k][n] = sum over the rows handled by CTA p of X[r][k] Y[r][n]
  * (K % 128 == 0, NO in {64,128,192,256}); the caller sums the n_part partials (deterministic). */
 int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const float* Y, int ldy, int NO, int64_t N,

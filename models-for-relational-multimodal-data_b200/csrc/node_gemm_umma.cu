@@ -38,6 +38,7 @@ struct NodeLinArgs {
     const float* X; const float* Wimg; const float* bias; float* Y;
     const float* X1; const float* X2;         // segmented input: columns 64 s .. 64 s + 63 of X come from X<s>, each [N, 64]
     int ysplit;                               // output as NO / 64 separate [N, 64] blocks (Y + g N 64) instead of [N, NO]
+    int ldy;                                  // row stride of Y in floats (NO unless the call fills a column block of a wider output)
 };
 // Row epilogue of b200mp_row_linear (the per-edge linears at H = 128 run on this kernel): for tile row k
 //   z = X[xrow[k]] W^T + bias + [pre-addend rows];  relu: z = max(z, 0);  [mask rows]: z = z * [mask > 0]
@@ -228,7 +229,7 @@ __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a,
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
                     const int r = g * 8 + i;
-                    float* yo = a.ysplit ? a.Y + ((int64_t)grp * a.N + row0 + r) * 64 : a.Y + (row0 + r) * NO + grp * 64;
+                    float* yo = a.ysplit ? a.Y + ((int64_t)grp * a.N + row0 + r) * 64 : a.Y + (row0 + r) * a.ldy + grp * 64;
                     if (r < nrows) st4(yo + j * 4, lds4(stage + stage_off(r, j)) + b4);
                 }
             }
@@ -391,12 +392,12 @@ static int launch_node_wgrad(const NodeWgArgs& a, int n_part, cudaStream_t st) {
 
 }  // namespace b200mp
 
-extern "C" int b200mp_node_linear(const float* X, int64_t N, int K, int ldx, const float* Wimg, int NO, const float* bias,
-                                  float* Y, void* stream) {
+extern "C" int b200mp_node_linear_ld(const float* X, int64_t N, int K, int ldx, const float* Wimg, int NO, const float* bias,
+                                     float* Y, int ldy, void* stream) {
     using namespace b200mp;
-    if (N < 0 || K <= 0 || K % 32 || ldx < K || ldx % 4 || !X || !Wimg || !Y) return B200MP_EINVAL;
+    if (N < 0 || K <= 0 || K % 32 || ldx < K || ldx % 4 || ldy < NO || ldy % 4 || !X || !Wimg || !Y) return B200MP_EINVAL;
     if (N == 0) return 0;
-    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0};
+    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0, ldy};
     cudaStream_t st = (cudaStream_t)stream;
     switch (NO) {
         case 64: return launch_node_linear<64>(a, st);
@@ -405,6 +406,11 @@ extern "C" int b200mp_node_linear(const float* X, int64_t N, int K, int ldx, con
         case 256: return launch_node_linear<256>(a, st);
     }
     return B200MP_EINVAL;
+}
+
+extern "C" int b200mp_node_linear(const float* X, int64_t N, int K, int ldx, const float* Wimg, int NO, const float* bias,
+                                  float* Y, void* stream) {
+    return b200mp_node_linear_ld(X, N, K, ldx, Wimg, NO, bias, Y, NO, stream);
 }
 
 extern "C" int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const float* Y, int ldy, int NO, int64_t N,
@@ -440,7 +446,7 @@ extern "C" int b200mp_node_linear64(const float* X0, const float* X1, const floa
     using namespace b200mp;
     if (N < 0 || nx < 1 || nx > 3 || !X0 || (nx > 1 && !X1) || (nx > 2 && !X2) || !Wimg || !Y) return B200MP_EINVAL;
     if (N == 0) return 0;
-    NodeLinArgs a{N, 64 * nx, 64, X0, Wimg, bias, Y, nx > 1 ? X1 : X0, nx > 2 ? X2 : X0, ysplit};
+    NodeLinArgs a{N, 64 * nx, 64, X0, Wimg, bias, Y, nx > 1 ? X1 : X0, nx > 2 ? X2 : X0, ysplit, NO};
     cudaStream_t st = (cudaStream_t)stream;
     switch (NO) {
         case 64: return launch_node_linear<64>(a, st);
@@ -462,7 +468,7 @@ extern "C" int b200mp_row_linear(const float* X, const int32_t* xrow, int64_t N,
     using namespace b200mp;
     if (N < 0 || K <= 0 || K % 32 || ldx < K || ldx % 4 || !X || !Wimg || !Y || (T1 && !idx1) || (T2 && !idx2)) return B200MP_EINVAL;
     if (N == 0) return 0;
-    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0};
+    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0, NO};
     EpiSlot slots[2] = {{nullptr, nullptr, 0, 0.f}, {nullptr, nullptr, 0, 0.f}};
     int ns = 0;
     auto add = [&](const float* p, const int32_t* idx, int role, float coef) {

@@ -185,22 +185,28 @@ def _w_image(W):
 
 def _node_kernel_ok(rows, K, NO):
     """Y[rows, NO] = X[rows, K] W^T on the tcgen05 node kernel (node_gemm_umma.cu)."""
-    return rows >= 4096 and K % 32 == 0 and K >= 128 and NO in (64, 128, 192, 256)
+    return rows >= 4096 and K % 32 == 0 and K >= 128 and NO % 64 == 0 and 64 <= NO <= 1024
+
+
+def _col_blocks(NO):
+    """column blocks of <= 256 (the accumulator width of the node kernels) covering NO outputs"""
+    return [(c0, min(256, NO - c0)) for c0 in range(0, NO, 256)]
 
 
 def _node_linear(x, W, b):
     N, K = x.shape
     NO = W.shape[0]
     y = torch.empty((N, NO), dtype=torch.float32, device=x.device)
-    img = _w_image(W)
-    with torch.cuda.device(x.device), _track("node_linear"):
-        L.check(L.lib().b200mp_node_linear(L.ptr(x), N, K, K, L.ptr(img), NO, L.ptr(b), L.ptr(y), L.stream()),
-                "b200mp_node_linear")
+    for c0, nc in _col_blocks(NO):           # more than 256 outputs (post_nn at H = 128): column blocks of the same output
+        img = _w_image(W[c0:c0 + nc])
+        with torch.cuda.device(x.device), _track("node_linear"):
+            L.check(L.lib().b200mp_node_linear_ld(L.ptr(x), N, K, K, L.ptr(img), nc, L.ptr(None if b is None else b[c0:c0 + nc]),
+                                                  L.ptr(y[:, c0:]), NO, L.stream()), "b200mp_node_linear_ld")
     return y
 
 
 def _node_wgrad_ok(rows, K, NO):
-    return rows >= 4096 and K % 128 == 0 and NO in (64, 128, 192, 256)
+    return rows >= 4096 and K % 128 == 0 and NO % 64 == 0 and 64 <= NO <= 1024
 
 
 def _node_wgrad(x, y):
@@ -208,11 +214,14 @@ def _node_wgrad(x, y):
     N, K = x.shape
     NO = y.shape[1]
     npart = torch.cuda.get_device_properties(x.device).multi_processor_count
-    part = torch.empty((npart, K, NO), dtype=torch.float32, device=x.device)
-    with torch.cuda.device(x.device), _track("node_linear_wgrad"):
-        L.check(L.lib().b200mp_node_linear_wgrad(L.ptr(x), K, K, L.ptr(y), NO, NO, N, L.ptr(part), npart, L.stream()),
-                "b200mp_node_linear_wgrad")
-    return part.sum(0)
+    outs = []
+    for c0, nc in _col_blocks(NO):
+        part = torch.empty((npart, K, nc), dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device), _track("node_linear_wgrad"):
+            L.check(L.lib().b200mp_node_linear_wgrad(L.ptr(x), K, K, L.ptr(y[:, c0:]), NO, nc, N, L.ptr(part), npart, L.stream()),
+                    "b200mp_node_linear_wgrad")
+        outs.append(part.sum(0))
+    return outs[0] if len(outs) == 1 else torch.cat(outs, 1)
 
 
 class _Linear3x(torch.autograd.Function):

@@ -99,7 +99,7 @@ class _Backbone(_EdgeStorage, nn.Module):
         st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
         H = x.shape[1]
         e = self._store(e)
-        if H != 64 or not BF.row_maps_available():
+        if not (H == 64 or BF.wide_tc_available(H)) or not BF.row_maps_available():
             return self._layers_permuted(x, st, e)
         # e stays in the caller's edge order at both ends: the first layer's kernels read it through
         # the CSC permutation, the last edge update writes through it -- no permutation passes
@@ -284,7 +284,7 @@ class _ColumnStacks(nn.Module):
         x = self.node_emb(x.view(x.shape[0], -1))
         st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
         L = self.num_gnn_layers
-        fast = (not self.reverse_mp) and x.shape[1] == 64 and BF.row_maps_available()
+        fast = (not self.reverse_mp) and (x.shape[1] == 64 or BF.wide_tc_available(x.shape[1])) and BF.row_maps_available()
         perm32 = st.fwd.perm32() if fast else None
         cols = []
         for c in range(self.num_cols):

@@ -10,7 +10,7 @@ from tests.util import rel_err
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("N,K,NO", [(4096, 256, 192), (5000, 192, 256), (4097, 128, 128), (9999, 256, 256)])
+@pytest.mark.parametrize("N,K,NO", [(4096, 256, 192), (5000, 192, 256), (4097, 128, 128), (9999, 256, 256), (5003, 384, 64), (4999, 512, 384), (4100, 384, 512)])
 def test_node_linear(N, K, NO):
     g = torch.Generator(device="cuda").manual_seed(N + K)
     X = torch.randn(N, K, device="cuda", generator=g) * torch.logspace(-2, 2, K, device="cuda")
@@ -23,7 +23,7 @@ def test_node_linear(N, K, NO):
     assert err < 2e-6
 
 
-@pytest.mark.parametrize("N,K,NO", [(4096, 256, 192), (5001, 128, 64), (7777, 256, 256)])
+@pytest.mark.parametrize("N,K,NO", [(4096, 256, 192), (5001, 128, 64), (7777, 256, 256), (4999, 512, 384), (4100, 384, 512)])
 def test_node_wgrad(N, K, NO):
     g = torch.Generator(device="cuda").manual_seed(N + NO)
     X = torch.randn(N, K, device="cuda", generator=g)
@@ -35,9 +35,11 @@ def test_node_wgrad(N, K, NO):
     assert err < 2e-6
 
 
-def test_linear3x_autograd_matches_fp64():
+@pytest.mark.parametrize("N,K,NO", [(6000, 256, 192), (5000, 512, 384), (4500, 384, 64), (4500, 128, 128)])
+def test_linear3x_autograd_matches_fp64(N, K, NO):
+    """(5000, 512, 384): PNAConv post_nn at H = 128 -- more than 256 outputs, column blocks of one output (b200mp_node_linear_ld);
+    (4500, 384, 64): the [E, K C] -> [E, H] edge embedding; (4500, 128, 128): the H = 128 node linears"""
     g = torch.Generator(device="cuda").manual_seed(5)
-    N, K, NO = 6000, 256, 192
     x = torch.randn(N, K, device="cuda", generator=g, requires_grad=True)
     W = (torch.randn(NO, K, device="cuda", generator=g) / 16).requires_grad_(True)
     b = torch.randn(NO, device="cuda", generator=g, requires_grad=True)

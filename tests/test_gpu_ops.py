@@ -231,13 +231,17 @@ def test_wide_tensor_core_path_equals_simt(e, n, det):
     c = cf[seg.seg32.long()].double().view(e, 7, H)
     md = m.double()
     G64 = c[:, 1] * (md - c[:, 6]) + c[:, 0] + (md == c[:, 3]) * c[:, 2] + (md == c[:, 5]) * c[:, 4]
+    gW64 = G64.t() @ E_[pl].double()
     errs = {"arbiter g_e (wide)": rel_err(got[4], G64 @ W1.double()), "arbiter g_e (simt)": rel_err(ref[4], G64 @ W1.double()),
+            "arbiter gW (wide)": rel_err(got[6], gW64), "arbiter gW (simt)": rel_err(ref[6], gW64),
             "arbiter gb (wide)": rel_err(got[7], G64.sum(0)), "arbiter gb (simt)": rel_err(ref[7], G64.sum(0))}
     bad = {k: v for k, v in errs.items() if v > 1e-5 and "wide" in k}
+    # two fp32 evaluations of a sum over E rows (3xTF32 in tensor memory, drained every 1024 rows | FFMA in registers) each carry up
+    # to ~6e-6 against fp64 (profiles/r02_wgrad_chain_and_node_precision.txt): 1e-5 against the arbiter, 2e-5 against each other
     for i, (a, b, c_) in enumerate(zip(got, ref, got_mapped)):
         assert a.shape == b.shape == c_.shape
-        if rel_err(a, b) > 1e-5:
+        if rel_err(a, b) > 2e-5:
             bad[i] = rel_err(a, b)
-        if rel_err(c_, a) > 1e-5:
+        if rel_err(c_, a) > 2e-5:
             bad[("mapped", i)] = rel_err(c_, a)
     assert not bad, (bad, errs)
