@@ -91,6 +91,10 @@ int b200mp_node_linear_ld(const float* X, int64_t N, int K, int ldx, const float
  * (K % 128 == 0, NO in {64,128,192,256}); the caller sums the n_part partials (deterministic). */
 int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const float* Y, int ldy, int NO, int64_t N,
                              float* part, int n_part, void* stream);
+/* The same with row maps: reduction row r reads X[xrow[r]] and Y[yrow[r]] (NULL = r) -- the weight gradients of the H = 128 per-edge
+ * products pair gradient rows in segment order with edge features in the caller's order (b200mp_row_linear). */
+int b200mp_node_linear_wgrad_rows(const float* X, const int32_t* xrow, int ldx, int K, const float* Y, const int32_t* yrow,
+                                  int ldy, int NO, int64_t N, float* part, int n_part, void* stream);
 /* Several H = 64 node linears in one pass: X = [X0 | X1 | X2] (nx blocks of [N,64], e.g. the gradients of
  * A | B | out0), Y = X W^T + bias, NO in {64,128,192,256}; ysplit != 0 writes Y as NO/64 separate [N,64]
  * blocks (A, B, out0 of PNAConv's hoisted pre_nn / post_nn self term; P, Q of the edge update). */

@@ -42,6 +42,7 @@ _SIGS = {
     "b200mp_node_linear": [_p, _l, _i, _i, _p, _i, _p, _p, _p],
     "b200mp_node_linear_ld": [_p, _l, _i, _i, _p, _i, _p, _p, _i, _p],
     "b200mp_node_linear_wgrad": [_p, _i, _i, _p, _i, _i, _l, _p, _i, _p],
+    "b200mp_node_linear_wgrad_rows": [_p, _p, _i, _i, _p, _p, _i, _i, _l, _p, _i, _p],
     "b200mp_node_linear64": [_p, _p, _p, _i, _l, _p, _i, _p, _p, _i, _p],
     "b200mp_node_pair_wgrad": [_p, _p, _p, _l, _p, _i, _p],
     "b200mp_negative_sample_workspace_bytes": [_l, _p],

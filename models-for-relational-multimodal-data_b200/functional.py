@@ -436,14 +436,15 @@ def _row_linear(x, W, b=None, *, xrow=None, T1=None, idx1=None, T2=None, idx2=No
     return out
 
 
-def _rows_wgrad(a, b):
-    """a^T b over the E rows ([E,Ka], [E,Kb] -> [Ka,Kb]) on the tcgen05 weight-gradient kernel; few rows: library GEMM"""
-    if a.shape[0] == 0:
+def _rows_wgrad(a, b, arow=None, brow=None):
+    """sum_r a[arow[r]]^T b[brow[r]] over the E rows ([E,Ka], [E,Kb] -> [Ka,Kb]; row maps None = r) on the tcgen05 weight-gradient kernel"""
+    E = a.shape[0]
+    if E == 0:
         return a.new_zeros((a.shape[1], b.shape[1]))
     npart = torch.cuda.get_device_properties(a.device).multi_processor_count
     part = torch.empty((npart, a.shape[1], b.shape[1]), dtype=torch.float32, device=a.device)
-    L.check(L.lib().b200mp_node_linear_wgrad(L.ptr(a), a.shape[1], a.shape[1], L.ptr(b), b.shape[1], b.shape[1], a.shape[0],
-                                             L.ptr(part), npart, L.stream()), "b200mp_node_linear_wgrad")
+    L.check(L.lib().b200mp_node_linear_wgrad_rows(L.ptr(a), L.ptr(arow), a.shape[1], a.shape[1], L.ptr(b), L.ptr(brow), b.shape[1], b.shape[1],
+                                                  E, L.ptr(part), npart, L.stream()), "b200mp_node_linear_wgrad_rows")
     return part.sum(0)
 
 
@@ -469,8 +470,7 @@ def _message_bwd_wide(kind, seg, m, e, node_in, W, need_T1, N, g_e, accumulate, 
                                                  L.ptr(gT1), L.stream()), "b200mp_message_grad_rows")
         # g_e[eid[k]] (+)= G_k W (+ g_acc[k])
         _row_linear(G, W.t(), None, R=g_e if accumulate else None, rrow=eid, alpha=1.0, beta=1.0, R2=g_acc, out=g_e, orow=eid)
-        e_rows = e if eid is None else _permute(e, eid.long(), False)
-        gW = _rows_wgrad(G, e_rows)
+        gW = _rows_wgrad(G, e, brow=eid)
     if need_T1 and det:
         gT1 = _sum_rows_by_neighbour(seg, G, N)
     return g_e, gT1, gW, G.sum(0)
@@ -483,10 +483,8 @@ def _edge_update_bwd_wide(st, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q, 
     with torch.cuda.device(dev), _track("edge_update_bwd", 4):
         Gh = _row_linear(g_out, W2.t(), None, xrow=g_eid, mask=h, beta=beta)               # beta (g W2) [h > 0]
         g_e = _row_linear(Gh, W1.t(), None, R=g_out, rrow=g_eid, alpha=alpha, beta=1.0)     # alpha g + Gh W1
-        g_rows = g_out if g_eid is None else _permute(g_out, g_eid.long(), False)
-        e_rows = e if e_eid is None else _permute(e, e_eid.long(), False)
-        gW2 = _rows_wgrad(g_rows, h) * beta
-        gW1 = _rows_wgrad(Gh, e_rows)
+        gW2 = _rows_wgrad(g_out, h, arow=g_eid) * beta
+        gW1 = _rows_wgrad(Gh, e, brow=e_eid)
         gP = gQ = None
         if need_P and not det:
             gP = torch.zeros((nP or st.num_nodes, H), dtype=torch.float32, device=dev)
@@ -495,7 +493,7 @@ def _edge_update_bwd_wide(st, g_out, h, e, W1, W2, alpha, beta, need_P, need_Q, 
         gQ = _segment_sum_rows(st.fwd, Gh)[: (nQ or st.num_nodes)]
     if need_P and det:
         gP = _sum_rows_by_neighbour(st.fwd, Gh, nP or st.num_nodes)
-    return g_e, gP, gQ, gW1, Gh.sum(0), gW2, g_rows.sum(0) * beta
+    return g_e, gP, gQ, gW1, Gh.sum(0), gW2, g_out.sum(0) * beta        # (a column sum does not care about the row map)
 
 
 # ----------------------------------------------------------------------------- raw launches

@@ -235,9 +235,9 @@ def test_wide_tensor_core_path_equals_simt(e, n, det):
     errs = {"arbiter g_e (wide)": rel_err(got[4], G64 @ W1.double()), "arbiter g_e (simt)": rel_err(ref[4], G64 @ W1.double()),
             "arbiter gW (wide)": rel_err(got[6], gW64), "arbiter gW (simt)": rel_err(ref[6], gW64),
             "arbiter gb (wide)": rel_err(got[7], G64.sum(0)), "arbiter gb (simt)": rel_err(ref[7], G64.sum(0))}
+    # (a sum kept in tensor memory loses accuracy linearly in the number of MMAs added into one accumulator -- 1.06e-5 of max|gW| on this
+    # case with 1024 rows between two drains of the weight-gradient kernel, hence its 512: profiles/r02_wgrad_chain_and_node_precision.txt)
     bad = {k: v for k, v in errs.items() if v > 1e-5 and "wide" in k}
-    # two fp32 evaluations of a sum over E rows (3xTF32 in tensor memory, drained every 1024 rows | FFMA in registers) each carry up
-    # to ~6e-6 against fp64 (profiles/r02_wgrad_chain_and_node_precision.txt): 1e-5 against the arbiter, 2e-5 against each other
     for i, (a, b, c_) in enumerate(zip(got, ref, got_mapped)):
         assert a.shape == b.shape == c_.shape
         if rel_err(a, b) > 2e-5:

@@ -70,9 +70,15 @@ def _check(case, name, got, refs32, o64, forward, flipped=False):
     # parameter gradients are sums over ALL rows: a kink decision that an input gradient of the same run has already shown (flipped)
     # shifts every element of them coherently, so only the relative L2 bound applies there
     shifted = (not forward) and flipped and k[2] < 2e-2
+    # a gradient the fp32 ORACLE cannot deliver at 1e-5 either (its own relative L2 distance to fp64 exceeds the tolerance: sums with
+    # massive cancellation, e.g. a bias in front of a normalisation) amplifies forward round-off by its condition number.  The kernels'
+    # forward round-off is the 3xTF32 one, 2^-20 per product against fp32's 2^-24, so up to 16x the oracle's own error is the same
+    # conditioning, not a different result; the bulk bound (2e-2) still applies
+    ill = (not forward) and o[2] > TOL and k[2] <= 16 * o[2] and k[2] < 2e-2
     _emit(txt + ("" if strict else "   [kink decision: bulk at oracle level]" if kink else
-                 "   [sums over rows of a run with a kink decision]" if shifted else "   [FAIL]"))
-    assert strict or kink or shifted, (case, name, k, o)
+                 "   [sums over rows of a run with a kink decision]" if shifted else
+                 "   [ill-conditioned: within 16x the fp32 oracle's own distance to fp64]" if ill else "   [FAIL]"))
+    assert strict or kink or shifted or ill, (case, name, k, o)
     return strict
 
 
