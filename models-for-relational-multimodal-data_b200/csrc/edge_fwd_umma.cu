@@ -33,8 +33,13 @@ template <int MODE> struct FwdCfg { static constexpr int NTH = MODE == 2 ? 512 :
 // everything that touches global memory -- e rows, gathered node rows, h / e' / m rows -- runs in
 // the coalesced mapping (thread (g, j): 16-byte chunk j of NP adjacent rows), with the gathered
 // rows and the residual e rows kept in registers instead of shared memory.
-template <int MODE, typename T>
+// GPF (mode 2 only): the node rows P[src] / Q[dst] of the NEXT tile are gathered behind this tile's second product -- the
+// registers that held this tile's gathered rows are free from the first epilogue on -- so that they are in flight across the
+// tile boundary instead of between the first MMA and its epilogue, where a random-row DRAM latency (~1 us) outlasts the 0.4 us
+// of tensor work it was meant to hide behind.  The next tile's indices go into the other half of a double-buffered index stage.
+template <int MODE, typename T, bool GPF = false>
 __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_linear_fwd_umma_kernel(EdgeFwdUArgs<T> a) {
+    static_assert(!GPF || MODE == 2, "gather prefetch is an edge-update variant");
     constexpr int NTH = FwdCfg<MODE>::NTH;
     constexpr int CW = HH / (NTH / TE);       // accumulator columns per tensor-memory thread
     constexpr int NP = RowRegs<NTH>::NP;
@@ -48,7 +53,7 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
     float* W2_hi = W1_lo + WT::FLOATS;        // mode 2 only
     float* W2_lo = W2_hi + WT::FLOATS;
     __shared__ TileSync sync;
-    __shared__ int sidx[2][TE];               // gather indices of the tile (clamped rows)
+    __shared__ int sidx_s[GPF ? 2 : 1][2][TE];   // gather indices of the tile (clamped rows); GPF: this tile's | the next one's
 
     const int tid = threadIdx.x, warp = tid >> 5;
     const int t = tid & (TE - 1), ch = tid >> 7;           // tensor-memory side: row t, columns CW ch ..
@@ -84,13 +89,16 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
                          (int)min64(TE, a.E - ((int64_t)blockIdx.x + gridDim.x) * TE), tid);
     }
 
+    RowRegs<NTH> G2;                         // mode 2 (registers to spare): the add waits until the prefetch is issued
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         const int64_t row0 = tile * TE;
         const int nrows = nrows_pf;
         const uint32_t par = it & 1;
+        int (*sidx)[TE] = sidx_s[GPF ? (it & 1) : 0];
+        const bool own_gather = !GPF || it == 0;          // GPF: later tiles had theirs issued during the previous tile
 
         store_rows_split(R, E_hi, E_lo, nrows, tid);
-        if (ch < 2) sidx[ch][t] = idx_pf;
+        if (own_gather && ch < 2) sidx[ch][t] = idx_pf;
         fence_async_smem();
         fence_before();
         __syncthreads();
@@ -99,8 +107,7 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
             gemm3_data(tm, E_hi, E_lo, W1_hi, W1_lo, 0);
             mma_commit(&sync.bar[0]);
         }
-        RowRegs<NTH> G2;                     // mode 2 (registers to spare): the add waits until the prefetch is issued
-        if (MODE == 2) gather_rows_issue(G, G2, a.T1, sidx[0], a.T2, sidx[1], tid);
+        if (MODE == 2) { if (own_gather) gather_rows_issue(G, G2, a.T1, sidx[0], a.T2, sidx[1], tid); }
         else gather_rows(G, a.T1, sidx[0], a.T2, sidx[1], tid);   // coalesced, in flight while the MMAs run
         RowRegs<NTH> Rn;                     // mode 2 keeps this tile's e rows for the residual
         int nrows_next = 0;
@@ -140,6 +147,8 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
             }
         }
         if (MODE == 2) {
+            const bool has_next = GPF && nrows_next > 0;
+            if (has_next && ch < 2) sidx_s[GPF ? ((it + 1) & 1) : 0][ch][t] = idx_pf;      // the next tile's indices (fetched above)
             fence_async_smem();
             fence_before();
             __syncthreads();
@@ -147,6 +156,10 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
             if (tid == 0) {
                 gemm3_data(tm + 64, E_hi, E_lo, W2_hi, W2_lo, 0);
                 mma_commit(&sync.bar[1]);
+            }
+            if (has_next) {                  // G / G2 are dead since the first epilogue: the next tile's node rows take their place
+                int (*nidx)[TE] = sidx_s[GPF ? ((it + 1) & 1) : 0];
+                gather_rows_issue(G, G2, a.T1, nidx[0], a.T2, nidx[1], tid);
             }
             int64_t orow[NP];
 #pragma unroll
@@ -343,10 +356,10 @@ static int launch_update_fwd_pipe(const EdgeFwdUArgs<T>& a, cudaStream_t st) {
     return 0;
 }
 
-template <int MODE, typename T>
+template <int MODE, typename T, bool GPF = false>
 static int launch_fwd_umma_mode(const EdgeFwdUArgs<T>& a, cudaStream_t st) {
     const size_t smem = (MODE == 2 ? 3 * RT::BYTES + 4 * WT::BYTES : 2 * RT::BYTES + 2 * WT::BYTES) + 1024;
-    auto kern = edge_linear_fwd_umma_kernel<MODE, T>;
+    auto kern = edge_linear_fwd_umma_kernel<MODE, T, GPF>;
     constexpr int NTH = FwdCfg<MODE>::NTH;
     B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ntiles = (a.E + TE - 1) / TE;
@@ -370,7 +383,11 @@ static int launch_edge_fwd_umma_t(int mode, int64_t E, const T* e, const int32_t
             // hi_medium 9.80 -> 9.94 ms (the residual rows re-read behind the MMAs stop hitting L2 once 148 SMs stream 8 GB tensors)
             const char* v = getenv("B200MP_UPD_PIPE");
             const bool pipe = v && v[0] == '1';
-            return pipe ? launch_update_fwd_pipe<T>(a, st) : launch_fwd_umma_mode<2, T>(a, st);
+            if (pipe) return launch_update_fwd_pipe<T>(a, st);
+            // B200MP_UPD_GPF=1: the next tile's node rows gathered behind this tile's second product (A/B switch)
+            const char* gv = getenv("B200MP_UPD_GPF");
+            const bool gpf = gv && gv[0] == '1';
+            return gpf ? launch_fwd_umma_mode<2, T, true>(a, st) : launch_fwd_umma_mode<2, T, false>(a, st);
         }
     }
     return B200MP_EINVAL;

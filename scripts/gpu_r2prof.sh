@@ -9,6 +9,9 @@ timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/b
 timeout 600 python bench.py --model gine --steps 5 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/bench_gine.json 2>/dev/null; python scripts/benchsum.py gpurun_out/bench_gine.json | head -2
 timeout 600 python bench.py --workload hi_small --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/bench_small.json 2>/dev/null; python scripts/benchsum.py gpurun_out/bench_small.json | head -2
 timeout 600 python bench.py --dtype bf16 --steps 5 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/bench_bf16.json 2>/dev/null; python scripts/benchsum.py gpurun_out/bench_bf16.json | head -2
+for f in 1 0; do   # H = 128 (pna.py:50 default width): tcgen05 composition (1) against the fused SIMT kernels (0)
+  B200MP_TC128=$f timeout 600 python bench.py --workload hi_small --hidden 128 --steps 5 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/bench_small_h128_tc$f.json 2>/dev/null; python scripts/benchsum.py gpurun_out/bench_small_h128_tc$f.json | head -1
+done
 CMD="python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 echo "ncu list rc=$?"

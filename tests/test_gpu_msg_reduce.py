@@ -141,3 +141,24 @@ def test_edge_update_backward_split_barriers_equals_single(e, n):
     assert torch.equal(a[0], b[0])
     for x, y in zip(a[1:], b[1:]):
         assert rel_err(y, x) < 1e-5
+
+
+@pytest.mark.parametrize("maps", [False, True])
+@pytest.mark.parametrize("e,n", [(37, 50), (128, 10), (129, 40), (100_001, 9000), (2_000_000, 150_000)])
+def test_edge_update_forward_gather_prefetch_equals_serial(e, n, maps):
+    """B200MP_UPD_GPF=1 (the next tile's P[src] / Q[dst] rows gathered behind this tile's second product, indices double buffered) is
+    the same arithmetic on the same operands as the kernel that gathers between its first product and its epilogue: bit for bit"""
+    g = torch.Generator(device="cuda").manual_seed(e + 3)
+    ei = torch.stack([torch.randint(0, n, (e,), device="cuda", generator=g), torch.randint(0, n, (e,), device="cuda", generator=g)])
+    st = G.edge_structure(ei, n)
+    ea = torch.randn(e, H, device="cuda", generator=g)
+    W1, W2 = torch.randn(H, H, device="cuda", generator=g) / 8, torch.randn(H, H, device="cuda", generator=g) / 8
+    b1, b2 = torch.randn(H, device="cuda", generator=g), torch.randn(H, device="cuda", generator=g)
+    P, Q = torch.randn(n, H, device="cuda", generator=g), torch.randn(n, H, device="cuda", generator=g)
+    eid = st.fwd.perm32() if maps else None
+    outs = []
+    for flag in ("0", "1"):
+        os.environ["B200MP_UPD_GPF"] = flag
+        outs.append(BF._edge_linear_fwd(2, ea, eid, W1, b1, P, st.src32, Q, st.dst32, W2, b2, 0.5, 0.5, eid))
+    os.environ.pop("B200MP_UPD_GPF")
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
