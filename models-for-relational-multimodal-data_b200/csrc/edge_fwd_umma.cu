@@ -384,9 +384,10 @@ static int launch_edge_fwd_umma_t(int mode, int64_t E, const T* e, const int32_t
             const char* v = getenv("B200MP_UPD_PIPE");
             const bool pipe = v && v[0] == '1';
             if (pipe) return launch_update_fwd_pipe<T>(a, st);
-            // B200MP_UPD_GPF=1: the next tile's node rows gathered behind this tile's second product (A/B switch)
+            // default: the next tile's node rows gathered behind this tile's second product (same-box A/B on hi_medium, two pairs:
+            // 9.86 / 9.92 -> 9.38 / 9.41 ms; hi_small 1.54 -> 1.44 ms; bit-identical outputs); B200MP_UPD_GPF=0 gathers per tile
             const char* gv = getenv("B200MP_UPD_GPF");
-            const bool gpf = gv && gv[0] == '1';
+            const bool gpf = !(gv && gv[0] == '0');
             return gpf ? launch_fwd_umma_mode<2, T, true>(a, st) : launch_fwd_umma_mode<2, T, false>(a, st);
         }
     }
