@@ -29,6 +29,7 @@ extern "C" {
 
 #define B200MP_EINVAL   (-1)   /* bad argument (unsupported H, null pointer, ...) */
 #define B200MP_EWORKSP  (-2)   /* workspace too small */
+#define B200MP_ELIMIT   (-3)   /* size beyond the fixed maximum of an entry point that owns its scratch memory */
 
 /* Library / device introspection. */
 int b200mp_version(void);
@@ -65,6 +66,18 @@ int b200mp_bincount(const int64_t* vals, int64_t n, int64_t* hist, int64_t nbins
 int b200mp_relabel_workspace_bytes(int64_t M, size_t* bytes);
 int b200mp_relabel(const int64_t* ids, int64_t M, int64_t* nodes, int64_t* n_unique,
                    int64_t* local, void* workspace, size_t workspace_bytes, void* stream);
+
+/* b200mp_relabel without any allocation on either side of the call.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and results (bit-exact) as b200mp_relabel; the workspace is a file-scope
+ * `static __device__` array of B200MP_RELABEL_STATIC_BYTES inside the library (held by every GPU that loads it until exit),
+ * resolved once per device with cudaGetSymbolAddress.  Limit: M <= B200MP_RELABEL_STATIC_MAX_IDS, beyond it -> B200MP_ELIMIT
+ * (nothing is launched).  The entry point calls no cudaMalloc / cudaFree / allocating library routine.  All calls share the one
+ * array (it keeps the previous call's contents; nothing in it needs to start at zero): calls that overlap on the GPU --
+ * different streams or host threads on one device -- race; serialise them on one stream. */
+#define B200MP_RELABEL_STATIC_MAX_IDS 262144
+#define B200MP_RELABEL_STATIC_BYTES   (8u << 20)
+int b200mp_relabel_static(const int64_t* ids, int64_t M, int64_t* nodes, int64_t* n_unique, int64_t* local, void* stream);
 
 /* Row permutation of an [n,H] fp32 matrix: out[i] = in[idx[i]] / out[idx[i]] = in[i]. */
 int b200mp_gather_rows(const float* in, const int64_t* idx, float* out, int64_t n, int H, void* stream);

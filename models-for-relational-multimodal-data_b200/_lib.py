@@ -28,6 +28,7 @@ _SIGS = {
     "b200mp_bincount": [_p, _l, _p, _l, _p],
     "b200mp_relabel_workspace_bytes": [_l, _p],
     "b200mp_relabel": [_p, _l, _p, _p, _p, _p, _sz, _p],
+    "b200mp_relabel_static": [_p, _l, _p, _p, _p, _p],
     "b200mp_gather_rows": [_p, _p, _p, _l, _i, _p],
     "b200mp_scatter_rows": [_p, _p, _p, _l, _i, _p],
     "b200mp_edge_linear_fwd": [_i, _i, _l, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p],
@@ -119,7 +120,7 @@ class B200MPError(RuntimeError):
 
 def check(rc: int, what: str):
     if rc != 0:
-        kind = {-1: "invalid argument", -2: "workspace too small"}.get(rc, f"cudaError {rc}" if rc > 0 else "error")
+        kind = {-1: "invalid argument", -2: "workspace too small", -3: "size beyond the entry point's fixed maximum"}.get(rc, f"cudaError {rc}" if rc > 0 else "error")
         raise B200MPError(f"{what} failed: {kind} (rc={rc})")
 
 

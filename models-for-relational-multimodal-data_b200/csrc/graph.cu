@@ -10,6 +10,7 @@
 #include "common.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 
@@ -324,6 +325,49 @@ extern "C" int b200mp_relabel(const int64_t* ids, int64_t M, int64_t* nodes, int
     relabel_search_kernel<<<grid_for(M), 256, 0, st>>>(ids, M, nodes, n_unique, local);
     B200MP_LAUNCH_CHECK();
     return 0;
+}
+
+// ---- batch relabel without any allocation (b200mp_relabel_static) -----------------------------------------------------------
+// Same launches as b200mp_relabel; the workspace is a file-scope device array instead of a caller buffer, for callers that cannot
+// allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library holds the
+// B200MP_RELABEL_STATIC_BYTES until exit.  The array is shared by every call and keeps the previous call's contents: nothing in
+// it has to start at zero (sorted / flag / pos are fully rewritten for the M ids of a call, the sort's temporary storage is
+// initialised by the sort itself), and two calls that overlap on the GPU (different streams or threads) race on it.
+namespace b200mp {
+constexpr size_t RELABEL_STATIC_BYTES = (size_t)B200MP_RELABEL_STATIC_BYTES;
+static __device__ __align__(256) unsigned char relabel_static_scratch[RELABEL_STATIC_BYTES];
+constexpr int RELABEL_STATIC_MAX_DEVICES = 64;
+
+// The array's name is a host-side stand-in in host code, not a device address: resolve it once per device (with that device
+// current) and hand the kernels the resolved pointer.
+static int relabel_static_address(void** out) {
+    static std::atomic<void*> cache[RELABEL_STATIC_MAX_DEVICES];
+    int dev = -1;
+    B200MP_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= RELABEL_STATIC_MAX_DEVICES) return B200MP_EINVAL;
+    void* p = cache[dev].load(std::memory_order_acquire);
+    if (!p) {
+        const cudaError_t e = cudaGetSymbolAddress(&p, relabel_static_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!p) return B200MP_EINVAL;
+        cache[dev].store(p, std::memory_order_release);      // idempotent: a concurrent first call resolves the same address
+    }
+    *out = p;
+    return 0;
+}
+}  // namespace b200mp
+
+extern "C" int b200mp_relabel_static(const int64_t* ids, int64_t M, int64_t* nodes, int64_t* n_unique, int64_t* local, void* stream) {
+    if (M < 0) return B200MP_EINVAL;
+    if (M > (int64_t)B200MP_RELABEL_STATIC_MAX_IDS) return B200MP_ELIMIT;
+    size_t need = 0;
+    int rc = b200mp_relabel_workspace_bytes(M, &need);
+    if (rc) return rc;
+    if (need > RELABEL_STATIC_BYTES) return B200MP_ELIMIT;
+    void* scratch = nullptr;
+    rc = relabel_static_address(&scratch);
+    if (rc) return rc;
+    return b200mp_relabel(ids, M, nodes, n_unique, local, scratch, RELABEL_STATIC_BYTES, stream);
 }
 
 extern "C" int b200mp_gather_rows(const float* in, const int64_t* idx, float* out, int64_t n, int H, void* stream) {
