@@ -480,6 +480,13 @@ def run_b200(args, rank, world, local_rank):
     value = e / (ms_step * 1e-3)                 # N > 1: ONE graph partitioned over the ranks (strong scaling)
     checksum = step(keep=True)
     torch.cuda.synchronize()
+    if os.environ.get("B200MP_TORCH_PROFILE") and rank == 0:     # diagnosis only (after the timed region): one more step under torch.profiler
+        from torch.profiler import profile, ProfilerActivity
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+            step()
+            torch.cuda.synchronize()
+        with open(os.environ["B200MP_TORCH_PROFILE"], "w") as f:
+            f.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=60, max_name_column_width=90))
 
     # whole model ("report whole-model numbers separately"): node_emb / edge_emb included, N = 1, f32 line only
     whole = None

@@ -113,6 +113,12 @@ int b200mp_node_linear_wgrad_rows(const float* X, const int32_t* xrow, int ldx, 
  * blocks (A, B, out0 of PNAConv's hoisted pre_nn / post_nn self term; P, Q of the edge update). */
 int b200mp_node_linear64(const float* X0, const float* X1, const float* X2, int nx, int64_t N, const float* Wimg,
                          int NO, const float* bias, float* Y, int ysplit, void* stream);
+/* b200mp_node_linear64 (NO = 64, Y [N,64]) that also returns the column sums of X = [X0 | X1 | X2] as per-CTA partials
+ * colsum_part [n_part][64 nx] (zeroed by the caller; summed by the caller, fixed order): with X = the output gradients of the Q | K | V
+ * projections (or of one linear) of nn.TransformerEncoderLayer (tabgnn.py:116-128 through torch MultiheadAttention / Linear backward),
+ * one pass yields the data gradient and the bias gradients, which torch computes with a separate sum over every gradient tensor. */
+int b200mp_node_linear64_colsum(const float* X0, const float* X1, const float* X2, int nx, int64_t N, const float* Wimg,
+                                const float* bias, float* Y, float* colsum_part, int n_part, void* stream);
 /* Weight gradients of two H = 64 node linears sharing their input Y (PNAConv pre_nn halves A | B, edge
  * update halves P | Q, pna.py:71-84): part[p][0:64] = G0^T Y, part[p][64:128] = G1^T Y; all [N,64]. */
 int b200mp_node_pair_wgrad(const float* G0, const float* G1, const float* Y, int64_t N, float* part, int n_part,
@@ -253,6 +259,22 @@ int b200mp_add_dropout_layernorm_fwd(const float* x, const float* sub, int64_t r
 int b200mp_add_dropout_layernorm_bwd(const float* g, const float* x, const float* sub, const float* stats, int64_t rows,
                                      int C, float p_drop, uint64_t seed, const float* gamma, float* gx, float* gsub,
                                      float* ggamma, float* gbeta, void* stream);
+
+/* Extended forms for a STACK of encoder layers evaluated as one unit (tabgnn.py:116-131: `x = (x + layer(x)) / 2` per layer, then
+ * `(x + x_tab) / 2` into the embeddings): the residual blends are written by the layer's last LayerNorm instead of separate add / div
+ * passes, and a gradient that is still a sum of terms is consumed as such:
+ *   forward   y = yscale * LayerNorm(x + dropout(sub)) + bs0 * b0 + bs1 * b1       (b0, b1 nullable; b1 needs b0)
+ *   backward  as above with the incoming gradient g = gs0 * g0 + gs1 * g1 + gs2 * g2  (g1, g2 nullable; g2 needs g1)
+ * b200mp_scaled_sum: out = sum_{i<n} scales[i] * terms[i], n <= 6 tensors of numel floats (numel % 4 == 0; `terms` / `scales` are
+ * HOST arrays): writes such a gradient once where it leaves the stack. */
+int b200mp_add_dropout_layernorm_fwd_ex(const float* x, const float* sub, int64_t rows, int C, float p_drop, uint64_t seed,
+                                        const float* gamma, const float* beta, float eps, float yscale, const float* b0, float bs0,
+                                        const float* b1, float bs1, float* y, float* stats, void* stream);
+int b200mp_add_dropout_layernorm_bwd_ex(const float* g0, float gs0, const float* g1, float gs1, const float* g2, float gs2,
+                                        const float* x, const float* sub, const float* stats, int64_t rows, int C, float p_drop,
+                                        uint64_t seed, const float* gamma, float* gx, float* gsub, float* ggamma, float* gbeta,
+                                        void* stream);
+int b200mp_scaled_sum(const float* const* terms, const float* scales, int n, int64_t numel, float* out, void* stream);
 
 /* out = dropout(relu(x)) (g == NULL, first argument x) or its backward out = g * keep_scale where y > 0 (g != NULL, first
  * argument the saved forward output y): the feed-forward's inner activation of the encoder layer.  numel % 4 == 0. */

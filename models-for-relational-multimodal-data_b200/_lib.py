@@ -45,6 +45,7 @@ _SIGS = {
     "b200mp_node_linear_wgrad": [_p, _i, _i, _p, _i, _i, _l, _p, _i, _p],
     "b200mp_node_linear_wgrad_rows": [_p, _p, _i, _i, _p, _p, _i, _i, _l, _p, _i, _p],
     "b200mp_node_linear64": [_p, _p, _p, _i, _l, _p, _i, _p, _p, _i, _p],
+    "b200mp_node_linear64_colsum": [_p, _p, _p, _i, _l, _p, _p, _p, _p, _i, _p],
     "b200mp_node_pair_wgrad": [_p, _p, _p, _l, _p, _i, _p],
     "b200mp_negative_sample_workspace_bytes": [_l, _p],
     "b200mp_negative_sample": [_p, _l, _l, _p, _l, _i, C.c_uint64, _p, _p, _sz, _p],
@@ -59,6 +60,9 @@ _SIGS = {
     "b200mp_bn_relu_res_bwd_apply": [_p, _p, _l, _i, _p, _p, _p, _p, _p, _p, _p],
     "b200mp_add_dropout_layernorm_fwd": [_p, _p, _l, _i, _f, C.c_uint64, _p, _p, _f, _p, _p, _p],
     "b200mp_add_dropout_layernorm_bwd": [_p, _p, _p, _p, _l, _i, _f, C.c_uint64, _p, _p, _p, _p, _p, _p],
+    "b200mp_add_dropout_layernorm_fwd_ex": [_p, _p, _l, _i, _f, C.c_uint64, _p, _p, _f, _f, _p, _f, _p, _f, _p, _p, _p],
+    "b200mp_add_dropout_layernorm_bwd_ex": [_p, _f, _p, _f, _p, _f, _p, _p, _p, _l, _i, _f, C.c_uint64, _p, _p, _p, _p, _p, _p],
+    "b200mp_scaled_sum": [_p, _p, _i, _l, _p, _p],
     "b200mp_relu_dropout": [_p, _p, _l, _f, C.c_uint64, _p, _p],
     "b200mp_col_encode_fwd": [_p, _i, _p, _l, _i, _p, _p],
     "b200mp_col_encode_bwd": [_p, _i, _i, _l, _i, _p, _p, _p, _p, _p],

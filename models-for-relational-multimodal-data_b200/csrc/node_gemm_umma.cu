@@ -39,6 +39,7 @@ struct NodeLinArgs {
     const float* X1; const float* X2;         // segmented input: columns 64 s .. 64 s + 63 of X come from X<s>, each [N, 64]
     int ysplit;                               // output as NO / 64 separate [N, 64] blocks (Y + g N 64) instead of [N, NO]
     int ldy;                                  // row stride of Y in floats (NO unless the call fills a column block of a wider output)
+    float* colsum_part;                       // CS variant: [gridDim.x][K] column sums of X over the rows this CTA handled
 };
 // Row epilogue of b200mp_row_linear (the per-edge linears at H = 128 run on this kernel): for tile row k
 //   z = X[xrow[k]] W^T + bias + [pre-addend rows];  relu: z = max(z, 0);  [mask rows]: z = z * [mask > 0]
@@ -68,8 +69,12 @@ using namespace ng;
 // c - 1's MMAs run, and chunk c's X panel is split and stored while they run too -- the serial version
 // (two CTAs per SM, single buffers) spent ~3.4 us per chunk for 0.6 us of tensor work, mostly waiting for
 // the 48-64 KB weight copy from L2.
-template <int NO, bool EPI = false>
+// CS: the column sums of X fall out of the pass as a by-product (per-CTA partials, fixed summation order): with X = the gradients
+// [g_0 | g_1 | ..] of a group of linears, they ARE the bias gradients, which otherwise cost one more pass over every g_i.
+template <int NO, bool EPI = false, bool CS = false>
 __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a, typename std::conditional<EPI, RowEpi, NoEpi>::type ep) {
+    constexpr int CS_K = 192;                 // widest segmented input (three [N,64] blocks)
+    __shared__ float cs_s[CS ? NT2 / 32 : 1][CS ? CS_K : 1];      // one row per warp: no atomics, fixed order
     constexpr int W_PART = NO * KCH;                       // floats per hi (or lo) weight chunk
     constexpr int W_BUF = 2 * W_PART;                      // hi + lo
     extern __shared__ __align__(128) float smem_raw[];
@@ -88,6 +93,9 @@ __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a,
     if (tid == 0) {
         mbar_init(&bar_w[0], 1); mbar_init(&bar_w[1], 1); mbar_init(&bar_m[0], 1); mbar_init(&bar_m[1], 1);
         mbar_fence_init();
+    }
+    if constexpr (CS) {
+        for (int i = tid; i < (NT2 / 32) * CS_K; i += NT2) (&cs_s[0][0])[i] = 0.f;
     }
     fence_before();
     __syncthreads();
@@ -162,6 +170,23 @@ __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a,
                 const int o = XP::off(r, j8);
                 st4(X_hi + o, h);
                 st4(X_lo + o, l);
+            }
+            if constexpr (CS) {              // lanes (lane & 7) = piece j8, (lane >> 3) = the warp's four row groups
+                float4 cs = f4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (g8 * 4 + i < nrows) cs = cs + xr[0][i];
+#pragma unroll
+                for (int off = 8; off <= 16; off <<= 1) {
+                    cs.x += __shfl_xor_sync(0xffffffffu, cs.x, off);
+                    cs.y += __shfl_xor_sync(0xffffffffu, cs.y, off);
+                    cs.z += __shfl_xor_sync(0xffffffffu, cs.z, off);
+                    cs.w += __shfl_xor_sync(0xffffffffu, cs.w, off);
+                }
+                if ((tid & 31) < 8) {
+                    float* d = &cs_s[warp][c * KCH + j8 * 4];
+                    d[0] += cs.x; d[1] += cs.y; d[2] += cs.z; d[3] += cs.w;
+                }
             }
 #pragma unroll
             for (int k = 0; k + 1 < PF; ++k) {
@@ -241,7 +266,29 @@ __global__ void __launch_bounds__(NT2, 1) node_linear_umma_kernel(NodeLinArgs a,
     }
     fence_before();
     __syncthreads();
+    if constexpr (CS) {
+        if (tid < a.K) {
+            float sum = 0.f;
+#pragma unroll
+            for (int w = 0; w < NT2 / 32; ++w) sum += cs_s[w][tid];
+            a.colsum_part[(int64_t)blockIdx.x * a.K + tid] = sum;
+        }
+    }
     if (warp == 0) tmem_dealloc(tm, NCOLS);
+}
+
+// the CS variant: NO = 64 (the data gradient of a group of [*, 64] -> [*, 64] linears), at most n_part CTAs
+static int launch_node_linear_colsum(const NodeLinArgs& a, int n_part, cudaStream_t st) {
+    constexpr int NO = 64;
+    const size_t smem = 4 * XP::BYTES + 2 * (2 * NO * KCH * 4) + 1024;
+    auto kern = node_linear_umma_kernel<NO, false, true>;
+    B200MP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t ntiles = (a.N + TE - 1) / TE;
+    int grid = persistent_grid((const void*)kern, smem, ntiles, NT2);
+    if (grid > n_part) grid = n_part;
+    kern<<<grid, NT2, smem, st>>>(a, NoEpi{});
+    B200MP_LAUNCH_CHECK();
+    return 0;
 }
 
 template <int NO>
@@ -399,7 +446,7 @@ extern "C" int b200mp_node_linear_ld(const float* X, int64_t N, int K, int ldx, 
     using namespace b200mp;
     if (N < 0 || K <= 0 || K % 32 || ldx < K || ldx % 4 || ldy < NO || ldy % 4 || !X || !Wimg || !Y) return B200MP_EINVAL;
     if (N == 0) return 0;
-    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0, ldy};
+    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0, ldy, nullptr};
     cudaStream_t st = (cudaStream_t)stream;
     switch (NO) {
         case 64: return launch_node_linear<64>(a, st);
@@ -453,7 +500,7 @@ extern "C" int b200mp_node_linear64(const float* X0, const float* X1, const floa
     using namespace b200mp;
     if (N < 0 || nx < 1 || nx > 3 || !X0 || (nx > 1 && !X1) || (nx > 2 && !X2) || !Wimg || !Y) return B200MP_EINVAL;
     if (N == 0) return 0;
-    NodeLinArgs a{N, 64 * nx, 64, X0, Wimg, bias, Y, nx > 1 ? X1 : X0, nx > 2 ? X2 : X0, ysplit, NO};
+    NodeLinArgs a{N, 64 * nx, 64, X0, Wimg, bias, Y, nx > 1 ? X1 : X0, nx > 2 ? X2 : X0, ysplit, NO, nullptr};
     cudaStream_t st = (cudaStream_t)stream;
     switch (NO) {
         case 64: return launch_node_linear<64>(a, st);
@@ -475,7 +522,7 @@ extern "C" int b200mp_row_linear(const float* X, const int32_t* xrow, int64_t N,
     using namespace b200mp;
     if (N < 0 || K <= 0 || K % 32 || ldx < K || ldx % 4 || !X || !Wimg || !Y || (T1 && !idx1) || (T2 && !idx2)) return B200MP_EINVAL;
     if (N == 0) return 0;
-    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0, NO};
+    NodeLinArgs a{N, K, ldx, X, Wimg, bias, Y, nullptr, nullptr, 0, NO, nullptr};
     EpiSlot slots[2] = {{nullptr, nullptr, 0, 0.f}, {nullptr, nullptr, 0, 0.f}};
     int ns = 0;
     auto add = [&](const float* p, const int32_t* idx, int role, float coef) {
@@ -495,4 +542,16 @@ extern "C" int b200mp_row_linear(const float* X, const int32_t* xrow, int64_t N,
         case 256: return launch_row_linear<256>(a, ep, st);
     }
     return B200MP_EINVAL;
+}
+
+/* b200mp_node_linear64 with NO = 64 that also returns the column sums of X = [X0 | X1 | X2]: colsum_part [n_part][64 nx], row p = the
+ * sums over the rows CTA p handled (rows p >= the launched grid are left untouched: zero them first); the caller adds the rows up.
+ * With X the gradients of a group of linears this pass yields their data gradient AND their bias gradients. */
+extern "C" int b200mp_node_linear64_colsum(const float* X0, const float* X1, const float* X2, int nx, int64_t N, const float* Wimg,
+                                           const float* bias, float* Y, float* colsum_part, int n_part, void* stream) {
+    using namespace b200mp;
+    if (N <= 0 || nx < 1 || nx > 3 || !X0 || (nx > 1 && !X1) || (nx > 2 && !X2) || !Wimg || !Y || !colsum_part || n_part < 1)
+        return B200MP_EINVAL;
+    NodeLinArgs a{N, 64 * nx, 64, X0, Wimg, bias, Y, nx > 1 ? X1 : X0, nx > 2 ? X2 : X0, 0, 64, colsum_part};
+    return launch_node_linear_colsum(a, n_part, (cudaStream_t)stream);
 }

@@ -40,6 +40,11 @@ struct RowNormArgs {
     int64_t rows; int C;
     const float* x; const float* sub; float p; uint64_t seed;
     const float* gamma; const float* beta; float eps;
+    // extended forms (b200mp_add_dropout_layernorm_fwd_ex / _bwd_ex); the plain entry points leave them at {1, null, ...}:
+    //   forward   y = yscale * LayerNorm(z) + bs0 * b0 + bs1 * b1      (b0 / b1 nullable: residual blends such as (t + layer(t)) / 2)
+    //   backward  g = gs0 * g0 + gs1 * g1 + gs2 * g2                   (g1 / g2 nullable: a gradient that is still a sum of terms)
+    float yscale; const float* b0; float bs0; const float* b1; float bs1;
+    const float* g1; const float* g2; float gs0, gs1, gs2;
 };
 
 template <int LPR>
@@ -66,8 +71,13 @@ __global__ void __launch_bounds__(256) row_norm_fwd_kernel(RowNormArgs a, float*
         const float var = group_sum<LPR>(d.x * d.x + d.y * d.y + d.z * d.z + d.w * d.w) * inv_c;
         const float rstd = rsqrtf(var + a.eps);
         if (live) {
-            st4(y + r * a.C + c4 * 4, f4(d.x * rstd * gm.x + bt.x, d.y * rstd * gm.y + bt.y, d.z * rstd * gm.z + bt.z,
-                                         d.w * rstd * gm.w + bt.w));
+            float4 o = f4(d.x * rstd * gm.x + bt.x, d.y * rstd * gm.y + bt.y, d.z * rstd * gm.z + bt.z, d.w * rstd * gm.w + bt.w);
+            if (a.b0 || a.yscale != 1.f) {
+                o = a.yscale * o;
+                if (a.b0) o = o + a.bs0 * ldg4(a.b0 + r * a.C + c4 * 4);
+                if (a.b1) o = o + a.bs1 * ldg4(a.b1 + r * a.C + c4 * 4);
+            }
+            st4(y + r * a.C + c4 * 4, o);
             if (c4 == 0) *reinterpret_cast<float2*>(stats + r * 2) = make_float2(mean, rstd);
         }
     }
@@ -93,6 +103,11 @@ __global__ void __launch_bounds__(256) row_norm_bwd_kernel(RowNormArgs a, const 
         float mean = 0.f, rstd = 0.f;
         if (live) {
             gv = ldg4(g + r * a.C + c4 * 4);
+            if (a.g1 || a.gs0 != 1.f) {
+                gv = a.gs0 * gv;
+                if (a.g1) gv = gv + a.gs1 * ldg4(a.g1 + r * a.C + c4 * 4);
+                if (a.g2) gv = gv + a.gs2 * ldg4(a.g2 + r * a.C + c4 * 4);
+            }
             z = ldg4(a.x + r * a.C + c4 * 4);
             if (a.sub) {
                 float4 s = ldg4(a.sub + r * a.C + c4 * 4);
@@ -146,6 +161,19 @@ __global__ void __launch_bounds__(256) relu_dropout_kernel(const float* __restri
     }
 }
 
+// out = sum_i s_i t_i over up to 6 tensors (quads): a gradient carried as a sum of terms, written once where it leaves the column
+// stack (functional._ColumnStack) instead of being added up pair by pair
+struct ScaledSumArgs { const float* t[6]; float s[6]; int n; };
+__global__ void __launch_bounds__(256) scaled_sum_kernel(ScaledSumArgs a, int64_t quads, float* __restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < quads; i += (int64_t)gridDim.x * blockDim.x) {
+        float4 v = a.s[0] * ldg4(a.t[0] + i * 4);
+#pragma unroll
+        for (int k = 1; k < 6; ++k)
+            if (k < a.n) v = v + a.s[k] * ldg4(a.t[k] + i * 4);
+        st4(out + i * 4, v);
+    }
+}
+
 static int row_norm_grid(int64_t rows, int lpr) {
     const int64_t iters = (rows + 256 / lpr - 1) / (256 / lpr);
     const int64_t cap = (int64_t)device_info().sms * 8;
@@ -161,11 +189,19 @@ static bool row_norm_ok(int64_t rows, int C, float p) {
 extern "C" int b200mp_add_dropout_layernorm_fwd(const float* x, const float* sub, int64_t rows, int C, float p_drop,
                                                 uint64_t seed, const float* gamma, const float* beta, float eps, float* y,
                                                 float* stats, void* stream) {
+    return b200mp_add_dropout_layernorm_fwd_ex(x, sub, rows, C, p_drop, seed, gamma, beta, eps, 1.f, nullptr, 0.f, nullptr, 0.f, y, stats,
+                                               stream);
+}
+
+extern "C" int b200mp_add_dropout_layernorm_fwd_ex(const float* x, const float* sub, int64_t rows, int C, float p_drop,
+                                                   uint64_t seed, const float* gamma, const float* beta, float eps, float yscale,
+                                                   const float* b0, float bs0, const float* b1, float bs1, float* y, float* stats,
+                                                   void* stream) {
     using namespace b200mp;
     if (!row_norm_ok(rows, C, p_drop)) return B200MP_EINVAL;
     if (rows == 0) return 0;
-    if (!x || !gamma || !beta || !y || !stats) return B200MP_EINVAL;
-    RowNormArgs a{rows, C, x, sub, sub ? p_drop : 0.f, seed, gamma, beta, eps};
+    if (!x || !gamma || !beta || !y || !stats || (b1 && !b0)) return B200MP_EINVAL;
+    RowNormArgs a{rows, C, x, sub, sub ? p_drop : 0.f, seed, gamma, beta, eps, yscale, b0, bs0, b1, bs1, nullptr, nullptr, 1.f, 0.f, 0.f};
     cudaStream_t st = (cudaStream_t)stream;
     const int lpr = C / 4, grid = row_norm_grid(rows, lpr);
     switch (lpr) {
@@ -181,11 +217,20 @@ extern "C" int b200mp_add_dropout_layernorm_fwd(const float* x, const float* sub
 extern "C" int b200mp_add_dropout_layernorm_bwd(const float* g, const float* x, const float* sub, const float* stats,
                                                 int64_t rows, int C, float p_drop, uint64_t seed, const float* gamma, float* gx,
                                                 float* gsub, float* ggamma, float* gbeta, void* stream) {
+    return b200mp_add_dropout_layernorm_bwd_ex(g, 1.f, nullptr, 0.f, nullptr, 0.f, x, sub, stats, rows, C, p_drop, seed, gamma, gx, gsub,
+                                               ggamma, gbeta, stream);
+}
+
+extern "C" int b200mp_add_dropout_layernorm_bwd_ex(const float* g0, float gs0, const float* g1, float gs1, const float* g2, float gs2,
+                                                   const float* x, const float* sub, const float* stats, int64_t rows, int C,
+                                                   float p_drop, uint64_t seed, const float* gamma, float* gx, float* gsub,
+                                                   float* ggamma, float* gbeta, void* stream) {
     using namespace b200mp;
+    const float* g = g0;
     if (!row_norm_ok(rows, C, p_drop)) return B200MP_EINVAL;
     if (rows == 0) return 0;
-    if (!g || !x || !stats || !gamma || !gx || !ggamma || !gbeta || (sub && p_drop > 0.f && !gsub)) return B200MP_EINVAL;
-    RowNormArgs a{rows, C, x, sub, sub ? p_drop : 0.f, seed, gamma, nullptr, 0.f};
+    if (!g || !x || !stats || !gamma || !gx || !ggamma || !gbeta || (sub && p_drop > 0.f && !gsub) || (g2 && !g1)) return B200MP_EINVAL;
+    RowNormArgs a{rows, C, x, sub, sub ? p_drop : 0.f, seed, gamma, nullptr, 0.f, 1.f, nullptr, 0.f, nullptr, 0.f, g1, g2, gs0, gs1, gs2};
     cudaStream_t st = (cudaStream_t)stream;
     const int lpr = C / 4, grid = row_norm_grid(rows, lpr);
     switch (lpr) {
@@ -207,6 +252,25 @@ extern "C" int b200mp_relu_dropout(const float* x_or_y, const float* g, int64_t 
     if (!x_or_y || !out) return B200MP_EINVAL;
     const int64_t quads = numel / 4, want = (quads + 255) / 256, cap = (int64_t)device_info().sms * 16;
     relu_dropout_kernel<<<(int)(want < cap ? want : cap), 256, 0, (cudaStream_t)stream>>>(x_or_y, g, quads, p_drop, seed, out);
+    B200MP_LAUNCH_CHECK();
+    return 0;
+}
+
+/* out = sum_{i < n} scales[i] * terms[i]  (n <= 6 tensors of numel floats, numel % 4 == 0; host arrays of pointers / scales) */
+extern "C" int b200mp_scaled_sum(const float* const* terms, const float* scales, int n, int64_t numel, float* out, void* stream) {
+    using namespace b200mp;
+    if (n < 1 || n > 6 || numel < 0 || (numel & 3) || !terms || !scales) return B200MP_EINVAL;
+    if (numel == 0) return 0;
+    if (!out) return B200MP_EINVAL;
+    ScaledSumArgs a{};
+    a.n = n;
+    for (int i = 0; i < n; ++i) {
+        if (!terms[i]) return B200MP_EINVAL;
+        a.t[i] = terms[i];
+        a.s[i] = scales[i];
+    }
+    const int64_t quads = numel / 4, want = (quads + 255) / 256, cap = (int64_t)device_info().sms * 16;
+    scaled_sum_kernel<<<(int)(want < cap ? want : cap), 256, 0, (cudaStream_t)stream>>>(a, quads, out);
     B200MP_LAUNCH_CHECK();
     return 0;
 }

@@ -285,6 +285,21 @@ def _node_pair_wgrad(g0, g1, x):
     return G[:64], G[64:]
 
 
+def _node_linear64_colsum(xs, Wcat):
+    """([x_0 | x_1 | ..] Wcat^T  [N,64],  column sums of [x_0 | x_1 | ..]  [64 n]) in one pass of the tcgen05 node kernel"""
+    N, dev = xs[0].shape[0], xs[0].device
+    K = 64 * len(xs)
+    y = torch.empty((N, 64), dtype=torch.float32, device=dev)
+    npart = 2 * torch.cuda.get_device_properties(dev).multi_processor_count
+    part = torch.zeros((npart, K), dtype=torch.float32, device=dev)
+    img = _w_image(Wcat)
+    px = [L.ptr(t) for t in xs] + [None] * (3 - len(xs))
+    with torch.cuda.device(dev), _track("node_linear64"):
+        L.check(L.lib().b200mp_node_linear64_colsum(px[0], px[1], px[2], len(xs), N, L.ptr(img), None, L.ptr(y), L.ptr(part), npart,
+                                                    L.stream()), "b200mp_node_linear64_colsum")
+    return y, part.sum(0)
+
+
 def _node_linear64(xs, Wcat, bias, ysplit):
     """[x_0 | x_1 | ..] Wcat^T + bias for [N,64] blocks on the tcgen05 node kernel; ysplit: the result as
     Wcat.shape[0] / 64 separate contiguous [N,64] tensors."""
@@ -327,10 +342,16 @@ class _LinearGroup(torch.autograd.Function):
         n = ctx.n
         gs = [None if g is None else _f32c(g) for g in gs]
         gx = None
+        colsum = None
         if ctx.needs_input_grad[0]:
             if ctx.kernel_ok and all(g is not None for g in gs):
-                # gx = [g_0 | g_1 | ..] [W_0; W_1; ..]: one pass over the gradients, no separate adds
-                gx = _node_linear64(gs, torch.cat(list(Ws), 0).t(), None, False)
+                # gx = [g_0 | g_1 | ..] [W_0; W_1; ..]: one pass over the gradients, no separate adds -- and, where a bias wants
+                # its gradient, the column sums of the g_i out of the same pass
+                Wt = torch.cat(list(Ws), 0).t()
+                if any(ctx.needs_input_grad[2 + n + i] for i in range(n)):
+                    gx, colsum = _node_linear64_colsum(gs, Wt)
+                else:
+                    gx = _node_linear64(gs, Wt, None, False)
             else:
                 for g, W in zip(gs, Ws):
                     if g is not None:
@@ -348,7 +369,10 @@ class _LinearGroup(torch.autograd.Function):
         else:
             for i in want:
                 gW[i] = gs[i].t() @ x
-        gb = [gs[i].sum(0) if (gs[i] is not None and ctx.needs_input_grad[2 + n + i]) else None for i in range(n)]
+        if colsum is not None:
+            gb = [colsum[64 * i:64 * (i + 1)] if ctx.needs_input_grad[2 + n + i] else None for i in range(n)]
+        else:
+            gb = [gs[i].sum(0) if (gs[i] is not None and ctx.needs_input_grad[2 + n + i]) else None for i in range(n)]
         return (gx, None, *gW, *gb)
 
 
@@ -1063,6 +1087,47 @@ def _row_norm_bwd(g, x, sub, stats, p, seed, gamma):
                                                          L.ptr(gamma), L.ptr(gx), L.ptr(gsub), L.ptr(gg[0]), L.ptr(gg[1]), L.stream()),
                 "b200mp_add_dropout_layernorm_bwd")
     return gx, gsub, gg[0], gg[1]
+
+
+def _row_norm_fwd_ex(x, sub, p, seed, gamma, beta, eps, yscale=1.0, blends=(), out=None):
+    """y = yscale * LayerNorm(x + dropout(sub)) + sum_i s_i b_i  (blends: up to two (tensor, scale)); ``out``: where y goes"""
+    rows, Cc = x.shape
+    y = torch.empty_like(x) if out is None else out
+    stats = torch.empty(rows, 2, device=x.device, dtype=torch.float32)
+    b = list(blends) + [(None, 0.0)] * (2 - len(blends))
+    with torch.cuda.device(x.device), _track("add_dropout_layernorm_fwd"):
+        L.check(L.lib().b200mp_add_dropout_layernorm_fwd_ex(L.ptr(x), L.ptr(sub), rows, Cc, float(p), C_u64(seed), L.ptr(gamma), L.ptr(beta),
+                                                            float(eps), float(yscale), L.ptr(b[0][0]), float(b[0][1]), L.ptr(b[1][0]),
+                                                            float(b[1][1]), L.ptr(y), L.ptr(stats), L.stream()),
+                "b200mp_add_dropout_layernorm_fwd_ex")
+    return y, stats
+
+
+def _row_norm_bwd_ex(gterms, x, sub, stats, p, seed, gamma):
+    """_row_norm_bwd with the incoming gradient given as a sum of up to three (tensor, scale) terms"""
+    rows, Cc = x.shape
+    gx = torch.empty_like(x)
+    gsub = torch.empty_like(x) if (sub is not None and p > 0.0) else None
+    gg = torch.zeros(2, Cc, device=x.device, dtype=torch.float32)
+    t = list(gterms) + [(None, 0.0)] * (3 - len(gterms))
+    with torch.cuda.device(x.device), _track("add_dropout_layernorm_bwd"):
+        L.check(L.lib().b200mp_add_dropout_layernorm_bwd_ex(L.ptr(t[0][0]), float(t[0][1]), L.ptr(t[1][0]), float(t[1][1]), L.ptr(t[2][0]),
+                                                            float(t[2][1]), L.ptr(x), L.ptr(sub), L.ptr(stats), rows, Cc, float(p),
+                                                            C_u64(seed), L.ptr(gamma), L.ptr(gx), L.ptr(gsub), L.ptr(gg[0]), L.ptr(gg[1]),
+                                                            L.stream()), "b200mp_add_dropout_layernorm_bwd_ex")
+    return gx, gsub, gg[0], gg[1]
+
+
+def _scaled_sum(terms, out=None):
+    """sum_i s_i t_i over up to six (tensor, scale) terms of one shape, one pass"""
+    n = len(terms)
+    ref = terms[0][0]
+    y = torch.empty_like(ref) if out is None else out
+    ptrs = (L.C.c_void_p * n)(*[t.data_ptr() for t, _ in terms])
+    scales = (L.C.c_float * n)(*[float(sc) for _, sc in terms])
+    with torch.cuda.device(ref.device), _track("scaled_sum"):
+        L.check(L.lib().b200mp_scaled_sum(ptrs, scales, n, ref.numel(), L.ptr(y), L.stream()), "b200mp_scaled_sum")
+    return y
 
 
 class _AddDropoutLayerNorm(torch.autograd.Function):

@@ -92,6 +92,16 @@ def _embed(lin: nn.Linear, t):
     return BF.linear_group(t, (lin.weight,), (lin.bias,))[0]
 
 
+def _embed_wide(lin: nn.Linear, t, scale: float = 1.0):
+    """lin(scale * t) for the flattened column tokens [rows, S C] (tabgnn.py:130-131 and its twins: `edge_emb(((e + te) / 2).reshape(..))`):
+    the scale (a power of two, exact) is folded into the tiny weight instead of costing a pass over the [rows, S C] tensor, and the linear
+    runs on the tcgen05 node kernels (forward, data gradient in column blocks, weight gradient); small shapes: library GEMM"""
+    W = lin.weight if scale == 1.0 else lin.weight * scale
+    if t.shape[1] == 64:
+        return BF.linear_group(t, (W,), (lin.bias,))[0]
+    return BF.linear3x(t, W, lin.bias)
+
+
 class _Backbone(_EdgeStorage, nn.Module):
     """Shared layer loop of gine.py:86-89 / pna.py:95-99."""
 

@@ -19,9 +19,10 @@ import torch
 import torch.nn.functional as F
 from torch import Tensor, nn
 
+from .. import column_stack as CS
 from .. import functional as BF
 from ..graph import EdgeStructure, edge_structure
-from .backbones import PNAConvHetero, _EdgeStorage
+from .backbones import PNAConvHetero, _EdgeStorage, _embed_wide
 from .conv import BatchNorm, PNAConv, edge_update_sorted
 
 _AGGR = ['mean', 'max', 'min', 'std']
@@ -172,13 +173,23 @@ class TABGNN(_EdgeStorage, _SharedParams, nn.Module):
     def _with_cls(self, t: Tensor) -> Tensor:
         return torch.cat([self.cls_embedding.expand(t.shape[0], 1, -1), t], dim=1)
 
+    def _tabular(self, t: Tensor) -> Tensor:
+        """t + T_L(..T_1(t)), T_l(u) = (u + tab_norm_l(tab_conv_l(u))) / 2 (tabgnn.py:116-131; the same layers serve node and edge
+        tokens): one autograd node over the whole stack where the kernels cover the shapes (column_stack.supported), else layer by layer"""
+        convs = [layer.tab_conv for layer in self.tabular_backbone]
+        norms = [layer.tab_norm for layer in self.tabular_backbone]
+        if CS.supported(convs, norms, t):
+            return CS.column_stack(convs, norms, t, self.tabular_backbone[0].chunk_rows, add_input=True)
+        u = t
+        for layer in self.tabular_backbone:
+            u = layer(u)
+        return t + u
+
     def forward(self, x, edge_index, edge_attr):
         x, e = self._with_cls(x), self._with_cls(edge_attr)
-        tx, te = x, e
-        for layer in self.tabular_backbone:          # the same layer serves node and edge tokens
-            tx, te = layer(tx), layer(te)
-        x = self.node_emb(((x + tx) / 2).reshape(x.shape[0], -1))
-        e = self._store(self.edge_emb(((e + te) / 2).reshape(e.shape[0], -1)))
+        sx, se = self._tabular(x), self._tabular(e)           # x + x_tab, e + e_tab
+        x = _embed_wide(self.node_emb, sx.reshape(x.shape[0], -1), 0.5)
+        e = self._store(_embed_wide(self.edge_emb, se.reshape(e.shape[0], -1), 0.5))
         st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
         if not self.reverse_mp and x.shape[1] == 64 and BF.row_maps_available():
             # e stays in the caller's order at both ends: first layer reads / last layer writes through the CSC permutation
@@ -197,11 +208,9 @@ class TABGNN(_EdgeStorage, _SharedParams, nn.Module):
         row-local, so it shards with the rows; the graph half exchanges source-side node tables per layer.
         Returns the owned rows of (x, edge_attr) in the same orders."""
         x, e = self._with_cls(x_local), self._with_cls(edge_attr_local)
-        tx, te = x, e
-        for layer in self.tabular_backbone:
-            tx, te = layer(tx), layer(te)
-        x = self.node_emb(((x + tx) / 2).reshape(x.shape[0], -1))
-        e = self._store(self.edge_emb(((e + te) / 2).reshape(e.shape[0], -1)))
+        sx, se = self._tabular(x), self._tabular(e)
+        x = _embed_wide(self.node_emb, sx.reshape(x.shape[0], -1), 0.5)
+        e = self._store(_embed_wide(self.edge_emb, se.reshape(e.shape[0], -1), 0.5))
         for layer in self.gnn_backbone:
             x, e = layer.forward_sorted(x, None, e, part)
         return x, e
@@ -361,11 +370,11 @@ class TABGNNFused(_TabGraphModel):
         tgt0 = self.attend(self._with_cls(target_edge_attr))          # fused.py:160 (no residual)
         tok = self._with_cls(edge_attr)
         tok = (tok + self.attend(tok)) / 2                            # :164
-        e = self.edge_emb(tok.reshape(tok.shape[0], -1))
+        e = _embed_wide(self.edge_emb, tok.reshape(tok.shape[0], -1))
         st = edge_structure(edge_index, x.shape[0], reverse=self.reverse_mp)
         e = BF.gather_rows(e, st.fwd.perm)
         x_tab = tgt0
         for layer in self.backbone:
             x_tab, x, e = layer.forward_sorted(x_tab, x, st, e, target_edge_index, lp)
-        tgt = self.edge_emb(((x_tab + tgt0) / 2).reshape(tgt0.shape[0], -1))   # :172-174
+        tgt = _embed_wide(self.edge_emb, (x_tab + tgt0).reshape(tgt0.shape[0], -1), 0.5)   # :172-174
         return x, BF.scatter_rows(e, st.fwd.perm), tgt

@@ -250,6 +250,30 @@ def row_norm_bwd(g, x, sub, stats, p, seed, gamma):
     return gz.contiguous(), gsub, (g * zh).sum(0), g.sum(0)
 
 
+def row_norm_fwd_ex(x, sub, p, seed, gamma, beta, eps, yscale=1.0, blends=(), out=None):
+    y, stats = row_norm_fwd(x, sub, p, seed, gamma, beta, eps)
+    y = yscale * y
+    for b, sc in blends:
+        y = y + sc * b
+    if out is not None:
+        out.copy_(y)
+        y = out
+    return y, stats
+
+
+def row_norm_bwd_ex(gterms, x, sub, stats, p, seed, gamma):
+    g = sum(sc * t for t, sc in gterms)
+    return row_norm_bwd(g, x, sub, stats, p, seed, gamma)
+
+
+def scaled_sum(terms, out=None):
+    y = sum(sc * t for t, sc in terms)
+    if out is not None:
+        out.copy_(y)
+        return out
+    return y
+
+
 def bn_stats(c):
     cd = c.double()
     return torch.stack([cd.sum(0), (cd * cd).sum(0)])
@@ -319,6 +343,11 @@ def node_linear64(xs, Wcat, bias, ysplit):
     return [c.contiguous() for c in y.split(64, dim=1)] if ysplit else y.contiguous()
 
 
+def node_linear64_colsum(xs, Wcat):
+    x = torch.cat(list(xs), dim=1)
+    return (x @ Wcat.t()).contiguous(), x.sum(0)
+
+
 def node_pair_wgrad(g0, g1, x):
     return g0.t() @ x, g1.t() @ x
 
@@ -361,6 +390,10 @@ _PATCHES = [
     (BF, "_bf16_ok", lambda t: None),
     (BF, "fused_reduce_available", lambda H: False),          # the fused kernel's two halves are emulated separately
     (BF, "_node_linear64", node_linear64),
+    (BF, "_node_linear64_colsum", node_linear64_colsum),
+    (BF, "_row_norm_fwd_ex", row_norm_fwd_ex),
+    (BF, "_row_norm_bwd_ex", row_norm_bwd_ex),
+    (BF, "_scaled_sum", scaled_sum),
     (BF, "_node_pair_wgrad", node_pair_wgrad),
     (BF, "_node_linear", node_linear),
     (BF, "_node_wgrad", node_wgrad),

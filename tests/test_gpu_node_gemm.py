@@ -93,3 +93,18 @@ def test_linear_cat_matches_fp64(N, n):
         err = rel_err(a, t)
         print(f"linear_cat N={N} n={n} {name}: rel err {err:.2e}")
         assert err < 1e-5
+
+
+@pytest.mark.parametrize("N,n", [(4096, 3), (7001, 2), (130, 1), (300_001, 3)])
+def test_node_linear64_colsum(N, n):
+    """data gradient of a group of 64 -> 64 linears and their bias gradients (column sums of the incoming gradients) out of one pass"""
+    g = torch.Generator(device="cuda").manual_seed(N + n)
+    xs = [torch.randn(N, 64, device="cuda", generator=g) * (1 + i) + 0.25 * i for i in range(n)]
+    W = torch.randn(64, 64 * n, device="cuda", generator=g) / 8
+    y, cs = BF._node_linear64_colsum(xs, W)
+    X = torch.cat(xs, 1).double()
+    assert rel_err(y, X @ W.double().t()) < 2e-6
+    assert rel_err(cs, X.sum(0)) < 2e-6
+    y2, cs2 = BF._node_linear64_colsum(xs, W)            # fixed summation order: bit-identical from run to run
+    assert torch.equal(y, y2) and torch.equal(cs, cs2)
+    assert torch.equal(y, BF._node_linear64(xs, W, None, False))
