@@ -120,7 +120,8 @@ int b200mp_node_linear64(const float* X0, const float* X1, const float* X2, int 
 int b200mp_node_linear64_colsum(const float* X0, const float* X1, const float* X2, int nx, int64_t N, const float* Wimg,
                                 const float* bias, float* Y, float* colsum_part, int n_part, void* stream);
 /* Weight gradients of two H = 64 node linears sharing their input Y (PNAConv pre_nn halves A | B, edge
- * update halves P | Q, pna.py:71-84): part[p][0:64] = G0^T Y, part[p][64:128] = G1^T Y; all [N,64]. */
+ * update halves P | Q, pna.py:71-84): part[p][0:64] = G0^T Y, part[p][64:128] = G1^T Y; all [N,64].  G1 == NULL: one gradient
+ * (G1 is not read, part[p][64:128] = 0). */
 int b200mp_node_pair_wgrad(const float* G0, const float* G1, const float* Y, int64_t N, float* part, int n_part,
                            void* stream);
 

@@ -140,13 +140,13 @@ def _chunk_backward(g_out, saved, P, cfg, seeds, gx_out, pgrads, need_param):
         g_hm, cs = BF._node_linear64_colsum([g_ff], W2.t())      # ff = hm W2^T + b2
         acc(base + 9, cs)
         if need_param[base + 8]:
-            acc(base + 8, BF._node_pair_wgrad(g_ff, g_ff, hm)[0])
+            acc(base + 8, BF._node_pair_wgrad(g_ff, None, hm)[0])
         g_h = BF._relu_dropout(hm, g_hm, pr, sr)
         del g_hm
         g_x1f, cs = BF._node_linear64_colsum([g_h], W1.t())      # h = x1 W1^T + b1
         acc(base + 7, cs)
         if need_param[base + 6]:
-            acc(base + 6, BF._node_pair_wgrad(g_h, g_h, x1)[0])
+            acc(base + 6, BF._node_pair_wgrad(g_h, None, x1)[0])
         del g_h
         g_tr, g_sa, gg1, gb1 = BF._row_norm_bwd_ex([(g_x1r, 1.0), (g_x1f, 1.0)], t, sa, st1, p1, s1, g1)
         acc(base + 4, gg1), acc(base + 5, gb1)
@@ -155,14 +155,14 @@ def _chunk_backward(g_out, saved, P, cfg, seeds, gx_out, pgrads, need_param):
         g_att, cs = BF._node_linear64_colsum([g_sa], Wo.t())     # sa = att Wo^T + bo
         acc(base + 3, cs)
         if need_param[base + 2]:
-            acc(base + 2, BF._node_pair_wgrad(g_sa, g_sa, att)[0])
+            acc(base + 2, BF._node_pair_wgrad(g_sa, None, att)[0])
         gq, gk, gv = BF._col_attention_bwd(q.view(R, S, 64), k.view(R, S, 64), v.view(R, S, 64), g_att.view(R, S, 64), nhead[li], pa, sa_)
         gq, gk, gv = gq.view(R * S, 64), gk.view(R * S, 64), gv.view(R * S, 64)
         g_tq, cs = BF._node_linear64_colsum([gq, gk, gv], Wqkv.t())          # [q | k | v] = t Wqkv^T + bqkv
         acc(base + 1, cs)
         if need_param[base]:
             gWq, gWk = BF._node_pair_wgrad(gq, gk, t)
-            gWv = BF._node_pair_wgrad(gv, gv, t)[0]
+            gWv = BF._node_pair_wgrad(gv, None, t)[0]
             acc(base, torch.cat([gWq, gWk, gWv], 0))
         G = [(g_tr, 1.0), (g_tq, 1.0)] + half
     if gx_out is not None:

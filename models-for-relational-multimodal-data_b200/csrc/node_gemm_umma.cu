@@ -329,6 +329,7 @@ struct NodeWgArgs {
     int K;
     const float* X1;                               // pair mode (K = 128): columns 64..127 of X come from X1, both at ldx
     const int32_t* xrow; const int32_t* yrow;      // storage rows of X / Y for reduction row r (null = r)
+    int single;                                    // pair mode with ONE gradient: columns 64..127 of X are zeros (not read)
 };
 }  // namespace ng
 
@@ -365,7 +366,8 @@ __global__ void __launch_bounds__(NT2, 2) node_wgrad_umma_kernel(NodeWgArgs a) {
         const int64_t rx = a.xrow ? (int64_t)__ldg(a.xrow + rc) : rc, ry = a.yrow ? (int64_t)__ldg(a.yrow + rc) : rc;
 #pragma unroll
         for (int p = 0; p < XPN; ++p)
-            xr[p] = ldg4((a.X1 && p >= 2) ? a.X1 + rx * a.ldx + (p - 2) * 32 + piece * 4
+            xr[p] = (a.single && p >= 2) ? f4(0.f, 0.f, 0.f, 0.f)
+                  : ldg4((a.X1 && p >= 2) ? a.X1 + rx * a.ldx + (p - 2) * 32 + piece * 4
                                           : a.X + rx * a.ldx + kb * 128 + p * 32 + piece * 4);
 #pragma unroll
         for (int p = 0; p < YPN; ++p) yr[p] = ldg4(a.Y + ry * a.ldy + p * 32 + piece * 4);
@@ -467,7 +469,7 @@ extern "C" int b200mp_node_linear_wgrad_rows(const float* X, const int32_t* xrow
     using namespace b200mp;
     if (N <= 0 || K <= 0 || K % 128 || ldx < K || ldx % 4 || ldy < NO || ldy % 4 || n_part <= 0 || !X || !Y || !part)
         return B200MP_EINVAL;
-    NodeWgArgs a{N, ldx, ldy, X, Y, part, K, nullptr, xrow, yrow};
+    NodeWgArgs a{N, ldx, ldy, X, Y, part, K, nullptr, xrow, yrow, 0};
     cudaStream_t st = (cudaStream_t)stream;
     switch (NO) {
         case 64: return launch_node_wgrad<64>(a, n_part, st);
@@ -488,8 +490,8 @@ extern "C" int b200mp_node_linear_wgrad(const float* X, int ldx, int K, const fl
 extern "C" int b200mp_node_pair_wgrad(const float* G0, const float* G1, const float* Y, int64_t N, float* part, int n_part,
                                       void* stream) {
     using namespace b200mp;
-    if (N <= 0 || n_part <= 0 || !G0 || !G1 || !Y || !part) return B200MP_EINVAL;
-    NodeWgArgs a{N, 64, 64, G0, Y, part, 128, G1, nullptr, nullptr};
+    if (N <= 0 || n_part <= 0 || !G0 || !Y || !part) return B200MP_EINVAL;
+    NodeWgArgs a{N, 64, 64, G0, Y, part, 128, G1 ? G1 : G0, nullptr, nullptr, G1 ? 0 : 1};   // G1 == NULL: part[p][64:128] = 0
     return launch_node_wgrad<64>(a, n_part, (cudaStream_t)stream);
 }
 

@@ -274,7 +274,7 @@ class _Linear3x(torch.autograd.Function):
 
 
 def _node_pair_wgrad(g0, g1, x):
-    """(g0^T x, g1^T x) for [N,64] tensors on the tcgen05 weight-gradient kernel (one launch)."""
+    """(g0^T x, g1^T x) for [N,64] tensors on the tcgen05 weight-gradient kernel (one launch); g1 None: (g0^T x, zeros), g0 read once."""
     N = x.shape[0]
     npart = torch.cuda.get_device_properties(x.device).multi_processor_count
     part = torch.empty((npart, 128, 64), dtype=torch.float32, device=x.device)
@@ -363,7 +363,7 @@ class _LinearGroup(torch.autograd.Function):
             for k in range(0, len(want), 2):
                 i0 = want[k]
                 i1 = want[k + 1] if k + 1 < len(want) else i0
-                gW[i0], g1 = _node_pair_wgrad(gs[i0], gs[i1], x)
+                gW[i0], g1 = _node_pair_wgrad(gs[i0], gs[i1] if i1 != i0 else None, x)
                 if i1 != i0:
                     gW[i1] = g1
         else:

@@ -8,6 +8,8 @@ permuted back at the end; all per-edge work runs in the b200mp CUDA kernels.
 """
 from __future__ import annotations
 
+import os as _os
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
@@ -94,9 +96,13 @@ def _embed(lin: nn.Linear, t):
 
 def _embed_wide(lin: nn.Linear, t, scale: float = 1.0):
     """lin(scale * t) for the flattened column tokens [rows, S C] (tabgnn.py:130-131 and its twins: `edge_emb(((e + te) / 2).reshape(..))`):
-    the scale (a power of two, exact) is folded into the tiny weight instead of costing a pass over the [rows, S C] tensor, and the linear
-    runs on the tcgen05 node kernels (forward, data gradient in column blocks, weight gradient); small shapes: library GEMM"""
+    the scale (a power of two, exact) is folded into the tiny weight instead of costing a pass over the [rows, S C] tensor.  The product
+    itself stays on the library's fp32 GEMM: measured on the TABGNN C = H = 64 parity case, the 3xTF32 node kernels here (~1e-6 per
+    product against fp32's 6e-8) are amplified ~100x by the last BatchNorm's weight-gradient sum (2e-4 against the oracle's 7e-6, every
+    activation still at 2e-6), for 11 ms of a 471 ms step.  B200MP_EMB_TC=1 selects the tcgen05 node kernels."""
     W = lin.weight if scale == 1.0 else lin.weight * scale
+    if _os.environ.get("B200MP_EMB_TC", "0") != "1":
+        return torch.nn.functional.linear(t, W, lin.bias)
     if t.shape[1] == 64:
         return BF.linear_group(t, (W,), (lin.bias,))[0]
     return BF.linear3x(t, W, lin.bias)

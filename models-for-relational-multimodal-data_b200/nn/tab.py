@@ -15,6 +15,8 @@ from __future__ import annotations
 
 from typing import Optional
 
+import os as _os
+
 import torch
 import torch.nn.functional as F
 from torch import Tensor, nn
@@ -178,7 +180,7 @@ class TABGNN(_EdgeStorage, _SharedParams, nn.Module):
         tokens): one autograd node over the whole stack where the kernels cover the shapes (column_stack.supported), else layer by layer"""
         convs = [layer.tab_conv for layer in self.tabular_backbone]
         norms = [layer.tab_norm for layer in self.tabular_backbone]
-        if CS.supported(convs, norms, t):
+        if CS.supported(convs, norms, t) and _os.environ.get("B200MP_TAB_STACK", "1") != "0":
             return CS.column_stack(convs, norms, t, self.tabular_backbone[0].chunk_rows, add_input=True)
         u = t
         for layer in self.tabular_backbone:

@@ -349,7 +349,7 @@ def node_linear64_colsum(xs, Wcat):
 
 
 def node_pair_wgrad(g0, g1, x):
-    return g0.t() @ x, g1.t() @ x
+    return g0.t() @ x, (g1.t() @ x if g1 is not None else torch.zeros(64, x.shape[1]))
 
 
 def node_linear(x, W, b):

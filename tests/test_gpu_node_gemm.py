@@ -108,3 +108,16 @@ def test_node_linear64_colsum(N, n):
     y2, cs2 = BF._node_linear64_colsum(xs, W)            # fixed summation order: bit-identical from run to run
     assert torch.equal(y, y2) and torch.equal(cs, cs2)
     assert torch.equal(y, BF._node_linear64(xs, W, None, False))
+
+
+@pytest.mark.parametrize("N", [130, 4096, 300_001])
+def test_node_pair_wgrad_single_gradient(N):
+    """b200mp_node_pair_wgrad with G1 == NULL: g^T x with g read once, the second half of the partials zero"""
+    g = torch.Generator(device="cuda").manual_seed(N)
+    g0 = torch.randn(N, 64, device="cuda", generator=g)
+    x = torch.randn(N, 64, device="cuda", generator=g)
+    a, z = BF._node_pair_wgrad(g0, None, x)
+    assert rel_err(a, g0.double().t() @ x.double()) < 2e-6
+    assert not bool(z.any())
+    b, _ = BF._node_pair_wgrad(g0, g0, x)
+    assert torch.equal(a, b)
