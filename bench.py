@@ -673,7 +673,19 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # NCCL's own log (whatever level the caller asked for with NCCL_DEBUG) goes to stderr: stdout carries the one JSON line
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # torch itself prints "NCCL version ..." on STDOUT when NCCL_DEBUG is set (communicator creation): keep stdout for the JSON
+        # line by pointing fd 1 at stderr while the communicator comes up (eager with device_id; the barrier covers a lazy one)
+        sys.stdout.flush()
+        keep_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(keep_fd, 1)
+            os.close(keep_fd)
     try:
         if args.workload == "eth_lp":
             run_eth_lp(args, rank, world, local_rank)

@@ -12,6 +12,7 @@ timeout 600 python bench.py --dtype bf16 --steps 5 --warmup 3 --no-e2e --no-cpu-
 for f in 1 0; do   # H = 128 (pna.py:50 default width): tcgen05 composition (1) against the fused SIMT kernels (0)
   B200MP_TC128=$f timeout 600 python bench.py --workload hi_small --hidden 128 --steps 5 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/bench_small_h128_tc$f.json 2>/dev/null; python scripts/benchsum.py gpurun_out/bench_small_h128_tc$f.json | head -1
 done
+timeout 900 python bench.py --model tabgnn --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/bench_tabgnn_small.json 2>/dev/null; python scripts/benchsum.py gpurun_out/bench_tabgnn_small.json | head -1
 CMD="python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline"
 $CMD > gpurun_out/plain.log 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 echo "ncu list rc=$?"
