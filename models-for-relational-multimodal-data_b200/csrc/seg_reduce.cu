@@ -10,6 +10,7 @@
 // gine.py:66-70,87.
 #include "umma_edge.cuh"      // ldg_e4: float | bf16 message rows
 #include <math_constants.h>
+#include <cstdlib>
 
 namespace b200mp {
 using ue::bf16;
@@ -131,8 +132,55 @@ __device__ __forceinline__ void finalize_store(const Acc<STATS>& a, int64_t deg,
     st4(t + H, a.cx);
 }
 
+// Two-pass statistics of a light segment (TWOPASS): sums and extrema first (4 instructions per element instead of the 14 of the
+// branch-free tie bookkeeping in Acc::add1), then the tie counts against the FINAL extrema over the same rows -- which the first
+// pass has just pulled through L1 (a 15-row segment is 3.8 KB).  Same summation order, same extrema, integer-valued counts: the
+// results are bit-identical to the one-pass form.
+__device__ __forceinline__ float4 min4(float4 a, float4 b) { return f4(fminf(a.x, b.x), fminf(a.y, b.y), fminf(a.z, b.z), fminf(a.w, b.w)); }
+__device__ __forceinline__ float4 max4(float4 a, float4 b) { return f4(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z), fmaxf(a.w, b.w)); }
+__device__ __forceinline__ float4 fma4(float4 a, float4 b, float4 c) { return f4(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y), fmaf(a.z, b.z, c.z), fmaf(a.w, b.w, c.w)); }
+__device__ __forceinline__ float4 eq4(float4 v, float4 r, float4 c) {
+    return f4(c.x + (v.x == r.x ? 1.f : 0.f), c.y + (v.y == r.y ? 1.f : 0.f), c.z + (v.z == r.z ? 1.f : 0.f), c.w + (v.w == r.w ? 1.f : 0.f));
+}
+template <int H, int LPR, typename T>
+__device__ __forceinline__ void two_pass_stats(Acc<true>& a, const T* __restrict__ m, int64_t first, int64_t end, int stride, int c) {
+    float4 s = f4(0.f, 0.f, 0.f, 0.f), q = s;
+    float4 mn = f4(CUDART_INF_F, CUDART_INF_F, CUDART_INF_F, CUDART_INF_F), mx = f4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
+    int64_t r = first;
+    for (; r + 3 * (int64_t)stride < end; r += 4 * (int64_t)stride) {
+        const float4 v0 = ldg_e4(m + r * H + c), v1 = ldg_e4(m + (r + stride) * H + c);
+        const float4 v2 = ldg_e4(m + (r + 2 * (int64_t)stride) * H + c), v3 = ldg_e4(m + (r + 3 * (int64_t)stride) * H + c);
+        s = s + v0; q = fma4(v0, v0, q); mn = min4(mn, v0); mx = max4(mx, v0);
+        s = s + v1; q = fma4(v1, v1, q); mn = min4(mn, v1); mx = max4(mx, v1);
+        s = s + v2; q = fma4(v2, v2, q); mn = min4(mn, v2); mx = max4(mx, v2);
+        s = s + v3; q = fma4(v3, v3, q); mn = min4(mn, v3); mx = max4(mx, v3);
+    }
+    for (; r < end; r += stride) {
+        const float4 v = ldg_e4(m + r * H + c);
+        s = s + v; q = fma4(v, v, q); mn = min4(mn, v); mx = max4(mx, v);
+    }
+#pragma unroll
+    for (int off = LPR; off < 32; off <<= 1) {
+        s = s + shfl_xor4(s, off); q = q + shfl_xor4(q, off);
+        mn = min4(mn, shfl_xor4(mn, off)); mx = max4(mx, shfl_xor4(mx, off));
+    }
+    float4 cn = f4(0.f, 0.f, 0.f, 0.f), cx = cn;
+    for (r = first; r + (int64_t)stride < end; r += 2 * (int64_t)stride) {
+        const float4 v0 = ldg_e4(m + r * H + c), v1 = ldg_e4(m + (r + stride) * H + c);
+        cn = eq4(v0, mn, cn); cx = eq4(v0, mx, cx);
+        cn = eq4(v1, mn, cn); cx = eq4(v1, mx, cx);
+    }
+    for (; r < end; r += stride) {
+        const float4 v = ldg_e4(m + r * H + c);
+        cn = eq4(v, mn, cn); cx = eq4(v, mx, cx);
+    }
+#pragma unroll
+    for (int off = LPR; off < 32; off <<= 1) { cn = cn + shfl_xor4(cn, off); cx = cx + shfl_xor4(cx, off); }
+    a.s = s; a.q = q; a.mn = mn; a.mx = mx; a.cn = cn; a.cx = cx;
+}
+
 // ---- light segments: one warp per node
-template <bool STATS, int H, typename T>
+template <bool STATS, int H, typename T, bool TWOPASS = false>
 __global__ void __launch_bounds__(NT, SEG_MINB) seg_light_kernel(int64_t N, const int64_t* __restrict__ ptr, const T* __restrict__ m,
                                                        float* __restrict__ agg, float* __restrict__ tie, int64_t light_max) {
     constexpr int LPR = H / 4, RPW = 32 / LPR;
@@ -147,9 +195,13 @@ __global__ void __launch_bounds__(NT, SEG_MINB) seg_light_kernel(int64_t N, cons
         if (node + warps < N) { nb = __ldg(ptr + node + warps); ne = __ldg(ptr + node + warps + 1); }   // next segment's bounds in flight
         if (end - begin > light_max) continue;          // handled by the heavy path
         Acc<STATS> a;
-        a.init();
-        accumulate_rows<STATS, H>(a, m, begin + g, end, RPW, c);
-        warp_merge<STATS, LPR>(a);
+        if constexpr (STATS && TWOPASS) {
+            two_pass_stats<H, LPR>(a, m, begin + g, end, RPW, c);
+        } else {
+            a.init();
+            accumulate_rows<STATS, H>(a, m, begin + g, end, RPW, c);
+            warp_merge<STATS, LPR>(a);
+        }
         if (g == 0) finalize_store<STATS, H>(a, end - begin, node, c, agg, tie);
     }
 }
@@ -221,7 +273,10 @@ static int launch_reduce(int64_t N, const int64_t* ptr, const T* m, float* agg, 
     if (N == 0) return 0;
     const int64_t want = (N + NT / 32 - 1) / (NT / 32);
     const int grid = (int)min64(want, (int64_t)device_info().sms * 32);
-    seg_light_kernel<STATS, H, T><<<grid, NT, 0, st>>>(N, ptr, m, agg, tie, light_max);
+    const char* tp = getenv("B200MP_SEG_TWOPASS");                  // A/B switch
+    const bool two_pass = tp && tp[0] == '1';
+    if (STATS && two_pass) seg_light_kernel<STATS, H, T, true><<<grid, NT, 0, st>>>(N, ptr, m, agg, tie, light_max);
+    else seg_light_kernel<STATS, H, T><<<grid, NT, 0, st>>>(N, ptr, m, agg, tie, light_max);
     B200MP_LAUNCH_CHECK();
     if (n_heavy > 0) {
         if (!heavy_node || !heavy_chunk_ptr || !chunk_heavy || !chunk_begin || !partial || n_chunks <= 0) return B200MP_EINVAL;

@@ -162,3 +162,22 @@ def test_edge_update_forward_gather_prefetch_equals_serial(e, n, maps):
         outs.append(BF._edge_linear_fwd(2, ea, eid, W1, b1, P, st.src32, Q, st.dst32, W2, b2, 0.5, 0.5, eid))
     os.environ.pop("B200MP_UPD_GPF")
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize("e,n,dt", [(37, 50, torch.float32), (100_001, 9000, torch.float32), (2_000_000, 150_000, torch.float32),
+                                    (100_001, 9000, torch.bfloat16)])
+def test_segment_reduce_two_pass_equals_one_pass(e, n, dt):
+    """B200MP_SEG_TWOPASS=1 (sums / extrema first, tie counts against the final extrema in a second sweep over the same rows) against the
+    one-pass bookkeeping: same summation order, same extrema, integer counts -> bit for bit, ties included (quantised messages)"""
+    g = torch.Generator(device="cuda").manual_seed(e)
+    ei = torch.stack([torch.randint(0, n, (e,), device="cuda", generator=g), (torch.rand(e, device="cuda", generator=g) ** 3 * n).long().clamp_(max=n - 1)])
+    seg = G.edge_structure(ei, n).fwd
+    m = (torch.randn(e, H, device="cuda", generator=g) * 4).round() / 4          # plenty of exact ties
+    m = m.to(dt)
+    outs = []
+    for flag in ("0", "1"):
+        os.environ["B200MP_SEG_TWOPASS"] = flag
+        outs.append(BF._segment_reduce(0, seg, m, H))
+    os.environ.pop("B200MP_SEG_TWOPASS")
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert float(outs[0][1].max()) > 1.0            # ties did occur
