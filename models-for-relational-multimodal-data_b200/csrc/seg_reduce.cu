@@ -273,8 +273,10 @@ static int launch_reduce(int64_t N, const int64_t* ptr, const T* m, float* agg, 
     if (N == 0) return 0;
     const int64_t want = (N + NT / 32 - 1) / (NT / 32);
     const int grid = (int)min64(want, (int64_t)device_info().sms * 32);
-    const char* tp = getenv("B200MP_SEG_TWOPASS");                  // A/B switch
-    const bool two_pass = tp && tp[0] == '1';
+    // two-pass statistics by default (same-box A/B on hi_medium, two pairs: 3.53 -> 2.93 ms per launch, bit-identical results);
+    // B200MP_SEG_TWOPASS=0 selects the one-pass bookkeeping
+    const char* tp = getenv("B200MP_SEG_TWOPASS");
+    const bool two_pass = !(tp && tp[0] == '0');
     if (STATS && two_pass) seg_light_kernel<STATS, H, T, true><<<grid, NT, 0, st>>>(N, ptr, m, agg, tie, light_max);
     else seg_light_kernel<STATS, H, T><<<grid, NT, 0, st>>>(N, ptr, m, agg, tie, light_max);
     B200MP_LAUNCH_CHECK();
