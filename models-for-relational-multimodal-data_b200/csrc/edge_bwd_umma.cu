@@ -313,6 +313,7 @@ struct MsgBwdUArgs {
     float* gW_part; float* gb_part;
     const T* g_acc;                                   // optional [E,H] in segment order added to g_e
     float* G_out;                                     // optional [E,H] (segment order): per-edge gradient rows G
+    int l2pf;                                         // 64-edge kernel: announce the next tile's node_in rows to L2 one tile ahead
 };
 
 // PNA per-edge gradient from the saved message and the destination's coefficient rows
@@ -527,11 +528,33 @@ __global__ void __launch_bounds__(256, 2) message_bwd_umma64_kernel(MsgBwdUArgs<
         }
     };
     if ((int64_t)blockIdx.x < ntiles) prefetch(blockIdx.x);
+    // node_in rows (PNA: 7 x 256 B of coefficients per destination, GINE: 256 B) are read by the one or two tiles that hold the node's
+    // edges: first touches in DRAM, and the per-edge gradient cannot start without them (ncu: 17 % of this kernel's samples wait at
+    // their first uses, the block barrier behind them another 24 %).  Threads 0..63 carry the destination of row tid of the NEXT tile
+    // (and of row tid - 1) and announce each distinct node's rows to L2 at the top of the iteration before.
+    int pf_id = -1, pf_prev = -1;
+    auto load_pf_ids = [&](int64_t tile_) {
+        pf_id = -1;
+        if (a.l2pf && tid < RG && tile_ < ntiles) {
+            const int64_t r0_ = tile_ * RG;
+            if (r0_ + tid < a.E) {
+                pf_id = __ldg(a.seg + r0_ + tid);
+                pf_prev = tid > 0 ? __ldg(a.seg + r0_ + tid - 1) : -1;
+            }
+        }
+    };
+    load_pf_ids((int64_t)blockIdx.x + gridDim.x);
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         const int64_t row0 = tile * RG;
         const int nrows = nrows_pf;
 
+        if (pf_id >= 0 && pf_id != pf_prev) {
+            const float* q = a.node_in + (int64_t)pf_id * (KIND == 0 ? 7 * HH : HH);
+#pragma unroll
+            for (int k = 0; k < (KIND == 0 ? 14 : 2); ++k) prefetch_l2(q + k * 32);
+        }
+        load_pf_ids(tile + 2 * (int64_t)gridDim.x);
         store_rows_split(Re, E_hi, E_lo, nrows, tid);
         {
             float4 Gv[NP];
@@ -628,7 +651,8 @@ template <typename T>
 static int launch_msg_bwd_umma_t(int kind, int64_t E, const T* m, const T* e, const int32_t* eid, const float* node_in,
                                  const int32_t* seg, const int32_t* nbr, const float* W, T* g_e, int accumulate, float* gT1,
                                  float* gW_part, float* gb_part, int n_part, const T* g_acc, cudaStream_t st, float* G_out) {
-    MsgBwdUArgs<T> a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, g_acc, G_out};
+    const char* lv = getenv("B200MP_L2PF");                 // A/B switch of the L2 announcements (default on)
+    MsgBwdUArgs<T> a{E, m, e, eid, node_in, seg, nbr, W, g_e, accumulate, gT1, gW_part, gb_part, g_acc, G_out, (lv && lv[0] == '0') ? 0 : 1};
     {   // the 64-edge / two-CTAs-per-SM variant is the default (same-box A/B on hi_medium: PNA 11.77 -> 11.36 ms, GINE 10.85 -> 10.61 ms);
         // B200MP_MSG_BWD64=0 selects the 128-edge kernel
         const char* v = getenv("B200MP_MSG_BWD64");

@@ -22,6 +22,7 @@ struct EdgeFwdUArgs {
     const float* W2; const float* b2;
     float alpha, beta;
     T* out1; T* out2; const int32_t* out_eid;
+    int l2pf;                                 // modes 0 / 1: announce the next tile's T1 rows (random source rows) to L2 at the end of a tile
 };
 
 // threads per CTA: the message modes fit two CTAs of 256 per SM; the update's tiles fill shared
@@ -179,6 +180,11 @@ __global__ void __launch_bounds__(FwdCfg<MODE>::NTH, MODE == 2 ? 1 : 2) edge_lin
             }
 #pragma unroll
             for (int i = 0; i < NP; ++i) R.v[i] = Rn.v[i];
+        }
+        if (MODE < 2 && a.l2pf && nrows_next > 0 && ch == 0 && a.T1) {      // idx_pf = idx1 of row t of the next tile (arrived by now)
+            const float* q = a.T1 + (int64_t)idx_pf * HH;
+            prefetch_l2(q);
+            prefetch_l2(q + 32);
         }
         nrows_pf = nrows_next;
         fence_before();
@@ -374,7 +380,8 @@ static int launch_edge_fwd_umma_t(int mode, int64_t E, const T* e, const int32_t
                                   const float* T1, const int32_t* idx1, const float* T2, const int32_t* idx2,
                                   const float* W2, const float* b2, float alpha, float beta, T* out1, T* out2,
                                   const int32_t* out_eid, cudaStream_t st) {
-    EdgeFwdUArgs<T> a{E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2, out_eid};
+    const char* lv = getenv("B200MP_L2PF");                 // A/B switch of the L2 announcements (default on)
+    EdgeFwdUArgs<T> a{E, e, eid, W1, b1, T1, idx1, T2, idx2, W2, b2, alpha, beta, out1, out2, out_eid, (lv && lv[0] == '0') ? 0 : 1};
     switch (mode) {
         case 0: return launch_fwd_umma_mode<0, T>(a, st);
         case 1: return launch_fwd_umma_mode<1, T>(a, st);
