@@ -84,7 +84,8 @@ template <int HD>
 __global__ void __launch_bounds__(ATT_BT) col_attention_fwd_kernel(AttnArgs a, float* __restrict__ out) {
     constexpr int NG = ATT_BT / 8;
     constexpr int LD = HD % 4 == 0 ? HD : 4;
-    __shared__ __align__(16) float sk[NG][8][LD], sv[NG][8][LD];
+    constexpr int GS = 8 * LD + 8;            // group stride: +8 floats, so that the four groups of a warp read four different bank octets
+    __shared__ __align__(16) float sk[NG][GS], sv[NG][GS];
     const int grp = threadIdx.x >> 3, i = threadIdx.x & 7;
     const int64_t gid = (int64_t)blockIdx.x * NG + grp;
     const bool live = gid < a.R * a.nhead && i < a.S;
@@ -97,10 +98,10 @@ __global__ void __launch_bounds__(ATT_BT) col_attention_fwd_kernel(AttnArgs a, f
         ld_vec<HD>(qi, a.q + o);
         ld_vec<HD>(tmp, a.k + o);
 #pragma unroll
-        for (int c = 0; c < HD; ++c) sk[grp][i][c] = tmp[c];
+        for (int c = 0; c < HD; ++c) sk[grp][i * LD + c] = tmp[c];
         ld_vec<HD>(tmp, a.v + o);
 #pragma unroll
-        for (int c = 0; c < HD; ++c) sv[grp][i][c] = tmp[c];
+        for (int c = 0; c < HD; ++c) sv[grp][i * LD + c] = tmp[c];
     }
     __syncwarp();
     if (!live) return;
@@ -110,7 +111,7 @@ __global__ void __launch_bounds__(ATT_BT) col_attention_fwd_kernel(AttnArgs a, f
         float d = 0.f;
         if (j < a.S) {
 #pragma unroll
-            for (int c = 0; c < HD; ++c) d = fmaf(qi[c], sk[grp][j][c], d);
+            for (int c = 0; c < HD; ++c) d = fmaf(qi[c], sk[grp][j * LD + c], d);
         }
         s[j] = j < a.S ? d * scale : -INFINITY;
         m = fmaxf(m, s[j]);
@@ -127,7 +128,7 @@ __global__ void __launch_bounds__(ATT_BT) col_attention_fwd_kernel(AttnArgs a, f
         if (j < a.S) {
             const float pj = s[j] * inv_l * drop_scale(a.seed, r, h, i, j, a.p, inv_keep);
 #pragma unroll
-            for (int c = 0; c < HD; ++c) acc[c] = fmaf(pj, sv[grp][j][c], acc[c]);
+            for (int c = 0; c < HD; ++c) acc[c] = fmaf(pj, sv[grp][j * LD + c], acc[c]);
         }
     }
     st_vec<HD>(out + o, acc);
@@ -145,7 +146,8 @@ __global__ void __launch_bounds__(ATT_BT) col_attention_bwd_kernel(AttnArgs a, c
                                                                    float* __restrict__ gv) {
     constexpr int NG = ATT_BT / 8;
     constexpr int LD = HD % 4 == 0 ? HD : 4;              // 16-byte rows at least
-    __shared__ __align__(16) float sq[NG][8][LD], sk[NG][8][LD], sv[NG][8][LD], sg[NG][8][LD];
+    constexpr int GS = 8 * LD + 8;            // (as in the forward kernel: no bank conflicts between the groups of a warp)
+    __shared__ __align__(16) float sq[NG][GS], sk[NG][GS], sv[NG][GS], sg[NG][GS];
     __shared__ float sds[NG][8][9], spd[NG][8][9];
     const int grp = threadIdx.x >> 3, i = threadIdx.x & 7;
     const int64_t gid = (int64_t)blockIdx.x * NG + grp;
@@ -159,13 +161,13 @@ __global__ void __launch_bounds__(ATT_BT) col_attention_bwd_kernel(AttnArgs a, c
         ld_vec<HD>(qi, a.q + o);
         ld_vec<HD>(gi, g_out + o);
 #pragma unroll
-        for (int c = 0; c < HD; ++c) { sq[grp][i][c] = qi[c]; sg[grp][i][c] = gi[c]; }
+        for (int c = 0; c < HD; ++c) { sq[grp][i * LD + c] = qi[c]; sg[grp][i * LD + c] = gi[c]; }
         ld_vec<HD>(tmp, a.k + o);
 #pragma unroll
-        for (int c = 0; c < HD; ++c) sk[grp][i][c] = tmp[c];
+        for (int c = 0; c < HD; ++c) sk[grp][i * LD + c] = tmp[c];
         ld_vec<HD>(tmp, a.v + o);
 #pragma unroll
-        for (int c = 0; c < HD; ++c) sv[grp][i][c] = tmp[c];
+        for (int c = 0; c < HD; ++c) sv[grp][i * LD + c] = tmp[c];
     }
     __syncwarp();
     float dq[HD], dk[HD], dv[HD];
@@ -178,7 +180,7 @@ __global__ void __launch_bounds__(ATT_BT) col_attention_bwd_kernel(AttnArgs a, c
             float d = 0.f, e = 0.f;
             if (j < a.S) {
 #pragma unroll
-                for (int c = 0; c < HD; ++c) { d = fmaf(qi[c], sk[grp][j][c], d); e = fmaf(gi[c], sv[grp][j][c], e); }
+                for (int c = 0; c < HD; ++c) { d = fmaf(qi[c], sk[grp][j * LD + c], d); e = fmaf(gi[c], sv[grp][j * LD + c], e); }
             }
             s[j] = j < a.S ? d * scale : -INFINITY;
             dp[j] = j < a.S ? e * drop_scale(a.seed, r, h, i, j, a.p, inv_keep) : 0.f;
@@ -198,7 +200,7 @@ __global__ void __launch_bounds__(ATT_BT) col_attention_bwd_kernel(AttnArgs a, c
                 sds[grp][i][j] = ds;
                 spd[grp][i][j] = s[j] * drop_scale(a.seed, r, h, i, j, a.p, inv_keep);
 #pragma unroll
-                for (int c = 0; c < HD; ++c) dq[c] = fmaf(ds, sk[grp][j][c], dq[c]);
+                for (int c = 0; c < HD; ++c) dq[c] = fmaf(ds, sk[grp][j * LD + c], dq[c]);
             }
         }
     }
@@ -207,7 +209,7 @@ __global__ void __launch_bounds__(ATT_BT) col_attention_bwd_kernel(AttnArgs a, c
         for (int t = 0; t < a.S; ++t) {
             const float ds = sds[grp][t][i], pd = spd[grp][t][i];
 #pragma unroll
-            for (int c = 0; c < HD; ++c) { dk[c] = fmaf(ds, sq[grp][t][c], dk[c]); dv[c] = fmaf(pd, sg[grp][t][c], dv[c]); }
+            for (int c = 0; c < HD; ++c) { dk[c] = fmaf(ds, sq[grp][t * LD + c], dk[c]); dv[c] = fmaf(pd, sg[grp][t * LD + c], dv[c]); }
         }
         st_vec<HD>(gq + o, dq);
         st_vec<HD>(gk + o, dk);
