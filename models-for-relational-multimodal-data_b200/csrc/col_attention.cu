@@ -9,6 +9,7 @@
 // stage their tokens' slices in shared memory (each operand leaves global memory once), the rest is registers.
 // Attention-probability dropout (the layer's dropout applies to them in training) uses a counter hash
 // of (seed, row, head, i, j), recomputed in backward -- no mask tensor.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace b200mp {
@@ -134,6 +135,76 @@ __global__ void __launch_bounds__(ATT_BT) col_attention_fwd_kernel(AttnArgs a, f
     st_vec<HD>(out + o, acc);
 }
 
+// The same forward as a persistent loop: a CTA walks (row, head) groups gid, gid + stride, ... and the NEXT group's q / k / v slices are
+// in flight (registers) while the current one is computed -- the one-group-per-CTA form above alternates a load phase with a
+// compute phase and pays a CTA launch per 16 groups (524 k CTAs per 1 M rows).
+template <int HD>
+__global__ void __launch_bounds__(ATT_BT) col_attention_fwd_loop_kernel(AttnArgs a, float* __restrict__ out) {
+    constexpr int NG = ATT_BT / 8;
+    constexpr int LD = HD % 4 == 0 ? HD : 4;
+    constexpr int GS = 8 * LD + 8;
+    __shared__ __align__(16) float sk[NG][GS], sv[NG][GS];
+    const int grp = threadIdx.x >> 3, i = threadIdx.x & 7;
+    const int64_t groups = a.R * a.nhead, stride = (int64_t)gridDim.x * NG;
+    const float scale = rsqrtf((float)HD), inv_keep = a.p > 0.f ? 1.f / (1.f - a.p) : 1.f;
+    const bool tok = i < a.S;
+    float qi[HD], ki[HD], vi[HD];
+    int64_t gid = (int64_t)blockIdx.x * NG + grp;
+    auto offset = [&](int64_t g_) { return ((g_ / a.nhead) * a.S + i) * a.C + (g_ % a.nhead) * HD; };
+    if (tok && gid < groups) {
+        const int64_t o = offset(gid);
+        ld_vec<HD>(qi, a.q + o); ld_vec<HD>(ki, a.k + o); ld_vec<HD>(vi, a.v + o);
+    }
+    for (; gid - (grp & 3) < groups; gid += stride) {   // warp-uniform trip count: the four groups of a warp leave the loop together
+        const int h = (int)(gid % a.nhead);
+        const int64_t r = gid / a.nhead;
+        const bool on = tok && gid < groups;
+        if (on) {
+#pragma unroll
+            for (int c = 0; c < HD; ++c) { sk[grp][i * LD + c] = ki[c]; sv[grp][i * LD + c] = vi[c]; }
+        }
+        __syncwarp();
+        float q0[HD];
+#pragma unroll
+        for (int c = 0; c < HD; ++c) q0[c] = qi[c];
+        const int64_t nxt = gid + stride;
+        if (tok && nxt < groups) {                  // next group's slices in flight during this group's arithmetic
+            const int64_t o = offset(nxt);
+            ld_vec<HD>(qi, a.q + o); ld_vec<HD>(ki, a.k + o); ld_vec<HD>(vi, a.v + o);
+        }
+        if (on) {
+            float s[8], m = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float d = 0.f;
+                if (j < a.S) {
+#pragma unroll
+                    for (int c = 0; c < HD; ++c) d = fmaf(q0[c], sk[grp][j * LD + c], d);
+                }
+                s[j] = j < a.S ? d * scale : -INFINITY;
+                m = fmaxf(m, s[j]);
+            }
+            float l = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { s[j] = j < a.S ? __expf(s[j] - m) : 0.f; l += s[j]; }
+            const float inv_l = 1.f / l;
+            float acc[HD];
+#pragma unroll
+            for (int c = 0; c < HD; ++c) acc[c] = 0.f;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (j < a.S) {
+                    const float pj = s[j] * inv_l * drop_scale(a.seed, r, h, i, j, a.p, inv_keep);
+#pragma unroll
+                    for (int c = 0; c < HD; ++c) acc[c] = fmaf(pj, sv[grp][j * LD + c], acc[c]);
+                }
+            }
+            st_vec<HD>(out + (r * a.S + i) * a.C + h * HD, acc);
+        }
+        __syncwarp();                               // the group's shared slices are rewritten by the next iteration
+    }
+}
+
 // Backward: eight lanes per (row, head), lane i = token i (lanes >= S idle).  Each lane stages its token's q, k, v, dO
 // slices in shared memory once, computes ROW i of the probabilities (P = softmax rows, Pd = drop(P),
 // dPd_ij = dO_i . v_j, dP_ij = dPd_ij * dropscale_ij, D_i = sum_j P_ij dP_ij, dS_ij = P_ij (dP_ij - D_i)) and
@@ -229,6 +300,21 @@ extern "C" int b200mp_col_attention_fwd(const float* q, const float* k, const fl
     const int64_t groups = R * nhead;
     const unsigned grid = (unsigned)((groups + ATT_BT / 8 - 1) / (ATT_BT / 8));
     cudaStream_t st = (cudaStream_t)stream;
+    const char* lv = getenv("B200MP_ATT_LOOP");             // A/B switch: persistent forward with the next group's loads in flight
+    if (lv && lv[0] == '1') {
+        const int64_t cap = (int64_t)device_info().sms * 8;
+        const unsigned lgrid = (unsigned)((int64_t)grid < cap ? (int64_t)grid : cap);
+        switch (C / nhead) {
+            case 1: col_attention_fwd_loop_kernel<1><<<lgrid, ATT_BT, 0, st>>>(a, out); break;
+            case 2: col_attention_fwd_loop_kernel<2><<<lgrid, ATT_BT, 0, st>>>(a, out); break;
+            case 4: col_attention_fwd_loop_kernel<4><<<lgrid, ATT_BT, 0, st>>>(a, out); break;
+            case 8: col_attention_fwd_loop_kernel<8><<<lgrid, ATT_BT, 0, st>>>(a, out); break;
+            case 16: col_attention_fwd_loop_kernel<16><<<lgrid, ATT_BT, 0, st>>>(a, out); break;
+            default: return B200MP_EINVAL;
+        }
+        B200MP_LAUNCH_CHECK();
+        return 0;
+    }
     switch (C / nhead) {
         case 1: col_attention_fwd_kernel<1><<<grid, ATT_BT, 0, st>>>(a, out); break;
         case 2: col_attention_fwd_kernel<2><<<grid, ATT_BT, 0, st>>>(a, out); break;

@@ -77,3 +77,19 @@ def test_dropout_mask_consistent_between_forward_and_backward():
     # keep rate ~ 1 - p: E[out] preserved
     base = BF._col_attention_fwd(q, k, v, nhead, 0.0, 0)
     assert abs(float(out.mean()) - float(base.mean())) < 0.02
+
+
+@pytest.mark.parametrize("R,S,C,nhead,p", [(1000, 6, 64, 8, 0.0), (333, 8, 64, 8, 0.3), (257, 6, 128, 8, 0.0), (100_003, 6, 64, 8, 0.2), (101, 5, 12, 3, 0.0),
+                                           (77, 3, 16, 1, 0.1)])
+def test_forward_loop_kernel_equals_one_group_per_cta(R, S, C, nhead, p):
+    """B200MP_ATT_LOOP=1 (persistent CTAs, the next group's slices in flight during the arithmetic) is the same arithmetic per
+    (row, head): bit for bit, dropout mask included, also where the group count is not a multiple of the groups per warp"""
+    import os
+    g = torch.Generator(device="cuda").manual_seed(R)
+    q, k, v = (torch.randn(R, S, C, device="cuda", generator=g) for _ in range(3))
+    outs = []
+    for flag in ("0", "1"):
+        os.environ["B200MP_ATT_LOOP"] = flag
+        outs.append(BF._col_attention_fwd(q, k, v, nhead, p, 1234567))
+    os.environ.pop("B200MP_ATT_LOOP")
+    assert torch.equal(outs[0], outs[1])
